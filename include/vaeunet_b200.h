@@ -1,0 +1,187 @@
+/* vaeunet_b200 — C ABI of the B200-native VAE-UNet hot path.
+ *
+ * The reference (tmuird/VAEUNET) has no FFI layer: its boundary is the PyTorch module surface
+ * (SURVEY.md 8b). This header is what the torch custom-op shims in vaeunet_b200/ops.py bind
+ * (ctypes); every entry point names the reference operation it replaces (file:line in the
+ * upstream repo). Conventions:
+ *   - all pointers are DEVICE pointers unless the name ends in _host; activations are
+ *     NHWC-contiguous 16-bit (bf16 by default, fp16 when dtype == VU_F16) unless stated;
+ *   - `ctot` is the channel pitch of a buffer, `coff` the first channel of the slice used
+ *     (concat is done by writing into channel slices; torch.cat never runs);
+ *   - kernels are enqueued on `stream` and never synchronise; no allocation happens inside;
+ *   - return 0 on success or a negative vu_status; vu_last_error() gives a thread-local text.
+ */
+#ifndef VAEUNET_B200_H
+#define VAEUNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* vu_stream_t; /* cudaStream_t */
+
+enum vu_status {
+    VU_OK = 0,
+    VU_ERR_INVALID = -1,     /* bad shape / argument */
+    VU_ERR_ALIGN = -2,       /* misaligned pointer or channel offset */
+    VU_ERR_UNSUPPORTED = -3, /* combination not implemented */
+    VU_ERR_CUDA = -4,        /* CUDA runtime / driver error */
+    VU_ERR_NO_DEVICE = -5    /* no sm_100 device: there is no CPU fallback */
+};
+enum vu_dtype { VU_BF16 = 0, VU_F16 = 1 };
+
+const char* vu_last_error(void);
+int vu_version(void);
+/* 0 when the current device is sm_100 (B200), VU_ERR_NO_DEVICE otherwise. */
+int vu_device_check(void);
+
+/* ---------------------------------------------------------------- dense contractions
+ * Implicit-GEMM convolution on tcgen05/TMEM, operands staged by TMA (128B swizzle).
+ * Replaces nn.Conv2d (+ folded eval BatchNorm2d + ReLU + residual add) everywhere on the path:
+ *   3x3 s1 p1  unet/unet_parts.py:40,43 ; unet/unet_resnet.py:60,66 ; ResNet BasicBlock convs
+ *   3x3 s2 p1 / 1x1 s2 ResNet stage entry + downsample shortcut (timm call site unet_resnet.py:131)
+ *   1x1 s1     attention W_g / W_x unet/unet_parts.py:10-17, unet/unet_resnet.py:9-16
+ *   ConvTranspose2d k2 s2 (unet/unet_parts.py:76) as four 1x1 GEMMs with a pixel-shuffle store
+ *     (out_up = 2, out_dh/out_dw select the sub-pixel).
+ * y[n, ho*out_up+out_dh, wo*out_up+out_dw, y_coff+co] =
+ *     act( scale[co] * sum_{r,s,ci} x[n, ho*stride+r-pad, wo*stride+s-pad, x_coff+ci] * w[co][r*KW+s][ci]
+ *          + bias[co] + residual[n,ho,wo,res_coff+co] )
+ */
+typedef struct vu_conv_args {
+    const void* x; int N, H, W, x_ctot, x_coff, Cin;
+    const void* w;            /* packed [Cout][KH*KW][Cin], 16-bit (vu_pack_conv_weight) */
+    int Cout, KH, KW, stride, pad;
+    const float* scale;       /* [Cout] fp32 or NULL (1)  — folded BN gamma/sqrt(var+eps) */
+    const float* bias;        /* [Cout] fp32 or NULL (0)  — folded BN beta - mean*scale (+ conv bias) */
+    const void* residual; int res_ctot, res_coff;  /* NHWC at output resolution, or NULL */
+    int relu;
+    void* y; int y_ctot, y_coff;
+    int out_up, out_dh, out_dw;  /* 1,0,0 for ordinary convs */
+    int dtype;                   /* vu_dtype */
+    int max_ctas;                /* 0 = one persistent CTA per SM */
+} vu_conv_args;
+int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
+
+/* OIHW fp32 -> [O][KH*KW][I] 16-bit. transpose_io: weight is IOHW (ConvTranspose2d). */
+int vu_pack_conv_weight(const float* w_oihw, void* w_packed, int O, int I, int KH, int KW,
+                        int transpose_io, int dtype, vu_stream_t stream);
+/* ConvTranspose2d k2 s2 weight [I][O][2][2] fp32 -> four packed 1x1 filters [4][O][1][I]. */
+int vu_pack_convT2x2_weight(const float* w_iohw, void* w_packed, int I, int O, int dtype,
+                            vu_stream_t stream);
+
+/* ---------------------------------------------------------------- layout / pooling / resize */
+/* NCHW fp32 -> NHWC 16-bit into a channel slice (first op on images; train.py:382). */
+int vu_nchw_to_nhwc(const float* x, void* y, int N, int C, int H, int W, int y_ctot, int y_coff,
+                    int dtype, vu_stream_t stream);
+/* NHWC 16-bit slice -> NCHW fp32 (module-surface returns). */
+int vu_nhwc_to_nchw(const void* x, float* y, int N, int C, int H, int W, int x_ctot, int x_coff,
+                    int dtype, vu_stream_t stream);
+/* ResNet stem conv 7x7 s2 p3 (Cin <= 4) + folded BN + ReLU, NCHW fp32 in -> NHWC 16-bit out.
+ * (timm resnet34 conv1/bn1/act1 reached from unet/unet_resnet.py:131-137,201). w: OIHW fp32. */
+int vu_stem_conv7x7s2(const float* x_nchw, const float* w_oihw, const float* scale, const float* bias,
+                      void* y, int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff,
+                      int dtype, vu_stream_t stream);
+/* Direct 3x3 s1 p1 conv for tiny Cin (basic UNet `inc`, unet/unet_parts.py:40 with Cin = n_channels). */
+int vu_conv3x3_small_cin(const float* x_nchw, const float* w_oihw, const float* scale, const float* bias,
+                         void* y, int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff,
+                         int relu, int dtype, vu_stream_t stream);
+/* MaxPool2d(k, s, p) on NHWC 16-bit: (3,2,1) ResNet stem pool; (2,2,0) unet/unet_parts.py:57. */
+int vu_maxpool_nhwc(const void* x, void* y, int N, int H, int W, int C, int x_ctot, int x_coff,
+                    int k, int s, int p, int y_ctot, int y_coff, int dtype, vu_stream_t stream);
+/* F.interpolate(mode='bilinear', align_corners=True) NHWC 16-bit -> channel slice
+ * (unet/unet_resnet.py:79; nn.Upsample unet/unet_parts.py:73). pad_*: F.pad offsets of Up
+ * (unet/unet_parts.py:88) — destination is [N,Hd,Wd], the resized map lands at (pad_t,pad_l). */
+int vu_bilinear_ac_nhwc(const void* x, void* y, int N, int Hs, int Ws, int C, int x_ctot, int x_coff,
+                        int Ho, int Wo, int Hd, int Wd, int pad_t, int pad_l, int y_ctot, int y_coff,
+                        int dtype, vu_stream_t stream);
+/* Broadcast per-image vectors v[Nimg][C] (fp32) over H x W into a channel slice: the spatially
+ * constant maps z_initial(z_spatial) and z_proj(z) (unet/unet_resnet.py:93-94,221-226). */
+int vu_broadcast_vec_nhwc(const float* v, void* y, int N, int H, int W, int C, int y_ctot, int y_coff,
+                          int dtype, vu_stream_t stream);
+
+/* ---------------------------------------------------------------- attention gate
+ * out = skip * sigmoid(psi_scale * <psi_w, relu(g1 + x1)> + psi_bias)
+ * (unet/unet_parts.py:24-30 == unet/unet_resnet.py:24-29). g1 = BN(W_g g) [Ng,H,W,F] and
+ * x1 = BN(W_x skip) [Ns,H,W,F] come from vu_conv2d_fwd; Ng = Ns * rep (rep MC samples share one
+ * skip/x1). psi_w fp32 [F]; psi (optional, fp32 [Ng,H,W]) keeps the gate map for hooks. */
+int vu_attention_gate(const void* g1, int g1_ctot, int g1_coff, const void* x1, int x1_ctot, int x1_coff,
+                      const void* skip, int skip_ctot, int skip_coff, const float* psi_w,
+                      float psi_scale, float psi_bias, void* out, int out_ctot, int out_coff,
+                      float* psi, int Ng, int rep, int H, int W, int F, int Cl, int dtype,
+                      vu_stream_t stream);
+
+/* ---------------------------------------------------------------- latent head
+ * mu/logvar = GAP(conv1x1(f4) + b) = W * mean_hw(f4) + b (unet/unet_resnet.py:140-147,205-206;
+ * utils/vae_utils.py:13-25), then for every MC sample n: z[n,b,:] = mu + eps[n,b,:]*exp(.5 logvar)*T
+ * (utils/vae_utils.py:5-10,47-50; unet_resnet.py:191-194). f4 NHWC 16-bit [B,h,w,C]; w_mu/w_lv fp32
+ * [L][C]; eps fp32 [Ns,B,L] or NULL (z = mu). Outputs fp32: mu,logvar [B,L]; z [Ns,B,L]. */
+int vu_latent_head(const void* f4, int B, int h, int w, int C, int f_ctot, int f_coff,
+                   const float* w_mu, const float* b_mu, const float* w_lv, const float* b_lv,
+                   const float* eps, float temperature, int Ns, int L,
+                   float* mu, float* logvar, float* z, int dtype, vu_stream_t stream);
+/* v[i,:] = act(scale * (W z[i,:] + b) + shift): the 1x1 conv + BN + ReLU applied to a spatially
+ * constant map (z_initial unet_resnet.py:150-154; z_proj :37-41). z fp32 [M][L], W fp32 [C][L]. */
+int vu_latent_project(const float* z, const float* w, const float* scale, const float* shift,
+                      float* v, int M, int L, int C, int relu, vu_stream_t stream);
+
+/* ---------------------------------------------------------------- output head + uncertainty
+ * final_conv 1x1 C->1 + bias on NHWC 16-bit -> fp32 logits [N,H,W] (unet_resnet.py:189,237;
+ * OutConv unet/unet_parts.py:97-103 for n_classes = 1). */
+int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_ctot, int x_coff,
+                   const float* w, float bias, float* logits, int dtype, vu_stream_t stream);
+/* bilinear (align_corners=True) resize of fp32 maps [N,Hs,Ws] -> [N,Ho,Wo], optional sigmoid
+ * before (predict_with_patches order, visualize_vae.py:345-358) or after (forward /
+ * predict_full_image order, unet_resnet.py:238; visualize_vae.py:81-83). mode: 0 none, 1 pre, 2 post */
+int vu_resize_logits(const float* x, float* y, int N, int Hs, int Ws, int Ho, int Wo, int sigmoid_mode,
+                     vu_stream_t stream);
+/* calculate_uncertainty_metrics (visualize_vae.py:90-117) fused with the final upsample+sigmoid:
+ * logits fp32 [B, Ns, Hs, Ws] (sample-minor per patch) -> per-pixel over Ns:
+ * mean, unbiased std, entropy of mean, mutual information, coeff. of variation, each [B,Ho,Wo] fp32
+ * (any output pointer may be NULL). input_is_prob: skip resize+sigmoid (maps already [B,Ns,Ho,Wo]).
+ * probs_out (optional) receives the per-sample probability maps [B,Ns,Ho,Wo]. */
+int vu_uncertainty_reduce(const float* logits, int B, int Ns, int Hs, int Ws, int Ho, int Wo,
+                          int input_is_prob, float* mean, float* stdev, float* entropy,
+                          float* mutual_info, float* coeff_var, float* probs_out, vu_stream_t stream);
+/* Chan merge of per-shard moments for sample-sharded MC: (count, mean, M2, sumH). */
+int vu_moments_partial(const float* probs, int Ns, size_t npix, float* mean, float* m2, float* sum_ent,
+                       vu_stream_t stream);
+int vu_moments_finalize(const float* counts_host, const float* mean, const float* m2, const float* sum_ent,
+                        int nshards, size_t npix, float* out_mean, float* out_std, float* out_entropy,
+                        float* out_mi, float* out_cv, vu_stream_t stream);
+
+/* ---------------------------------------------------------------- tile blending
+ * predict_with_patches accumulation (visualize_vae.py:361-384,409): ramp weights are analytic in
+ * tile coordinates. acc/wsum fp32 [H,W]; tile fp32 [ph,pw] probabilities. */
+int vu_blend_accumulate(const float* tile, int ph, int pw, int sh, int sw, int ti, int tj, int nth, int ntw,
+                        int overlap, float* acc, float* wsum, int H, int W, vu_stream_t stream);
+int vu_blend_finalize(const float* acc, const float* wsum, float* out, size_t n, vu_stream_t stream);
+
+/* ---------------------------------------------------------------- losses / metrics
+ * One pass over logits+targets -> 8 partial sums (fp64 accumulators in `sums`):
+ *   [0] sum p, [1] sum t, [2] sum p*t, [3] sum BCE-with-logits, [4] sum focal term,
+ *   [5] count, [6] sum (p-t)^2 (Brier), [7] sum NLL(clamp(p,1e-9))
+ * (utils/loss.py:6-28,54-63,75-92; utils/uncertainty_metrics.py:137-139,334-338).
+ * input_is_prob: x already holds probabilities (metrics on mean maps). */
+int vu_seg_loss_sums(const float* x, const float* target, size_t n, int input_is_prob,
+                     float focal_alpha, float focal_gamma, double* sums, vu_stream_t stream);
+/* d(loss)/d(logits) for  w_bce*BCE + w_dice*dice + w_focal*focal, from the sums above. */
+int vu_seg_loss_bwd(const float* logits, const float* target, size_t n, const double* sums,
+                    float w_bce, float w_dice, float w_focal, float focal_alpha, float focal_gamma,
+                    float smooth, float grad_scale, float* dlogits, vu_stream_t stream);
+/* kl_with_free_bits (utils/loss.py:148-170) forward value + analytic grads. */
+int vu_kl_free_bits(const float* mu, const float* logvar, int B, int L, float free_bits,
+                    float* kl_out, float* dmu, float* dlogvar, float grad_scale, vu_stream_t stream);
+/* ECE histogram (utils/uncertainty_metrics.py:108-135): per-bin count, sum gt, sum p (fp64 [3*bins]). */
+int vu_ece_hist(const float* p, const float* gt, size_t n, int num_bins, double* hist, vu_stream_t stream);
+/* Thresholded confusion counts (utils/metrics.py:98-117; uncertainty_metrics.py:340-353):
+ * counts[0..3] = tp, fp, tn, fn of (x > thr) vs (t > 0.5) as fp64. */
+int vu_confusion_counts(const float* x, const float* t, size_t n, float thr, double* counts,
+                        vu_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VAEUNET_B200_H */

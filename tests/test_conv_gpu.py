@@ -1,0 +1,90 @@
+"""GPU parity of the tcgen05 implicit-GEMM conv (through the C ABI) against torch CPU fp32
+F.conv2d on the same 16-bit-rounded operands (the oracle's primitive)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    # name, N, H, W, Cin, Cout, k, stride, relu, residual, x_extra(coff,ctot+), y_extra, dtype
+    ("3x3_64_64", 2, 32, 32, 64, 64, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_partialK_224", 1, 40, 40, 224, 64, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_800_512_res", 3, 16, 16, 800, 512, 3, 1, True, True, (0, 0), (0, 0), "bf16"),
+    ("1x1_512_128", 2, 32, 32, 512, 128, 1, 1, False, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_s2_64_128", 2, 32, 32, 64, 128, 3, 2, True, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_s2_odd", 2, 35, 29, 64, 128, 3, 2, True, False, (0, 0), (0, 0), "bf16"),
+    ("1x1_s2_ds", 2, 32, 32, 64, 128, 1, 2, False, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_slices", 2, 24, 24, 96, 64, 3, 1, True, False, (32, 160), (64, 192), "bf16"),
+    ("3x3_tiny_maps", 5, 4, 4, 128, 256, 3, 1, True, True, (0, 0), (0, 0), "bf16"),
+    ("3x3_cin32", 2, 16, 16, 32, 32, 3, 1, False, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_fp16", 2, 32, 32, 128, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("3x3_22x22", 2, 22, 22, 256, 256, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_1024", 1, 32, 32, 1024, 1024, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("3x3_big_persistent", 4, 128, 128, 64, 64, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_conv_igemm(case, cuda_dev):
+    from vaeunet_b200 import ops
+    name, N, H, W, Cin, Cout, k, stride, relu, use_res, xs, ys, dt = case
+    tdt = torch.bfloat16 if dt == "bf16" else torch.float16
+    odt = ops.BF16 if dt == "bf16" else ops.F16
+    g = torch.Generator().manual_seed(hash(name) % (2 ** 31))
+    pad = 1 if k == 3 else 0
+    x = torch.randn(N, Cin, H, W, generator=g)
+    w = torch.randn(Cout, Cin, k, k, generator=g) * (1.0 / (Cin * k * k) ** 0.5)
+    scale = torch.rand(Cout, generator=g) + 0.5
+    bias = torch.randn(Cout, generator=g) * 0.1
+    xq = x.to(tdt).float()
+    wq = w.to(tdt).float()
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    res = torch.randn(N, Cout, Ho, Wo, generator=g).to(tdt).float() if use_res else None
+    ref = F.conv2d(xq, wq, None, stride, pad) * scale.view(1, -1, 1, 1) + bias.view(1, -1, 1, 1)
+    if use_res:
+        ref = ref + res
+    if relu:
+        ref = F.relu(ref)
+
+    dev = cuda_dev
+    x_ctot = xs[1] if xs[1] else Cin
+    xbuf = torch.full((N, H, W, x_ctot), 7.0, dtype=tdt, device=dev)
+    xbuf[..., xs[0]:xs[0] + Cin] = xq.permute(0, 2, 3, 1).to(tdt).to(dev)
+    xa = ops.Act(xbuf, xs[0], Cin)
+    y_ctot = ys[1] if ys[1] else Cout
+    ybuf = torch.full((N, Ho, Wo, y_ctot), -3.0, dtype=tdt, device=dev)
+    ya = ops.Act(ybuf, ys[0], Cout)
+    wp = ops.pack_conv_weight(w.to(dev), odt)
+    ra = ops.Act(res.permute(0, 2, 3, 1).contiguous().to(tdt).to(dev)) if use_res else None
+    ops.conv2d(xa, wp, k, stride, pad, scale.to(dev), bias.to(dev), relu, out=ya, residual=ra)
+    torch.cuda.synchronize()
+    got = ybuf[..., ys[0]:ys[0] + Cout].float().cpu().permute(0, 3, 1, 2)
+    err = (got - ref).abs().max().item()
+    tol = 2e-2 * ref.abs().max().item()
+    assert err <= tol, f"{name}: max err {err} > {tol}"
+    rel = ((got - ref).norm() / ref.norm()).item()
+    assert rel < 6e-3, f"{name}: rel l2 err {rel}"
+    if ys[1]:  # untouched channels of the concat buffer stay untouched
+        assert (ybuf[..., :ys[0]].float() == -3.0).all() and (ybuf[..., ys[0] + Cout:].float() == -3.0).all()
+
+
+def test_convT2x2_pixel_shuffle(cuda_dev):
+    """ConvTranspose2d k2 s2 (unet/unet_parts.py:76) as four 1x1 GEMMs with out_up=2."""
+    from vaeunet_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    N, Cin, Cout, H, W = 2, 128, 64, 16, 16
+    x = torch.randn(N, Cin, H, W, generator=g)
+    w = torch.randn(Cin, Cout, 2, 2, generator=g) * 0.1
+    b = torch.randn(Cout, generator=g) * 0.1
+    xq, wq = x.bfloat16().float(), w.bfloat16().float()
+    ref = F.conv_transpose2d(xq, wq, b, stride=2)
+    dev = cuda_dev
+    xa = ops.Act(xq.permute(0, 2, 3, 1).contiguous().bfloat16().to(dev))
+    wp = ops.pack_convT2x2_weight(w.to(dev))
+    out = ops.new_act(N, 2 * H, 2 * W, Cout)
+    for ab in range(4):
+        ops.conv2d(xa, wp[ab], 1, 1, 0, None, b.to(dev), False, out=out, out_up=2, out_dh=ab // 2, out_dw=ab % 2)
+    torch.cuda.synchronize()
+    got = out.t.float().cpu().permute(0, 3, 1, 2)
+    assert (got - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()

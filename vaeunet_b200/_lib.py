@@ -1,0 +1,108 @@
+"""ctypes binding of libvaeunet_b200.so (the C ABI declared in include/vaeunet_b200.h).
+
+There is NO CPU fallback: importing works anywhere (so `state_dict` surgery and host logic can be
+tested on CPU), but any compute call raises `VaeUnetError` unless the extension is built and a
+B200 (sm_100) device is current.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "libvaeunet_b200.so"
+
+
+class VaeUnetError(RuntimeError):
+    pass
+
+
+class ConvArgs(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("x_ctot", C.c_int), ("x_coff", C.c_int), ("Cin", C.c_int),
+        ("w", C.c_void_p),
+        ("Cout", C.c_int), ("KH", C.c_int), ("KW", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
+        ("scale", C.c_void_p), ("bias", C.c_void_p),
+        ("residual", C.c_void_p), ("res_ctot", C.c_int), ("res_coff", C.c_int),
+        ("relu", C.c_int),
+        ("y", C.c_void_p), ("y_ctot", C.c_int), ("y_coff", C.c_int),
+        ("out_up", C.c_int), ("out_dh", C.c_int), ("out_dw", C.c_int),
+        ("dtype", C.c_int), ("max_ctas", C.c_int),
+    ]
+
+
+i, f, p, sz = C.c_int, C.c_float, C.c_void_p, C.c_size_t
+# name -> argtypes (every symbol declared in include/vaeunet_b200.h)
+SIGNATURES = {
+    "vu_version": [],
+    "vu_device_check": [],
+    "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
+    "vu_pack_conv_weight": [p, p, i, i, i, i, i, i, p],
+    "vu_pack_convT2x2_weight": [p, p, i, i, i, p],
+    "vu_nchw_to_nhwc": [p, p, i, i, i, i, i, i, i, p],
+    "vu_nhwc_to_nchw": [p, p, i, i, i, i, i, i, i, p],
+    "vu_stem_conv7x7s2": [p, p, p, p, p, i, i, i, i, i, i, i, i, p],
+    "vu_conv3x3_small_cin": [p, p, p, p, p, i, i, i, i, i, i, i, i, i, p],
+    "vu_maxpool_nhwc": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_bilinear_ac_nhwc": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_broadcast_vec_nhwc": [p, p, i, i, i, i, i, i, i, p],
+    "vu_attention_gate": [p, i, i, p, i, i, p, i, i, p, f, f, p, i, i, p, i, i, i, i, i, i, i, p],
+    "vu_latent_head": [p, i, i, i, i, i, i, p, p, p, p, p, f, i, i, p, p, p, i, p],
+    "vu_latent_project": [p, p, p, p, p, i, i, i, i, p],
+    "vu_final_conv1": [p, i, i, i, i, i, i, p, f, p, i, p],
+    "vu_resize_logits": [p, p, i, i, i, i, i, i, p],
+    "vu_uncertainty_reduce": [p, i, i, i, i, i, i, i, p, p, p, p, p, p, p],
+    "vu_moments_partial": [p, i, sz, p, p, p, p],
+    "vu_moments_finalize": [p, p, p, p, i, sz, p, p, p, p, p, p],
+    "vu_blend_accumulate": [p, i, i, i, i, i, i, i, i, i, p, p, i, i, p],
+    "vu_blend_finalize": [p, p, p, sz, p],
+    "vu_seg_loss_sums": [p, p, sz, i, f, f, p, p],
+    "vu_seg_loss_bwd": [p, p, sz, p, f, f, f, f, f, f, f, p, p],
+    "vu_kl_free_bits": [p, p, i, i, f, p, p, p, f, p],
+    "vu_ece_hist": [p, p, sz, i, p, p],
+    "vu_confusion_counts": [p, p, sz, f, p, p],
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the extension; fail loudly if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise VaeUnetError(
+            f"{LIB_PATH} is not built. Run `python -m vaeunet_b200.build` (needs nvcc). "
+            "vaeunet_b200 has no CPU / eager fallback.")
+    lib = C.CDLL(str(LIB_PATH))
+    lib.vu_last_error.restype = C.c_char_p
+    lib.vu_last_error.argtypes = []
+    for name, argt in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so is stale
+        fn.restype = C.c_int
+        fn.argtypes = argt
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().vu_last_error().decode("utf-8", "replace")
+        raise VaeUnetError(f"{what} failed (vu_status {rc}): {msg}")
+
+
+_device_ok = None
+
+
+def require_device() -> None:
+    """Raise unless a B200-class device is current (product path has no fallback)."""
+    global _device_ok
+    if _device_ok:
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise VaeUnetError("vaeunet_b200 needs a CUDA sm_100 (B200) device; none is visible and there is no CPU fallback")
+    check(load().vu_device_check(), "vu_device_check")
+    _device_ok = True

@@ -1,0 +1,427 @@
+// Implicit-GEMM convolution for sm_100a: tcgen05.mma (UMMA 128 x BN x 16, bf16/fp16 -> fp32 in
+// TMEM), operands staged by TMA with 128-byte swizzle, persistent warp-specialised CTAs.
+//
+//   GEMM view:  M = output pixels (tiles of 128 = Nt x Ht x Wt pixels of the NHWC map),
+//               N = Cout (tiles of BN), K = taps x Cin (blocks of 64 channels per tap).
+//   A operand:  for tap (r,s) the 128 x 64 tile is ONE 4-D TMA box (64ch, Wt, Ht, Nt) of the NHWC
+//               activation tensor shifted by (r-pad, s-pad); zero padding = TMA out-of-bounds fill.
+//               Stride-2 convs read the four (row,col)-parity planes of the input through four
+//               strided tensor maps, so every tap is again a unit-stride box.
+//   B operand:  packed weights [Cout][tap][Cin] through a 3-D map, box (64ch, 1, BN).
+//   Both land in smem as rows of 128 B in the canonical K-major SWIZZLE_128B layout.
+//   Roles:      warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one lane),
+//               warps 2..5 = epilogue (TMEM -> regs -> scale/bias/residual/ReLU -> 16-bit NHWC slice).
+//   Pipelines:  smem full/empty ring (kStages), TMEM full/empty (2 accumulators) so the epilogue of
+//               tile i overlaps the MMAs of tile i+1.
+#include "vu_ptx.cuh"
+#include "vu_internal.h"
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+namespace vu {
+
+constexpr int kTileM = 128;
+constexpr int kBlockK = 64;                       // channels per K block (128 B rows)
+constexpr int kABytes = kTileM * kBlockK * 2;     // 16 KB
+constexpr int kMaxTaps = 9;
+constexpr int kMaxCout = 1024;
+constexpr int kThreads = 192;
+
+struct ConvKParams {
+    int n_img, ho, wo;             // output-resolution grid the M tiles cover
+    int wt, ht, nt;                // tile = nt x ht x wt pixels (product 128)
+    int tiles_w, tiles_h, tiles_n;
+    int num_m_tiles, num_n_tiles;
+    int cout;
+    int num_taps, kblocks, last_ksteps;
+    int8_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_map[kMaxTaps], tap_widx[kMaxTaps];
+    const float* scale; const float* bias;
+    const uint16_t* residual; int res_ctot, res_coff;
+    uint16_t* y; int y_ctot, y_coff;
+    int out_h, out_w, out_up, out_dh, out_dw;
+    int relu, dtype;
+};
+
+template <int BN> struct ConvCfg {
+    static constexpr int kBBytes = BN * kBlockK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
+    static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
+    static constexpr int kBarBytes = 1024;  // barriers + tmem ptr
+    static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes +
+                                      2 * kMaxCout * 4;
+};
+
+__device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
+    if (dtype == 0) {
+        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&v);
+    } else {
+        __half2 v = __floats2half2_rn(a, b);
+        return *reinterpret_cast<uint32_t*>(&v);
+    }
+}
+__device__ __forceinline__ float2 unpack2(uint32_t u, int dtype) {
+    if (dtype == 0) {
+        __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
+        return __bfloat1622float2(v);
+    } else {
+        __half2 v = *reinterpret_cast<__half2*>(&u);
+        return __half22float2(v);
+    }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
+                  const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a3,
+                  const __grid_constant__ CUtensorMap map_w, const ConvKParams p) {
+    using Cfg = ConvCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+    // barrier slots (8 B each)
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 4);
+    volatile uint32_t* tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
+    float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
+    float* s_bias = s_scale + kMaxCout;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_a0);
+        tma_prefetch_desc(&map_w);
+        for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 128); }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+        tmem_relinquish();
+    }
+    for (int c = threadIdx.x; c < p.cout; c += kThreads) {
+        s_scale[c] = p.scale ? p.scale[c] : 1.0f;
+        s_bias[c] = p.bias ? p.bias[c] : 0.0f;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+    const int k_iters = p.num_taps * p.kblocks;
+
+    if (warp == 0) {
+        // ===================== TMA producer (one lane) =====================
+        if (lane == 0) {
+            const CUtensorMap* maps[4] = {&map_a0, &map_a1, &map_a2, &map_a3};
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int n_tile = tile % p.num_n_tiles;
+                const int m_tile = tile / p.num_n_tiles;
+                const int wb = m_tile % p.tiles_w;
+                const int hb = (m_tile / p.tiles_w) % p.tiles_h;
+                const int nb = m_tile / (p.tiles_w * p.tiles_h);
+                const int w0 = wb * p.wt, h0 = hb * p.ht, n0 = nb * p.nt;
+                for (int tap = 0; tap < p.num_taps; ++tap) {
+                    const CUtensorMap* ma = maps[p.tap_map[tap]];
+                    const int ww = w0 + p.tap_dw[tap], hh = h0 + p.tap_dh[tap];
+                    const int widx = p.tap_widx[tap];
+                    for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+                        const int s = it % Cfg::kStages;
+                        const uint32_t ph = (it / Cfg::kStages) & 1;
+                        mbar_wait(empty_bar(s), ph ^ 1);
+                        const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                        mbar_arrive_expect_tx(full_bar(s), Cfg::kStageBytes);
+                        tma_load_4d(sa, ma, full_bar(s), kb * kBlockK, ww, hh, n0);
+                        tma_load_3d(sa + kABytes, &map_w, full_bar(s), kb * kBlockK, widx, n_tile * BN);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (one lane) =====================
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_f16(kTileM, BN, p.dtype == 0 ? 1u : 0u);
+            uint32_t it = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+                const int acc = tcount & 1;
+                const uint32_t accph = (tcount >> 1) & 1;
+                mbar_wait(tempty_bar(acc), accph ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int ki = 0; ki < k_iters; ++ki, ++it) {
+                    const int s = it % Cfg::kStages;
+                    const uint32_t ph = (it / Cfg::kStages) & 1;
+                    mbar_wait(full_bar(s), ph);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                    const uint64_t adesc = umma_desc_k_sw128(sa);
+                    const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
+                    const int kb = ki % p.kblocks;
+                    const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
+                    for (int k = 0; k < nk; ++k) {
+                        // +32 B per K=16 step inside the 128 B swizzle row (encoded >> 4)
+                        umma_f16_ss(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
+                    }
+                    umma_commit(empty_bar(s));
+                }
+                umma_commit(tfull_bar(acc));
+            }
+        }
+    } else {
+        // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+        const int q = warp & 3;                   // TMEM lane quarter this warp may access
+        const int m = q * 32 + lane;              // row of the tile = pixel
+        const int w_l = m % p.wt;
+        const int h_l = (m / p.wt) % p.ht;
+        const int n_l = m / (p.wt * p.ht);
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+            const int acc = tcount & 1;
+            const uint32_t accph = (tcount >> 1) & 1;
+            const int n_tile = tile % p.num_n_tiles;
+            const int m_tile = tile / p.num_n_tiles;
+            const int wb = m_tile % p.tiles_w;
+            const int hb = (m_tile / p.tiles_w) % p.tiles_h;
+            const int nb = m_tile / (p.tiles_w * p.tiles_h);
+            const int wo = wb * p.wt + w_l, ho = hb * p.ht + h_l, ni = nb * p.nt + n_l;
+            const bool valid = (wo < p.wo) && (ho < p.ho) && (ni < p.n_img);
+            const size_t opix = (static_cast<size_t>(ni) * p.out_h + (ho * p.out_up + p.out_dh)) * p.out_w +
+                                (wo * p.out_up + p.out_dw);
+            const size_t rpix = (static_cast<size_t>(ni) * p.ho + ho) * p.wo + wo;
+            mbar_wait(tfull_bar(acc), accph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(taddr + c * 32, r);
+                tmem_ld_wait();
+                const int ch0 = n_tile * BN + c * 32;
+                uint32_t outw[16];
+                uint4 rv[4];
+                if (p.residual != nullptr && valid) {
+                    const uint4* rp = reinterpret_cast<const uint4*>(
+                        p.residual + rpix * p.res_ctot + p.res_coff + ch0);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+                }
+                const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    float v0 = __uint_as_float(r[2 * j]) * s_scale[ch0 + 2 * j] + s_bias[ch0 + 2 * j];
+                    float v1 = __uint_as_float(r[2 * j + 1]) * s_scale[ch0 + 2 * j + 1] + s_bias[ch0 + 2 * j + 1];
+                    if (p.residual != nullptr) {
+                        float2 rr = unpack2(rw[j], p.dtype);
+                        v0 += rr.x; v1 += rr.y;
+                    }
+                    if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
+                    outw[j] = pack2(v0, v1, p.dtype);
+                }
+                if (valid) {
+                    uint4* op = reinterpret_cast<uint4*>(p.y + opix * p.y_ctot + p.y_coff + ch0);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        op[j] = make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(tempty_bar(acc));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(f);
+    }
+    return fn;
+}
+
+static int encode_map(CUtensorMap* m, int dtype, int rank, const void* base, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box) {
+    PFN_encodeTiled fn = get_encode_fn();
+    if (!fn) return set_error(VU_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(m, dtype == 0 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                    rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(VU_ERR_CUDA, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+    return 0;
+}
+
+static int pow2_ge(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+// choose (wt, ht, nt), product 128, maximising the fraction of useful rows
+static void choose_tile(int n, int h, int w, int* wt_o, int* ht_o, int* nt_o) {
+    double best = -1.0;
+    for (int wt = 128; wt >= 1; wt >>= 1) {
+        for (int ht = 128 / wt; ht >= 1; ht >>= 1) {
+            const int nt = 128 / (wt * ht);
+            if (nt > 128) continue;
+            const double cover = (double)((w + wt - 1) / wt * wt) * ((h + ht - 1) / ht * ht) *
+                                 ((n + nt - 1) / nt * nt);
+            const double eff = (double)w * h * n / cover;
+            if (eff > best + 1e-9) { best = eff; *wt_o = wt; *ht_o = ht; *nt_o = nt; }
+        }
+    }
+}
+
+template <int BN>
+static int launch_conv(const CUtensorMap* am, const CUtensorMap& wm, const ConvKParams& kp, int max_ctas,
+                       cudaStream_t stream) {
+    using Cfg = ConvCfg<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::kSmemBytes);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    int grid = kp.num_m_tiles * kp.num_n_tiles;
+    const int sms = num_sms();
+    int cap = (max_ctas > 0) ? max_ctas : sms;
+    if (grid > cap) grid = cap;
+    conv_igemm_kernel<BN><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(am[0], am[1], am[2], am[3], wm, kp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_igemm launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!a || !a->x || !a->w || !a->y) return set_error(VU_ERR_INVALID, "conv: null pointer");
+    const int KH = a->KH, KW = a->KW, S = a->stride, P = a->pad;
+    const bool ok_geom = (KH == KW) && ((KH == 3 && P == 1) || (KH == 1 && P == 0)) && (S == 1 || S == 2);
+    if (!ok_geom) return set_error(VU_ERR_UNSUPPORTED, "conv: only 3x3 p1 / 1x1 p0, stride 1|2 (got k%d s%d p%d)", KH, S, P);
+    if (a->Cin < 8 || a->Cin % 8 || a->x_ctot % 8 || a->x_coff % 8 || a->y_ctot % 8 || a->y_coff % 8)
+        return set_error(VU_ERR_ALIGN, "conv: channel counts/offsets must be multiples of 8 (Cin=%d x_ctot=%d x_coff=%d y_ctot=%d y_coff=%d)",
+                         a->Cin, a->x_ctot, a->x_coff, a->y_ctot, a->y_coff);
+    if (a->residual && (a->res_ctot % 8 || a->res_coff % 8)) return set_error(VU_ERR_ALIGN, "conv: residual slice misaligned");
+    if (a->Cout % 32 || a->Cout > kMaxCout) return set_error(VU_ERR_UNSUPPORTED, "conv: Cout must be a multiple of 32 and <= %d (got %d)", kMaxCout, a->Cout);
+    if ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->w) | reinterpret_cast<uintptr_t>(a->y) |
+         reinterpret_cast<uintptr_t>(a->residual)) & 15)
+        return set_error(VU_ERR_ALIGN, "conv: pointers must be 16-byte aligned");
+    if (a->N < 1 || a->H < 1 || a->W < 1) return set_error(VU_ERR_INVALID, "conv: empty input");
+    const int up = a->out_up > 0 ? a->out_up : 1;
+
+    const int Ho = (a->H + 2 * P - KH) / S + 1, Wo = (a->W + 2 * P - KW) / S + 1;
+    ConvKParams kp{};
+    kp.n_img = a->N; kp.ho = Ho; kp.wo = Wo;
+    choose_tile(a->N, Ho, Wo, &kp.wt, &kp.ht, &kp.nt);
+    kp.tiles_w = (Wo + kp.wt - 1) / kp.wt; kp.tiles_h = (Ho + kp.ht - 1) / kp.ht; kp.tiles_n = (a->N + kp.nt - 1) / kp.nt;
+    kp.num_m_tiles = kp.tiles_w * kp.tiles_h * kp.tiles_n;
+    kp.cout = a->Cout;
+    kp.num_taps = KH * KW;
+    kp.kblocks = (a->Cin + kBlockK - 1) / kBlockK;
+    kp.last_ksteps = ((a->Cin - (kp.kblocks - 1) * kBlockK) + 15) / 16;
+    kp.scale = a->scale; kp.bias = a->bias;
+    kp.residual = static_cast<const uint16_t*>(a->residual); kp.res_ctot = a->res_ctot; kp.res_coff = a->res_coff;
+    kp.y = static_cast<uint16_t*>(a->y); kp.y_ctot = a->y_ctot; kp.y_coff = a->y_coff;
+    kp.out_up = up; kp.out_dh = a->out_dh; kp.out_dw = a->out_dw;
+    kp.out_h = Ho * up; kp.out_w = Wo * up;
+    kp.relu = a->relu; kp.dtype = a->dtype;
+
+    // BN tile: largest of 256/128/64/32 dividing Cout that still yields >= ~1 wave of tiles
+    int bn = 256;
+    while (bn > 32 && (a->Cout % bn)) bn >>= 1;
+    const int sms = num_sms();
+    while (bn > 64 && (long)kp.num_m_tiles * (a->Cout / bn) < sms) bn >>= 1;
+    kp.num_n_tiles = a->Cout / bn;
+
+    // activation tensor maps
+    CUtensorMap am[4];
+    const uint16_t* xb = static_cast<const uint16_t*>(a->x) + a->x_coff;
+    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)kp.wt, (uint32_t)kp.ht, (uint32_t)kp.nt};
+    const uint64_t pix = (uint64_t)a->x_ctot * 2;
+    int nmaps = 0;
+    if (S == 1) {
+        const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * a->W, pix * a->W * a->H};
+        int rc = encode_map(&am[0], a->dtype, 4, xb, dims, str, box);
+        if (rc) return rc;
+        nmaps = 1;
+        int t = 0;
+        for (int r = 0; r < KH; ++r)
+            for (int s = 0; s < KW; ++s, ++t) {
+                kp.tap_dh[t] = (int8_t)(r - P); kp.tap_dw[t] = (int8_t)(s - P);
+                kp.tap_map[t] = 0; kp.tap_widx[t] = (int8_t)t;
+            }
+    } else {
+        // parity planes: plane (pr,pc) holds rows pr, pr+2, ... and cols pc, pc+2, ...
+        for (int pr = 0; pr < 2; ++pr)
+            for (int pc = 0; pc < 2; ++pc) {
+                const int hp = (a->H - pr + 1) / 2, wp = (a->W - pc + 1) / 2;
+                const int id = pr * 2 + pc;
+                if (hp <= 0 || wp <= 0) { am[id] = am[0]; continue; }
+                const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)wp, (uint64_t)hp, (uint64_t)a->N};
+                const uint64_t str[3] = {pix * 2, pix * a->W * 2, pix * a->W * a->H};
+                int rc = encode_map(&am[id], a->dtype, 4, xb + ((size_t)pr * a->W + pc) * a->x_ctot, dims, str, box);
+                if (rc) return rc;
+            }
+        nmaps = 4;
+        int t = 0;
+        for (int r = 0; r < KH; ++r)
+            for (int s = 0; s < KW; ++s, ++t) {
+                const int ir = r - P, ic = s - P;             // input offset relative to 2*ho, 2*wo
+                const int pr = ((ir % 2) + 2) % 2, pc = ((ic % 2) + 2) % 2;
+                kp.tap_dh[t] = (int8_t)((ir - pr) / 2); kp.tap_dw[t] = (int8_t)((ic - pc) / 2);
+                kp.tap_map[t] = (int8_t)(pr * 2 + pc); kp.tap_widx[t] = (int8_t)t;
+            }
+    }
+    for (int i = nmaps; i < 4; ++i) am[i] = am[0];
+
+    // weight map: [Cout][taps][Cin]
+    CUtensorMap wm;
+    {
+        const uint64_t dims[3] = {(uint64_t)a->Cin, (uint64_t)(KH * KW), (uint64_t)a->Cout};
+        const uint64_t str[2] = {(uint64_t)a->Cin * 2, (uint64_t)a->Cin * 2 * KH * KW};
+        const uint32_t wbox[3] = {(uint32_t)kBlockK, 1u, (uint32_t)bn};
+        int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
+        if (rc) return rc;
+    }
+    switch (bn) {
+        case 256: return launch_conv<256>(am, wm, kp, a->max_ctas, stream);
+        case 128: return launch_conv<128>(am, wm, kp, a->max_ctas, stream);
+        case 64: return launch_conv<64>(am, wm, kp, a->max_ctas, stream);
+        default: return launch_conv<32>(am, wm, kp, a->max_ctas, stream);
+    }
+}

@@ -1,0 +1,234 @@
+// Attention-gate tail, latent head (GAP + mu/logvar + reparameterisation), constant-map
+// projections and the 1x1 output head. All memory/latency bound: 16-byte accesses, shuffles.
+#include "vu_internal.h"
+#include "vu_half.cuh"
+
+namespace vu {
+
+// G threads cooperate on one pixel (G = power of two <= 32, G*8 >= max(F, Cl) unless looping).
+template <int G>
+__global__ void __launch_bounds__(256)
+attention_gate_kernel(const uint16_t* __restrict__ g1, int g1_ctot, int g1_coff, const uint16_t* __restrict__ x1,
+                      int x1_ctot, int x1_coff, const uint16_t* __restrict__ skip, int skip_ctot, int skip_coff,
+                      const float* __restrict__ psi_w, float psi_scale, float psi_bias, uint16_t* __restrict__ out,
+                      int out_ctot, int out_coff, float* __restrict__ psi_out, size_t npix, int rep, int HW, int F8,
+                      int C8, int dtype) {
+    const int sub = threadIdx.x % G;
+    const size_t gid = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) / G;
+    const size_t gstride = ((size_t)gridDim.x * blockDim.x) / G;
+    const size_t gl = (threadIdx.x & 31) / G;  // group index inside the warp (loop exit is warp-uniform)
+    for (size_t pix_ = gid; pix_ - gl < npix; pix_ += gstride) {
+        const bool valid = pix_ < npix;
+        const size_t pix = valid ? pix_ : npix - 1;
+        const size_t n = pix / HW, hw = pix % HW;
+        const size_t spix = (n / rep) * HW + hw;
+        float dot = 0.0f;
+        for (int f8 = sub; f8 < F8; f8 += G) {
+            const uint4 a = __ldg(reinterpret_cast<const uint4*>(g1 + pix * g1_ctot + g1_coff) + f8);
+            const uint4 b = __ldg(reinterpret_cast<const uint4*>(x1 + spix * x1_ctot + x1_coff) + f8);
+            float fa[8], fb[8];
+            unpack8(a, fa, dtype); unpack8(b, fb, dtype);
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(psi_w) + f8 * 2);
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(psi_w) + f8 * 2 + 1);
+            const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dot = fmaf(w[j], fmaxf(fa[j] + fb[j], 0.0f), dot);
+        }
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o, G);
+        const float psi = 1.0f / (1.0f + expf(-(psi_scale * dot + psi_bias)));
+        if (!valid) continue;
+        if (psi_out != nullptr && sub == 0) psi_out[pix] = psi;
+        for (int c8 = sub; c8 < C8; c8 += G) {
+            const uint4 s = __ldg(reinterpret_cast<const uint4*>(skip + spix * skip_ctot + skip_coff) + c8);
+            float f[8];
+            unpack8(s, f, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] *= psi;
+            *(reinterpret_cast<uint4*>(out + pix * out_ctot + out_coff) + c8) = pack8(f, dtype);
+        }
+    }
+}
+
+// one CTA per image: GAP over h*w into smem, then 2L dot products (warp per output), then z for all samples
+__global__ void __launch_bounds__(256)
+latent_head_kernel(const uint16_t* __restrict__ f4, int HW, int C, int f_ctot, int f_coff,
+                   const float* __restrict__ w_mu, const float* __restrict__ b_mu, const float* __restrict__ w_lv,
+                   const float* __restrict__ b_lv, const float* __restrict__ eps, float temperature, int Ns, int B,
+                   int L, float* __restrict__ mu, float* __restrict__ logvar, float* __restrict__ z, int dtype) {
+    extern __shared__ float sm[];
+    float* s_mean = sm;          // [C]
+    float* s_out = sm + C;       // [2L]
+    const int b = blockIdx.x;
+    const int C8 = C / 8;
+    // phase 1: thread t owns channel group t % C8, strides over pixels; partials reduced through smem atomics
+    for (int c = threadIdx.x; c < C; c += blockDim.x) s_mean[c] = 0.0f;
+    __syncthreads();
+    {
+        const int c8 = threadIdx.x % C8;
+        const int lanes_per = blockDim.x / C8 > 0 ? blockDim.x / C8 : 1;
+        const int pl = threadIdx.x / C8;
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (pl < lanes_per) {
+            for (int p = pl; p < HW; p += lanes_per) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(f4 + ((size_t)b * HW + p) * f_ctot + f_coff) + c8);
+                float f[8];
+                unpack8(v, f, dtype);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += f[j];
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) atomicAdd(&s_mean[c8 * 8 + j], acc[j]);
+        }
+    }
+    __syncthreads();
+    const float inv = 1.0f / (float)HW;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) s_mean[c] *= inv;
+    __syncthreads();
+    // phase 2
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int o = warp; o < 2 * L; o += nwarps) {
+        const float* wrow = (o < L) ? (w_mu + (size_t)o * C) : (w_lv + (size_t)(o - L) * C);
+        float d = 0.0f;
+        for (int c = lane; c < C; c += 32) d = fmaf(__ldg(wrow + c), s_mean[c], d);
+        d = warp_sum(d);
+        if (lane == 0) s_out[o] = d + ((o < L) ? b_mu[o] : b_lv[o - L]);
+    }
+    __syncthreads();
+    for (int l = threadIdx.x; l < L; l += blockDim.x) {
+        mu[(size_t)b * L + l] = s_out[l];
+        logvar[(size_t)b * L + l] = s_out[L + l];
+    }
+    if (z != nullptr) {
+        for (int i = threadIdx.x; i < Ns * L; i += blockDim.x) {
+            const int n = i / L, l = i % L;
+            const float m = s_out[l], lv = s_out[L + l];
+            float v = m;
+            if (eps != nullptr) {
+                // utils/vae_utils.py:8-10: std = exp(.5 lv) * T ; z = mu + eps * std
+                const float sd = expf(0.5f * lv) * temperature;
+                v = m + eps[((size_t)n * B + b) * L + l] * sd;
+            }
+            z[((size_t)n * B + b) * L + l] = v;
+        }
+    }
+}
+
+__global__ void latent_project_kernel(const float* __restrict__ z, const float* __restrict__ w,
+                                      const float* __restrict__ scale, const float* __restrict__ shift,
+                                      float* __restrict__ v, int M, int L, int C, int relu) {
+    const size_t total = (size_t)M * C;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c = idx % C;
+        const int i = idx / C;
+        float d = 0.0f;
+        for (int l = 0; l < L; ++l) d = fmaf(__ldg(w + (size_t)c * L + l), __ldg(z + (size_t)i * L + l), d);
+        d = d * (scale ? scale[c] : 1.0f) + (shift ? shift[c] : 0.0f);
+        v[idx] = relu ? fmaxf(d, 0.0f) : d;
+    }
+}
+
+// logits[pix] = <w, x[pix, :]> + bias ; G = C/8 threads per pixel
+template <int G>
+__global__ void __launch_bounds__(256)
+final_conv1_kernel(const uint16_t* __restrict__ x, size_t npix, int x_ctot, int x_coff, const float* __restrict__ w,
+                   float bias, float* __restrict__ logits, int C8, int dtype) {
+    const int sub = threadIdx.x % G;
+    const size_t gid = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) / G;
+    const size_t gstride = ((size_t)gridDim.x * blockDim.x) / G;
+    const size_t gl = (threadIdx.x & 31) / G;
+    for (size_t pix_ = gid; pix_ - gl < npix; pix_ += gstride) {
+        const bool valid = pix_ < npix;
+        const size_t pix = valid ? pix_ : npix - 1;
+        float d = 0.0f;
+        for (int c8 = sub; c8 < C8; c8 += G) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + pix * x_ctot + x_coff) + c8);
+            float f[8];
+            unpack8(v, f, dtype);
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(w) + c8 * 2);
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(w) + c8 * 2 + 1);
+            d = fmaf(f[0], w0.x, d); d = fmaf(f[1], w0.y, d); d = fmaf(f[2], w0.z, d); d = fmaf(f[3], w0.w, d);
+            d = fmaf(f[4], w1.x, d); d = fmaf(f[5], w1.y, d); d = fmaf(f[6], w1.z, d); d = fmaf(f[7], w1.w, d);
+        }
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o, G);
+        if (sub == 0 && valid) logits[pix] = d + bias;
+    }
+}
+
+static int grid_cap(size_t blocks) {
+    const size_t cap = (size_t)num_sms() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+extern "C" int vu_attention_gate(const void* g1, int g1_ctot, int g1_coff, const void* x1, int x1_ctot, int x1_coff,
+                                 const void* skip, int skip_ctot, int skip_coff, const float* psi_w, float psi_scale,
+                                 float psi_bias, void* out, int out_ctot, int out_coff, float* psi, int Ng, int rep,
+                                 int H, int W, int F, int Cl, int dtype, vu_stream_t st) {
+    if (!g1 || !x1 || !skip || !psi_w || !out) return set_error(VU_ERR_INVALID, "attention_gate: null");
+    if (rep < 1 || Ng % rep) return set_error(VU_ERR_INVALID, "attention_gate: Ng (%d) must be a multiple of rep (%d)", Ng, rep);
+    if (F % 8 || Cl % 8 || g1_ctot % 8 || g1_coff % 8 || x1_ctot % 8 || x1_coff % 8 || skip_ctot % 8 || skip_coff % 8 ||
+        out_ctot % 8 || out_coff % 8)
+        return set_error(VU_ERR_ALIGN, "attention_gate: channels %% 8");
+    const size_t npix = (size_t)Ng * H * W;
+    const int mx = (F > Cl ? F : Cl) / 8;
+    cudaStream_t s = (cudaStream_t)st;
+#define VU_GATE(G)                                                                                                   \
+    attention_gate_kernel<G><<<grid_cap((npix * G + 255) / 256), 256, 0, s>>>(                                        \
+        (const uint16_t*)g1, g1_ctot, g1_coff, (const uint16_t*)x1, x1_ctot, x1_coff, (const uint16_t*)skip, skip_ctot, \
+        skip_coff, psi_w, psi_scale, psi_bias, (uint16_t*)out, out_ctot, out_coff, psi, npix, rep, H* W, F / 8, Cl / 8, dtype)
+    if (mx <= 4) VU_GATE(4);
+    else if (mx <= 8) VU_GATE(8);
+    else if (mx <= 16) VU_GATE(16);
+    else VU_GATE(32);
+#undef VU_GATE
+    VU_CHECK_LAUNCH("attention_gate");
+    return 0;
+}
+
+extern "C" int vu_latent_head(const void* f4, int B, int h, int w, int C, int f_ctot, int f_coff, const float* w_mu,
+                              const float* b_mu, const float* w_lv, const float* b_lv, const float* eps,
+                              float temperature, int Ns, int L, float* mu, float* logvar, float* z, int dtype,
+                              vu_stream_t st) {
+    if (!f4 || !w_mu || !b_mu || !w_lv || !b_lv || !mu || !logvar) return set_error(VU_ERR_INVALID, "latent_head: null");
+    if (C % 8 || f_ctot % 8 || f_coff % 8) return set_error(VU_ERR_ALIGN, "latent_head: channels %% 8");
+    if (C / 8 > 256) return set_error(VU_ERR_UNSUPPORTED, "latent_head: C <= 2048");
+    if (B < 1 || L < 1 || Ns < 0) return set_error(VU_ERR_INVALID, "latent_head: bad sizes");
+    const size_t smem = (size_t)(C + 2 * L) * sizeof(float);
+    latent_head_kernel<<<B, 256, smem, (cudaStream_t)st>>>((const uint16_t*)f4, h * w, C, f_ctot, f_coff, w_mu, b_mu, w_lv,
+                                                           b_lv, eps, temperature, Ns, B, L, mu, logvar, z, dtype);
+    VU_CHECK_LAUNCH("latent_head");
+    return 0;
+}
+
+extern "C" int vu_latent_project(const float* z, const float* w, const float* scale, const float* shift, float* v, int M,
+                                 int L, int C, int relu, vu_stream_t st) {
+    if (!z || !w || !v || M < 1) return set_error(VU_ERR_INVALID, "latent_project: bad args");
+    const size_t total = (size_t)M * C;
+    latent_project_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(z, w, scale, shift, v, M, L, C, relu);
+    VU_CHECK_LAUNCH("latent_project");
+    return 0;
+}
+
+extern "C" int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_ctot, int x_coff, const float* w,
+                              float bias, float* logits, int dtype, vu_stream_t st) {
+    if (!x || !w || !logits) return set_error(VU_ERR_INVALID, "final_conv1: null");
+    if (C % 8 || x_ctot % 8 || x_coff % 8) return set_error(VU_ERR_ALIGN, "final_conv1: channels %% 8");
+    const size_t npix = (size_t)N * H * W;
+    const int c8 = C / 8;
+    cudaStream_t s = (cudaStream_t)st;
+    if (c8 <= 4)
+        final_conv1_kernel<4><<<grid_cap((npix * 4 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+    else if (c8 <= 8)
+        final_conv1_kernel<8><<<grid_cap((npix * 8 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+    else
+        final_conv1_kernel<16><<<grid_cap((npix * 16 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+    VU_CHECK_LAUNCH("final_conv1");
+    return 0;
+}

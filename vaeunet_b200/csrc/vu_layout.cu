@@ -1,0 +1,332 @@
+// Memory-bound layout / pooling / resize kernels (NHWC 16-bit, 8 channels = 16 B per thread access).
+#include "vu_internal.h"
+#include "vu_half.cuh"
+
+namespace vu {
+
+// ---------------------------------------------------------------- weight packing
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int O, int I,
+                                        int T, int transpose_io, int dtype) {
+    const size_t total = (size_t)O * T * I;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int i = idx % I;
+        const int t = (idx / I) % T;
+        const int o = idx / ((size_t)I * T);
+        const size_t src = transpose_io ? (((size_t)i * O + o) * T + t) : (((size_t)o * I + i) * T + t);
+        out[idx] = f2h(w[src], dtype);
+    }
+}
+
+// ConvTranspose2d k2 s2: w [I][O][2][2] -> [4 (a*2+b)][O][I]
+__global__ void pack_convT_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int I, int O, int dtype) {
+    const size_t total = (size_t)4 * O * I;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int i = idx % I;
+        const int o = (idx / I) % O;
+        const int ab = idx / ((size_t)I * O);
+        out[idx] = f2h(w[((size_t)i * O + o) * 4 + ab], dtype);
+    }
+}
+
+// ---------------------------------------------------------------- NCHW fp32 <-> NHWC 16-bit
+// 32 pixels x 32 channels tile through smem: coalesced on both sides.
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, uint16_t* __restrict__ y, int C, int HW,
+                                    int y_ctot, int y_coff, int dtype) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;  // 32 x 8
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, p = p0 + tx;
+        tile[j][tx] = (c < C && p < HW) ? x[((size_t)n * C + c) * HW + p] : 0.0f;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int p = p0 + j, c = c0 + tx;
+        if (c < C && p < HW) y[((size_t)n * HW + p) * y_ctot + y_coff + c] = f2h(tile[tx][j], dtype);
+    }
+}
+
+__global__ void nhwc_to_nchw_kernel(const uint16_t* __restrict__ x, float* __restrict__ y, int C, int HW,
+                                    int x_ctot, int x_coff, int dtype) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int j = ty; j < 32; j += 8) {
+        const int p = p0 + j, c = c0 + tx;
+        tile[j][tx] = (c < C && p < HW) ? h2f(x[((size_t)n * HW + p) * x_ctot + x_coff + c], dtype) : 0.0f;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, p = p0 + tx;
+        if (c < C && p < HW) y[((size_t)n * C + c) * HW + p] = tile[tx][j];
+    }
+}
+
+// ---------------------------------------------------------------- direct small-Cin convs
+// Generic direct conv for Cin <= 4 (stem 7x7 s2 p3; basic-UNet inc 3x3 s1 p1): a CTA computes a
+// 16x16 output tile for all Cout; input halo tile and the whole filter bank live in smem.
+template <int K, int S>
+__global__ void __launch_bounds__(256)
+small_cin_conv_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale,
+                      const float* __restrict__ bias, uint16_t* __restrict__ y, int Cin, int H, int W, int Cout,
+                      int Ho, int Wo, int pad, int y_ctot, int y_coff, int relu, int dtype) {
+    constexpr int TO = 16;
+    constexpr int TI = (TO - 1) * S + K;
+    extern __shared__ float sm[];
+    float* s_in = sm;                         // [Cin][TI][TI+1]
+    float* s_w = sm + 4 * TI * (TI + 1);      // [Cin*K*K][Cout]  (tap-major so a warp reads one row)
+    const int n = blockIdx.z;
+    const int oh0 = blockIdx.y * TO, ow0 = blockIdx.x * TO;
+    const int tid = threadIdx.x;
+    const int ih0 = oh0 * S - pad, iw0 = ow0 * S - pad;
+    for (int i = tid; i < Cin * TI * TI; i += 256) {
+        const int c = i / (TI * TI), r = (i / TI) % TI, q = i % TI;
+        const int ih = ih0 + r, iw = iw0 + q;
+        float v = 0.0f;
+        if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = x[(((size_t)n * Cin + c) * H + ih) * W + iw];
+        s_in[(c * TI + r) * (TI + 1) + q] = v;
+    }
+    const int KK = Cin * K * K;
+    for (int i = tid; i < KK * Cout; i += 256) {
+        const int co = i % Cout, t = i / Cout;   // t = (c*K + r)*K + s  == OIHW inner index
+        s_w[i] = w[(size_t)co * KK + t];
+    }
+    __syncthreads();
+    const int ty = tid / TO, tx = tid % TO;
+    const int oh = oh0 + ty, ow = ow0 + tx;
+    const bool valid = oh < Ho && ow < Wo;
+    for (int cb = 0; cb < Cout; cb += 32) {
+        float acc[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
+        for (int c = 0; c < Cin; ++c)
+            for (int r = 0; r < K; ++r)
+#pragma unroll
+                for (int s = 0; s < K; ++s) {
+                    const float v = s_in[(c * TI + ty * S + r) * (TI + 1) + tx * S + s];
+                    const float4* wp = reinterpret_cast<const float4*>(s_w + ((c * K + r) * K + s) * Cout + cb);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 ww = wp[j];
+                        acc[4 * j] = fmaf(v, ww.x, acc[4 * j]);
+                        acc[4 * j + 1] = fmaf(v, ww.y, acc[4 * j + 1]);
+                        acc[4 * j + 2] = fmaf(v, ww.z, acc[4 * j + 2]);
+                        acc[4 * j + 3] = fmaf(v, ww.w, acc[4 * j + 3]);
+                    }
+                }
+        if (valid) {
+            uint32_t o[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                float a = acc[2 * j] * scale[cb + 2 * j] + bias[cb + 2 * j];
+                float b = acc[2 * j + 1] * scale[cb + 2 * j + 1] + bias[cb + 2 * j + 1];
+                if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
+                o[j] = pack2h(a, b, dtype);
+            }
+            uint4* op = reinterpret_cast<uint4*>(y + (((size_t)n * Ho + oh) * Wo + ow) * y_ctot + y_coff + cb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) op[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        }
+    }
+}
+
+template <int K, int S>
+static int launch_small_cin(const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
+                            int Cin, int H, int W, int Cout, int pad, int y_ctot, int y_coff, int relu, int dtype,
+                            cudaStream_t stream) {
+    constexpr int TI = 15 * S + K;
+    if (Cin < 1 || Cin > 4) return set_error(VU_ERR_UNSUPPORTED, "small-cin conv: Cin must be 1..4 (got %d)", Cin);
+    if (Cout % 32 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "small-cin conv: Cout %% 32, slices %% 8");
+    if (!scale || !bias) return set_error(VU_ERR_INVALID, "small-cin conv: scale/bias required");
+    const int Ho = (H + 2 * pad - K) / S + 1, Wo = (W + 2 * pad - K) / S + 1;
+    const size_t smem = (size_t)(4 * TI * (TI + 1) + Cin * K * K * Cout) * sizeof(float);
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(small_cin_conv_kernel<K, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr = true;
+    }
+    if (smem > 200 * 1024) return set_error(VU_ERR_UNSUPPORTED, "small-cin conv: filter bank too large for smem");
+    dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, N);
+    small_cin_conv_kernel<K, S><<<grid, 256, smem, stream>>>(x, w, scale, bias, static_cast<uint16_t*>(y), Cin, H, W,
+                                                           Cout, Ho, Wo, pad, y_ctot, y_coff, relu, dtype);
+    VU_CHECK_LAUNCH("small_cin_conv");
+    return 0;
+}
+
+// ---------------------------------------------------------------- max-pool
+__global__ void maxpool_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ y, int N, int H, int W,
+                                    int C8, int x_ctot, int x_coff, int k, int s, int p, int Ho, int Wo, int y_ctot,
+                                    int y_coff, int dtype) {
+    const size_t total = (size_t)N * Ho * Wo * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int wo = (idx / C8) % Wo;
+        const int ho = (idx / ((size_t)C8 * Wo)) % Ho;
+        const int n = idx / ((size_t)C8 * Wo * Ho);
+        float m[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+        for (int r = 0; r < k; ++r) {
+            const int ih = ho * s - p + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int q = 0; q < k; ++q) {
+                const int iw = wo * s - p + q;
+                if (iw < 0 || iw >= W) continue;
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * H + ih) * W + iw) * x_ctot + x_coff) + c8);
+                float f[8];
+                unpack8(v, f, dtype);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+            }
+        }
+        *(reinterpret_cast<uint4*>(y + (((size_t)n * Ho + ho) * Wo + wo) * y_ctot + y_coff) + c8) = pack8(m, dtype);
+    }
+}
+
+// ---------------------------------------------------------------- bilinear, align_corners=True
+// Coordinate arithmetic follows ATen's upsample_bilinear2d (area_pixel_compute_scale /
+// _source_index with align_corners): scale = (in-1)/(out-1) in fp32, src = scale*dst.
+__global__ void bilinear_ac_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ y, int N, int Hs, int Ws,
+                                        int C8, int x_ctot, int x_coff, int Ho, int Wo, int Hd, int Wd, int pad_t,
+                                        int pad_l, int y_ctot, int y_coff, float sh, float sw, int dtype) {
+    const size_t total = (size_t)N * Ho * Wo * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int wo = (idx / C8) % Wo;
+        const int ho = (idx / ((size_t)C8 * Wo)) % Ho;
+        const int n = idx / ((size_t)C8 * Wo * Ho);
+        const float h1r = sh * ho;
+        const int h1 = (int)h1r;
+        const int h1p = (h1 < Hs - 1) ? 1 : 0;
+        const float h1l = h1r - h1, h0l = 1.0f - h1l;
+        const float w1r = sw * wo;
+        const int w1 = (int)w1r;
+        const int w1p = (w1 < Ws - 1) ? 1 : 0;
+        const float w1l = w1r - w1, w0l = 1.0f - w1l;
+        const uint16_t* base = x + ((size_t)n * Hs * Ws) * x_ctot + x_coff;
+        const uint4 v00 = __ldg(reinterpret_cast<const uint4*>(base + ((size_t)h1 * Ws + w1) * x_ctot) + c8);
+        const uint4 v01 = __ldg(reinterpret_cast<const uint4*>(base + ((size_t)h1 * Ws + w1 + w1p) * x_ctot) + c8);
+        const uint4 v10 = __ldg(reinterpret_cast<const uint4*>(base + ((size_t)(h1 + h1p) * Ws + w1) * x_ctot) + c8);
+        const uint4 v11 = __ldg(reinterpret_cast<const uint4*>(base + ((size_t)(h1 + h1p) * Ws + w1 + w1p) * x_ctot) + c8);
+        float a[8], b[8], c[8], d[8], o[8];
+        unpack8(v00, a, dtype); unpack8(v01, b, dtype); unpack8(v10, c, dtype); unpack8(v11, d, dtype);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = h0l * (w0l * a[j] + w1l * b[j]) + h1l * (w0l * c[j] + w1l * d[j]);
+        *(reinterpret_cast<uint4*>(y + (((size_t)n * Hd + ho + pad_t) * Wd + wo + pad_l) * y_ctot + y_coff) + c8) =
+            pack8(o, dtype);
+    }
+}
+
+__global__ void broadcast_vec_nhwc_kernel(const float* __restrict__ v, uint16_t* __restrict__ y, int N, int HW, int C8,
+                                          int C, int y_ctot, int y_coff, int dtype) {
+    const size_t total = (size_t)N * HW * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t pix = idx / C8;
+        const int n = pix / HW;
+        const float4* vp = reinterpret_cast<const float4*>(v + (size_t)n * C + c8 * 8);
+        const float4 a = __ldg(vp), b = __ldg(vp + 1);
+        const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        *(reinterpret_cast<uint4*>(y + pix * y_ctot + y_coff) + c8) = pack8(f, dtype);
+    }
+}
+
+static int grid_for(size_t total, int block) {
+    size_t g = (total + block - 1) / block;
+    const size_t cap = (size_t)num_sms() * 16;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+extern "C" int vu_pack_conv_weight(const float* w, void* out, int O, int I, int KH, int KW, int transpose_io, int dtype,
+                                   vu_stream_t st) {
+    if (!w || !out || O < 1 || I < 1) return set_error(VU_ERR_INVALID, "pack_conv_weight: bad args");
+    const size_t total = (size_t)O * I * KH * KW;
+    pack_conv_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, KH * KW,
+                                                                               transpose_io, dtype);
+    VU_CHECK_LAUNCH("pack_conv_weight");
+    return 0;
+}
+
+extern "C" int vu_pack_convT2x2_weight(const float* w, void* out, int I, int O, int dtype, vu_stream_t st) {
+    if (!w || !out) return set_error(VU_ERR_INVALID, "pack_convT: null");
+    pack_convT_kernel<<<grid_for((size_t)4 * I * O, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, I, O, dtype);
+    VU_CHECK_LAUNCH("pack_convT");
+    return 0;
+}
+
+extern "C" int vu_nchw_to_nhwc(const float* x, void* y, int N, int C, int H, int W, int y_ctot, int y_coff, int dtype,
+                               vu_stream_t st) {
+    if (!x || !y || N < 1 || C < 1) return set_error(VU_ERR_INVALID, "nchw_to_nhwc: bad args");
+    dim3 grid((H * W + 31) / 32, (C + 31) / 32, N), block(32, 8);
+    nchw_to_nhwc_kernel<<<grid, block, 0, (cudaStream_t)st>>>(x, (uint16_t*)y, C, H * W, y_ctot, y_coff, dtype);
+    VU_CHECK_LAUNCH("nchw_to_nhwc");
+    return 0;
+}
+
+extern "C" int vu_nhwc_to_nchw(const void* x, float* y, int N, int C, int H, int W, int x_ctot, int x_coff, int dtype,
+                               vu_stream_t st) {
+    if (!x || !y || N < 1 || C < 1) return set_error(VU_ERR_INVALID, "nhwc_to_nchw: bad args");
+    dim3 grid((H * W + 31) / 32, (C + 31) / 32, N), block(32, 8);
+    nhwc_to_nchw_kernel<<<grid, block, 0, (cudaStream_t)st>>>((const uint16_t*)x, y, C, H * W, x_ctot, x_coff, dtype);
+    VU_CHECK_LAUNCH("nhwc_to_nchw");
+    return 0;
+}
+
+extern "C" int vu_stem_conv7x7s2(const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
+                                 int Cin, int H, int W, int Cout, int y_ctot, int y_coff, int dtype, vu_stream_t st) {
+    if (!x || !w || !y) return set_error(VU_ERR_INVALID, "stem: null");
+    return launch_small_cin<7, 2>(x, w, scale, bias, y, N, Cin, H, W, Cout, 3, y_ctot, y_coff, 1, dtype, (cudaStream_t)st);
+}
+
+extern "C" int vu_conv3x3_small_cin(const float* x, const float* w, const float* scale, const float* bias, void* y,
+                                    int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff, int relu, int dtype,
+                                    vu_stream_t st) {
+    if (!x || !w || !y) return set_error(VU_ERR_INVALID, "conv3x3_small_cin: null");
+    return launch_small_cin<3, 1>(x, w, scale, bias, y, N, Cin, H, W, Cout, 1, y_ctot, y_coff, relu, dtype, (cudaStream_t)st);
+}
+
+extern "C" int vu_maxpool_nhwc(const void* x, void* y, int N, int H, int W, int C, int x_ctot, int x_coff, int k, int s,
+                               int p, int y_ctot, int y_coff, int dtype, vu_stream_t st) {
+    if (!x || !y) return set_error(VU_ERR_INVALID, "maxpool: null");
+    if (C % 8 || x_ctot % 8 || x_coff % 8 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "maxpool: channels %% 8");
+    const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+    const size_t total = (size_t)N * Ho * Wo * (C / 8);
+    maxpool_nhwc_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>((const uint16_t*)x, (uint16_t*)y, N, H, W, C / 8,
+                                                                           x_ctot, x_coff, k, s, p, Ho, Wo, y_ctot, y_coff, dtype);
+    VU_CHECK_LAUNCH("maxpool");
+    return 0;
+}
+
+extern "C" int vu_bilinear_ac_nhwc(const void* x, void* y, int N, int Hs, int Ws, int C, int x_ctot, int x_coff, int Ho,
+                                   int Wo, int Hd, int Wd, int pad_t, int pad_l, int y_ctot, int y_coff, int dtype,
+                                   vu_stream_t st) {
+    if (!x || !y) return set_error(VU_ERR_INVALID, "bilinear: null");
+    if (C % 8 || x_ctot % 8 || x_coff % 8 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "bilinear: channels %% 8");
+    if (pad_t < 0 || pad_l < 0 || pad_t + Ho > Hd || pad_l + Wo > Wd) return set_error(VU_ERR_INVALID, "bilinear: bad padding");
+    const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
+    const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
+    const size_t total = (size_t)N * Ho * Wo * (C / 8);
+    bilinear_ac_nhwc_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(
+        (const uint16_t*)x, (uint16_t*)y, N, Hs, Ws, C / 8, x_ctot, x_coff, Ho, Wo, Hd, Wd, pad_t, pad_l, y_ctot, y_coff, sh, sw, dtype);
+    VU_CHECK_LAUNCH("bilinear");
+    return 0;
+}
+
+extern "C" int vu_broadcast_vec_nhwc(const float* v, void* y, int N, int H, int W, int C, int y_ctot, int y_coff, int dtype,
+                                     vu_stream_t st) {
+    if (!v || !y) return set_error(VU_ERR_INVALID, "broadcast: null");
+    if (C % 8 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "broadcast: channels %% 8");
+    const size_t total = (size_t)N * H * W * (C / 8);
+    broadcast_vec_nhwc_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(v, (uint16_t*)y, N, H * W, C / 8, C, y_ctot,
+                                                                                 y_coff, dtype);
+    VU_CHECK_LAUNCH("broadcast");
+    return 0;
+}

@@ -1,0 +1,418 @@
+"""Thin torch-tensor wrappers over the C ABI (include/vaeunet_b200.h).
+
+PyTorch is plumbing here: it owns device memory and the current stream; every arithmetic
+operation below is one of this repo's CUDA kernels. Activations are NHWC 16-bit buffers
+(`Act`), possibly a channel slice of a wider concat buffer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import ConvArgs, check, load, require_device
+
+BF16, F16 = 0, 1
+_TORCH_DT = {BF16: torch.bfloat16, F16: torch.float16}
+
+# launch counter (bench.py reports it as gpu_launches)
+LAUNCHES = 0
+
+
+def _count(n: int = 1) -> None:
+    global LAUNCHES
+    LAUNCHES += n
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    assert t.dtype == torch.float32 and t.is_cuda and t.is_contiguous(), "expected contiguous CUDA fp32"
+    return t
+
+
+@dataclass
+class Act:
+    """Channel slice [coff, coff+C) of an NHWC 16-bit buffer t[N,H,W,ctot]."""
+    t: torch.Tensor
+    coff: int = 0
+    C: int = -1
+
+    def __post_init__(self):
+        assert self.t.dim() == 4 and self.t.is_contiguous() and self.t.is_cuda
+        if self.C < 0:
+            self.C = self.t.shape[3] - self.coff
+
+    @property
+    def N(self): return self.t.shape[0]
+    @property
+    def H(self): return self.t.shape[1]
+    @property
+    def W(self): return self.t.shape[2]
+    @property
+    def ctot(self): return self.t.shape[3]
+    @property
+    def dt(self): return BF16 if self.t.dtype == torch.bfloat16 else F16
+
+    def slice(self, coff: int, C: int) -> "Act":
+        assert 0 <= coff and coff + C <= self.C
+        return Act(self.t, self.coff + coff, C)
+
+
+def new_act(N, H, W, Cc, dtype=BF16, device=None) -> Act:
+    return Act(torch.empty((N, H, W, Cc), dtype=_TORCH_DT[dtype], device=device or torch.cuda.current_device()))
+
+
+# ------------------------------------------------------------------ weights
+def pack_conv_weight(w: torch.Tensor, dtype=BF16, transpose_io=False) -> torch.Tensor:
+    """OIHW fp32 -> [O][KH*KW][I] 16-bit."""
+    require_device()
+    w = _f32(w.detach().float().contiguous())
+    if transpose_io:
+        I, O, KH, KW = w.shape
+    else:
+        O, I, KH, KW = w.shape
+    out = torch.empty((O, KH * KW, I), dtype=_TORCH_DT[dtype], device=w.device)
+    check(load().vu_pack_conv_weight(w.data_ptr(), out.data_ptr(), O, I, KH, KW, int(transpose_io), dtype, _stream()),
+          "vu_pack_conv_weight")
+    _count()
+    return out
+
+
+def pack_convT2x2_weight(w: torch.Tensor, dtype=BF16) -> torch.Tensor:
+    require_device()
+    w = _f32(w.detach().float().contiguous())
+    I, O, KH, KW = w.shape
+    assert KH == 2 and KW == 2
+    out = torch.empty((4, O, 1, I), dtype=_TORCH_DT[dtype], device=w.device)
+    check(load().vu_pack_convT2x2_weight(w.data_ptr(), out.data_ptr(), I, O, dtype, _stream()), "vu_pack_convT2x2_weight")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------ conv
+def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale: Optional[torch.Tensor],
+           bias: Optional[torch.Tensor], relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None,
+           out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0) -> Act:
+    require_device()
+    Cout = w_packed.shape[0]
+    assert w_packed.shape[1] == k * k and w_packed.shape[2] == x.C, (tuple(w_packed.shape), k, x.C)
+    Ho = (x.H + 2 * pad - k) // stride + 1
+    Wo = (x.W + 2 * pad - k) // stride + 1
+    if out is None:
+        out = new_act(x.N, Ho * out_up, Wo * out_up, Cout, x.dt, x.t.device)
+    assert out.C == Cout and out.N == x.N and out.H == Ho * out_up and out.W == Wo * out_up, "conv output shape"
+    a = ConvArgs()
+    a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
+    a.w = w_packed.data_ptr(); a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad
+    a.scale = _ptr(scale); a.bias = _ptr(bias)
+    if residual is not None:
+        assert residual.N == x.N and residual.H == Ho and residual.W == Wo and residual.C == Cout
+        a.residual = residual.t.data_ptr(); a.res_ctot = residual.ctot; a.res_coff = residual.coff
+    else:
+        a.residual = None
+    a.relu = int(relu)
+    a.y = out.t.data_ptr(); a.y_ctot = out.ctot; a.y_coff = out.coff
+    a.out_up = out_up; a.out_dh = out_dh; a.out_dw = out_dw
+    a.dtype = x.dt; a.max_ctas = max_ctas
+    check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------ layout / pooling / resize
+def nchw_to_nhwc(x: torch.Tensor, out: Optional[Act] = None, dtype=BF16) -> Act:
+    require_device()
+    x = _f32(x.float().contiguous())
+    N, Cc, H, W = x.shape
+    if out is None:
+        out = new_act(N, H, W, Cc, dtype, x.device)
+    check(load().vu_nchw_to_nhwc(x.data_ptr(), out.t.data_ptr(), N, Cc, H, W, out.ctot, out.coff, out.dt, _stream()),
+          "vu_nchw_to_nhwc")
+    _count()
+    return out
+
+
+def nhwc_to_nchw(x: Act) -> torch.Tensor:
+    require_device()
+    y = torch.empty((x.N, x.C, x.H, x.W), dtype=torch.float32, device=x.t.device)
+    check(load().vu_nhwc_to_nchw(x.t.data_ptr(), y.data_ptr(), x.N, x.C, x.H, x.W, x.ctot, x.coff, x.dt, _stream()),
+          "vu_nhwc_to_nchw")
+    _count()
+    return y
+
+
+def stem_conv7x7s2(x: torch.Tensor, w: torch.Tensor, scale: torch.Tensor, bias: torch.Tensor, dtype=BF16,
+                   out: Optional[Act] = None) -> Act:
+    require_device()
+    x = _f32(x.float().contiguous())
+    N, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    Ho, Wo = (H + 6 - 7) // 2 + 1, (W + 6 - 7) // 2 + 1
+    if out is None:
+        out = new_act(N, Ho, Wo, Cout, dtype, x.device)
+    check(load().vu_stem_conv7x7s2(x.data_ptr(), _f32(w).data_ptr(), _f32(scale).data_ptr(), _f32(bias).data_ptr(),
+                                   out.t.data_ptr(), N, Cin, H, W, Cout, out.ctot, out.coff, out.dt, _stream()),
+          "vu_stem_conv7x7s2")
+    _count()
+    return out
+
+
+def conv3x3_small_cin(x: torch.Tensor, w: torch.Tensor, scale: torch.Tensor, bias: torch.Tensor, relu: bool,
+                      dtype=BF16, out: Optional[Act] = None) -> Act:
+    require_device()
+    x = _f32(x.float().contiguous())
+    N, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    if out is None:
+        out = new_act(N, H, W, Cout, dtype, x.device)
+    check(load().vu_conv3x3_small_cin(x.data_ptr(), _f32(w).data_ptr(), _f32(scale).data_ptr(), _f32(bias).data_ptr(),
+                                      out.t.data_ptr(), N, Cin, H, W, Cout, out.ctot, out.coff, int(relu), out.dt,
+                                      _stream()), "vu_conv3x3_small_cin")
+    _count()
+    return out
+
+
+def maxpool(x: Act, k: int, s: int, p: int, out: Optional[Act] = None) -> Act:
+    require_device()
+    Ho, Wo = (x.H + 2 * p - k) // s + 1, (x.W + 2 * p - k) // s + 1
+    if out is None:
+        out = new_act(x.N, Ho, Wo, x.C, x.dt, x.t.device)
+    check(load().vu_maxpool_nhwc(x.t.data_ptr(), out.t.data_ptr(), x.N, x.H, x.W, x.C, x.ctot, x.coff, k, s, p,
+                                 out.ctot, out.coff, x.dt, _stream()), "vu_maxpool_nhwc")
+    _count()
+    return out
+
+
+def bilinear_ac(x: Act, Ho: int, Wo: int, out: Optional[Act] = None, pad_t: int = 0, pad_l: int = 0) -> Act:
+    require_device()
+    if out is None:
+        out = new_act(x.N, Ho, Wo, x.C, x.dt, x.t.device)
+    check(load().vu_bilinear_ac_nhwc(x.t.data_ptr(), out.t.data_ptr(), x.N, x.H, x.W, x.C, x.ctot, x.coff, Ho, Wo,
+                                     out.H, out.W, pad_t, pad_l, out.ctot, out.coff, x.dt, _stream()),
+          "vu_bilinear_ac_nhwc")
+    _count()
+    return out
+
+
+def broadcast_vec(v: torch.Tensor, out: Act) -> Act:
+    """v fp32 [N, C] -> constant map in out[N,H,W,slice]."""
+    require_device()
+    v = _f32(v)
+    assert v.shape == (out.N, out.C)
+    check(load().vu_broadcast_vec_nhwc(v.data_ptr(), out.t.data_ptr(), out.N, out.H, out.W, out.C, out.ctot, out.coff,
+                                       out.dt, _stream()), "vu_broadcast_vec_nhwc")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------ attention gate / latent / head
+def attention_gate(g1: Act, x1: Act, skip: Act, psi_w: torch.Tensor, psi_scale: float, psi_bias: float, out: Act,
+                   psi_out: Optional[torch.Tensor] = None) -> Act:
+    require_device()
+    Ng, Ns = g1.N, skip.N
+    assert Ng % Ns == 0 and x1.N == Ns and g1.C == x1.C and out.C == skip.C and out.N == Ng
+    assert (g1.H, g1.W) == (skip.H, skip.W) == (x1.H, x1.W) == (out.H, out.W)
+    check(load().vu_attention_gate(g1.t.data_ptr(), g1.ctot, g1.coff, x1.t.data_ptr(), x1.ctot, x1.coff,
+                                   skip.t.data_ptr(), skip.ctot, skip.coff, _f32(psi_w).data_ptr(), float(psi_scale),
+                                   float(psi_bias), out.t.data_ptr(), out.ctot, out.coff, _ptr(psi_out), Ng, Ng // Ns,
+                                   g1.H, g1.W, g1.C, skip.C, g1.dt, _stream()), "vu_attention_gate")
+    _count()
+    return out
+
+
+def latent_head(f4: Act, w_mu, b_mu, w_lv, b_lv, eps: Optional[torch.Tensor], temperature: float, Ns: int):
+    """-> mu [B,L], logvar [B,L], z [Ns,B,L] (fp32)."""
+    require_device()
+    B, L = f4.N, w_mu.shape[0]
+    dev = f4.t.device
+    mu = torch.empty((B, L), dtype=torch.float32, device=dev)
+    lv = torch.empty((B, L), dtype=torch.float32, device=dev)
+    z = torch.empty((max(Ns, 1), B, L), dtype=torch.float32, device=dev) if Ns > 0 else None
+    if eps is not None:
+        eps = _f32(eps)
+        assert eps.shape == (Ns, B, L), (tuple(eps.shape), (Ns, B, L))
+    check(load().vu_latent_head(f4.t.data_ptr(), B, f4.H, f4.W, f4.C, f4.ctot, f4.coff, _f32(w_mu).data_ptr(),
+                                _f32(b_mu).data_ptr(), _f32(w_lv).data_ptr(), _f32(b_lv).data_ptr(), _ptr(eps),
+                                float(temperature), Ns, L, mu.data_ptr(), lv.data_ptr(), _ptr(z), f4.dt, _stream()),
+          "vu_latent_head")
+    _count()
+    return mu, lv, z
+
+
+def latent_project(z: torch.Tensor, w: torch.Tensor, scale: Optional[torch.Tensor], shift: Optional[torch.Tensor],
+                   relu: bool) -> torch.Tensor:
+    require_device()
+    z = _f32(z)
+    M, L = z.shape
+    Cc = w.shape[0]
+    v = torch.empty((M, Cc), dtype=torch.float32, device=z.device)
+    check(load().vu_latent_project(z.data_ptr(), _f32(w).data_ptr(), _ptr(scale), _ptr(shift), v.data_ptr(), M, L, Cc,
+                                   int(relu), _stream()), "vu_latent_project")
+    _count()
+    return v
+
+
+def final_conv1(x: Act, w: torch.Tensor, bias: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    require_device()
+    if out is None:
+        out = torch.empty((x.N, x.H, x.W), dtype=torch.float32, device=x.t.device)
+    check(load().vu_final_conv1(x.t.data_ptr(), x.N, x.H, x.W, x.C, x.ctot, x.coff, _f32(w).data_ptr(), float(bias),
+                                out.data_ptr(), x.dt, _stream()), "vu_final_conv1")
+    _count()
+    return out
+
+
+SIG_NONE, SIG_PRE, SIG_POST = 0, 1, 2
+
+
+def resize_logits(x: torch.Tensor, Ho: int, Wo: int, sigmoid_mode: int = SIG_NONE) -> torch.Tensor:
+    """x fp32 [N,Hs,Ws] -> [N,Ho,Wo], bilinear align_corners=True."""
+    require_device()
+    x = _f32(x)
+    N, Hs, Ws = x.shape
+    y = torch.empty((N, Ho, Wo), dtype=torch.float32, device=x.device)
+    check(load().vu_resize_logits(x.data_ptr(), y.data_ptr(), N, Hs, Ws, Ho, Wo, sigmoid_mode, _stream()),
+          "vu_resize_logits")
+    _count()
+    return y
+
+
+def uncertainty_reduce(x: torch.Tensor, Ho: int, Wo: int, input_is_prob: bool = False, want_probs: bool = False,
+                       outs=("mean", "std", "entropy", "mutual_info", "coeff_var")):
+    """x fp32 [B,Ns,Hs,Ws] (logits, or probabilities at output size) -> dict of [B,Ho,Wo] maps."""
+    require_device()
+    x = _f32(x)
+    B, Ns, Hs, Ws = x.shape
+    dev = x.device
+    res = {k: torch.empty((B, Ho, Wo), dtype=torch.float32, device=dev) for k in outs}
+    probs = torch.empty((B, Ns, Ho, Wo), dtype=torch.float32, device=dev) if want_probs else None
+    g = lambda k: _ptr(res.get(k))
+    check(load().vu_uncertainty_reduce(x.data_ptr(), B, Ns, Hs, Ws, Ho, Wo, int(input_is_prob), g("mean"), g("std"),
+                                       g("entropy"), g("mutual_info"), g("coeff_var"), _ptr(probs), _stream()),
+          "vu_uncertainty_reduce")
+    _count()
+    if want_probs:
+        res["samples"] = probs
+    return res
+
+
+def moments_partial(probs: torch.Tensor):
+    """probs fp32 [Ns, ...] -> (mean, M2, sum_entropy) per pixel."""
+    require_device()
+    probs = _f32(probs)
+    Ns = probs.shape[0]
+    shp = probs.shape[1:]
+    npix = int(probs[0].numel()) if Ns > 0 else 0
+    mk = lambda: torch.zeros(shp, dtype=torch.float32, device=probs.device)
+    mean, m2, sh = mk(), mk(), mk()
+    if Ns > 0:
+        check(load().vu_moments_partial(probs.data_ptr(), Ns, npix, mean.data_ptr(), m2.data_ptr(), sh.data_ptr(),
+                                        _stream()), "vu_moments_partial")
+        _count()
+    return mean, m2, sh
+
+
+def moments_finalize(counts, mean: torch.Tensor, m2: torch.Tensor, sh: torch.Tensor):
+    """Chan-merge stacked shard moments [S, ...] with per-shard sample counts -> dict of maps."""
+    require_device()
+    S = mean.shape[0]
+    shp = mean.shape[1:]
+    npix = int(mean[0].numel())
+    arr = (C.c_float * S)(*[float(c) for c in counts])
+    res = {k: torch.empty(shp, dtype=torch.float32, device=mean.device)
+           for k in ("mean", "std", "entropy", "mutual_info", "coeff_var")}
+    check(load().vu_moments_finalize(C.cast(arr, C.c_void_p), _f32(mean).data_ptr(), _f32(m2).data_ptr(),
+                                     _f32(sh).data_ptr(), S, npix, res["mean"].data_ptr(), res["std"].data_ptr(),
+                                     res["entropy"].data_ptr(), res["mutual_info"].data_ptr(),
+                                     res["coeff_var"].data_ptr(), _stream()), "vu_moments_finalize")
+    _count()
+    return res
+
+
+def blend_accumulate(tile: torch.Tensor, sh: int, sw: int, ti: int, tj: int, nth: int, ntw: int, overlap: int,
+                     acc: torch.Tensor, wsum: torch.Tensor) -> None:
+    require_device()
+    tile = _f32(tile)
+    ph, pw = tile.shape[-2:]
+    H, W = acc.shape[-2:]
+    check(load().vu_blend_accumulate(tile.data_ptr(), ph, pw, sh, sw, ti, tj, nth, ntw, overlap, _f32(acc).data_ptr(),
+                                     _f32(wsum).data_ptr(), H, W, _stream()), "vu_blend_accumulate")
+    _count()
+
+
+def blend_finalize(acc: torch.Tensor, wsum: torch.Tensor) -> torch.Tensor:
+    require_device()
+    out = torch.empty_like(acc)
+    check(load().vu_blend_finalize(_f32(acc).data_ptr(), _f32(wsum).data_ptr(), out.data_ptr(), acc.numel(), _stream()),
+          "vu_blend_finalize")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------ losses / metrics
+def seg_loss_sums(x: torch.Tensor, target: torch.Tensor, input_is_prob=False, focal_alpha=0.8, focal_gamma=2.0):
+    """-> fp64[8]: sum p, sum t, sum pt, sum bce, sum focal, count, sum (p-t)^2, sum nll."""
+    require_device()
+    x = _f32(x.contiguous()); target = _f32(target.float().contiguous())
+    assert x.numel() == target.numel()
+    sums = torch.empty(8, dtype=torch.float64, device=x.device)
+    check(load().vu_seg_loss_sums(x.data_ptr(), target.data_ptr(), x.numel(), int(input_is_prob), float(focal_alpha),
+                                  float(focal_gamma), sums.data_ptr(), _stream()), "vu_seg_loss_sums")
+    _count()
+    return sums
+
+
+def seg_loss_bwd(x, target, sums, w_bce, w_dice, w_focal, focal_alpha=0.8, focal_gamma=2.0, smooth=1.0,
+                 grad_scale=1.0) -> torch.Tensor:
+    require_device()
+    x = _f32(x.contiguous()); target = _f32(target.float().contiguous())
+    dx = torch.empty_like(x)
+    check(load().vu_seg_loss_bwd(x.data_ptr(), target.data_ptr(), x.numel(), sums.data_ptr(), float(w_bce),
+                                 float(w_dice), float(w_focal), float(focal_alpha), float(focal_gamma), float(smooth),
+                                 float(grad_scale), dx.data_ptr(), _stream()), "vu_seg_loss_bwd")
+    _count()
+    return dx
+
+
+def kl_free_bits(mu: torch.Tensor, logvar: torch.Tensor, free_bits: float, want_grad=False, grad_scale=1.0):
+    require_device()
+    mu = _f32(mu.contiguous()); logvar = _f32(logvar.contiguous())
+    B, L = mu.shape
+    kl = torch.empty((), dtype=torch.float32, device=mu.device)
+    dmu = torch.empty_like(mu) if want_grad else None
+    dlv = torch.empty_like(mu) if want_grad else None
+    check(load().vu_kl_free_bits(mu.data_ptr(), logvar.data_ptr(), B, L, float(free_bits), kl.data_ptr(), _ptr(dmu),
+                                 _ptr(dlv), float(grad_scale), _stream()), "vu_kl_free_bits")
+    _count()
+    return (kl, dmu, dlv) if want_grad else kl
+
+
+def ece_hist(p: torch.Tensor, gt: torch.Tensor, num_bins: int = 10) -> torch.Tensor:
+    """-> fp64 [3, bins]: count, sum gt, sum p."""
+    require_device()
+    p = _f32(p.contiguous()); gt = _f32(gt.float().contiguous())
+    hist = torch.empty((3, num_bins), dtype=torch.float64, device=p.device)
+    check(load().vu_ece_hist(p.data_ptr(), gt.data_ptr(), p.numel(), num_bins, hist.data_ptr(), _stream()), "vu_ece_hist")
+    _count(2)
+    return hist
+
+
+def confusion_counts(x: torch.Tensor, t: torch.Tensor, thr: float = 0.5) -> torch.Tensor:
+    """-> fp64 [4]: tp, fp, tn, fn of (x > thr) against (t > 0.5)."""
+    require_device()
+    x = _f32(x.contiguous()); t = _f32(t.float().contiguous())
+    c = torch.empty(4, dtype=torch.float64, device=x.device)
+    check(load().vu_confusion_counts(x.data_ptr(), t.data_ptr(), x.numel(), float(thr), c.data_ptr(), _stream()),
+          "vu_confusion_counts")
+    _count(2)
+    return c
