@@ -1,0 +1,70 @@
+"""Deterministic fixture weights (seeded init + committed BN-calibration overlay) used by the
+parity tests, `__graft_entry__.smoke()` and `bench.py` (there are no shipped checkpoints)."""
+from __future__ import annotations
+
+import math
+from pathlib import Path
+from typing import Dict
+
+import torch
+
+GOLDEN = Path(__file__).resolve().parent.parent / "tests" / "golden"
+
+
+def seeded_state_dict(template: Dict[str, torch.Tensor], seed: int = 0) -> Dict[str, torch.Tensor]:
+    """Fill a state_dict template (keys/shapes) with seeded values, in key order, on the CPU."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    for k, t in template.items():
+        shp = tuple(t.shape)
+        if k.endswith("num_batches_tracked"):
+            v = torch.zeros(shp, dtype=torch.int64)
+        elif k.endswith("running_mean"):
+            v = torch.zeros(shp)
+        elif k.endswith("running_var"):
+            v = torch.ones(shp)
+        elif len(shp) == 4:                              # conv / conv-transpose weight
+            if ".up.weight" in k:                        # ConvTranspose2d [I,O,2,2]
+                fan_in = shp[0]
+            else:
+                fan_in = shp[1] * shp[2] * shp[3]
+            v = torch.randn(shp, generator=g) * math.sqrt(2.0 / fan_in)
+        elif k.endswith(".weight"):                      # BN gamma
+            base = 0.6 if (".bn2." in k) else 1.0
+            v = base + 0.1 * torch.randn(shp, generator=g)
+        elif k.endswith(".bias"):
+            v = 0.1 * torch.randn(shp, generator=g)
+        else:
+            raise KeyError(k)
+        sd[k] = v
+    return sd
+
+
+def load_fixture(name: str, template: Dict[str, torch.Tensor], seed: int = 0) -> Dict[str, torch.Tensor]:
+    """seeded init + overlay of the small calibrated tensors in tests/golden/<name>.pt
+    (BN running stats, rescaled heads / output conv) written by tests/golden/make_golden.py."""
+    sd = seeded_state_dict(template, seed)
+    f = GOLDEN / f"{name}.pt"
+    if not f.exists():
+        raise FileNotFoundError(f"{f} missing: run tests/golden/make_golden.py in the build container")
+    overlay = torch.load(f, map_location="cpu", weights_only=True)
+    for k, v in overlay.items():
+        assert k in sd and sd[k].shape == v.shape, k
+        sd[k] = v.clone()
+    return sd
+
+
+def resnet_fixture(seed: int = 0, **model_kwargs):
+    """-> (state_dict on CPU, model kwargs). Template comes from the drop-in module itself."""
+    from .unet.unet_resnet import UNetResNet
+    kw = dict(n_channels=3, n_classes=1, pretrained=False)
+    kw.update(model_kwargs)
+    tmpl = UNetResNet(**kw).state_dict()
+    name = "fixture_resnet" + ("" if kw.get("latent_injection", "all") == "all" else "_" + str(kw["latent_injection"]))
+    return load_fixture(name, tmpl, seed), kw
+
+
+def unet_fixture(seed: int = 0, bilinear: bool = False):
+    from .unet.unet_model import UNet
+    tmpl = UNet(3, 1, bilinear).state_dict()
+    return load_fixture("fixture_unet" + ("_bilinear" if bilinear else ""), tmpl, seed)
