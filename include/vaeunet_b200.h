@@ -122,6 +122,10 @@ int vu_latent_head(const void* f4, int B, int h, int w, int C, int f_ctot, int f
                    const float* w_mu, const float* b_mu, const float* w_lv, const float* b_lv,
                    const float* eps, float temperature, int Ns, int L,
                    float* mu, float* logvar, float* z, int dtype, vu_stream_t stream);
+/* z[n, j] = mu[j] + eps[n, j] * exp(.5 logvar[j]) * T  (utils/vae_utils.py:5-10; unet_resnet.py:191-194).
+ * mu/logvar fp32 [n_per_sample]; eps/z fp32 [num_samples][n_per_sample]. */
+int vu_reparameterize(const float* mu, const float* logvar, const float* eps, float temperature, float* z,
+                      size_t n_per_sample, int num_samples, vu_stream_t stream);
 /* v[i,:] = act(scale * (W z[i,:] + b) + shift): the 1x1 conv + BN + ReLU applied to a spatially
  * constant map (z_initial unet_resnet.py:150-154; z_proj :37-41). z fp32 [M][L], W fp32 [C][L]. */
 int vu_latent_project(const float* z, const float* w, const float* scale, const float* shift,

@@ -156,6 +156,15 @@ final_conv1_kernel(const uint16_t* __restrict__ x, size_t npix, int x_ctot, int 
     }
 }
 
+__global__ void reparameterize_kernel(const float* __restrict__ mu, const float* __restrict__ lv,
+                                      const float* __restrict__ eps, float temperature, float* __restrict__ z,
+                                      size_t n_per_sample, size_t total) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t j = i % n_per_sample;
+        z[i] = mu[j] + eps[i] * (expf(0.5f * lv[j]) * temperature);
+    }
+}
+
 static int grid_cap(size_t blocks) {
     const size_t cap = (size_t)num_sms() * 16;
     if (blocks > cap) blocks = cap;
@@ -230,5 +239,15 @@ extern "C" int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_c
     else
         final_conv1_kernel<16><<<grid_cap((npix * 16 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
     VU_CHECK_LAUNCH("final_conv1");
+    return 0;
+}
+
+extern "C" int vu_reparameterize(const float* mu, const float* logvar, const float* eps, float temperature, float* z,
+                                 size_t n_per_sample, int num_samples, vu_stream_t st) {
+    if (!mu || !logvar || !eps || !z || num_samples < 1) return set_error(VU_ERR_INVALID, "reparameterize: bad args");
+    const size_t total = n_per_sample * (size_t)num_samples;
+    reparameterize_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(mu, logvar, eps, temperature, z,
+                                                                                      n_per_sample, total);
+    VU_CHECK_LAUNCH("reparameterize");
     return 0;
 }

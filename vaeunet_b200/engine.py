@@ -308,8 +308,12 @@ class ResNetVAEEngine:
         out = ops.resize_logits(lg.reshape(-1, lg.shape[2], lg.shape[3]), H, W, ops.SIG_NONE)
         return out.reshape(B, self.n_classes, H, W), mu, lv
 
+    def mc_logits_honour_skip(self, images, temperature, Ns, eps, sample=True):
+        """generate_predictions flavour (utils/vae_utils.py:63-65 honours model.use_skip)."""
+        return self.mc_logits(images, temperature, Ns, eps, sample, honour_use_skip=True)
+
     def mc_logits(self, images: torch.Tensor, temperature: float, Ns: int, eps: Optional[torch.Tensor],
-                  sample: bool = True):
+                  sample: bool = True, honour_use_skip: bool = False):
         """One encoder pass, Ns batched decodes. -> logits [B, Ns, h, w] (H/2), mu, logvar."""
         B = images.shape[0]
         feats = self.encode(images)
@@ -317,7 +321,7 @@ class ResNetVAEEngine:
             eps = torch.randn(Ns, B, self.latent_dim, device=self.dev)
         mu, lv, z = self.heads(feats[-1], eps if sample else None, temperature, Ns)
         z_dec = z.permute(1, 0, 2).reshape(B * Ns, self.latent_dim)   # sample-minor
-        lg = self.decode(feats, z_dec, honour_use_skip=False)
+        lg = self.decode(feats, z_dec, honour_use_skip=honour_use_skip)
         return lg.reshape(B, Ns, lg.shape[2], lg.shape[3]), mu, lv
 
     def mc_predict(self, images: torch.Tensor, temperature: float = 1.0, num_samples: int = 10,

@@ -20,6 +20,8 @@ _TORCH_DT = {BF16: torch.bfloat16, F16: torch.float16}
 
 # launch counter (bench.py reports it as gpu_launches)
 LAUNCHES = 0
+# when set to a list, conv2d appends (start_event, end_event, algorithmic_flop) per launch (bench.py roofline)
+CONV_TIMING = None
 
 
 def _count(n: int = 1) -> None:
@@ -124,7 +126,14 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
     a.y = out.t.data_ptr(); a.y_ctot = out.ctot; a.y_coff = out.coff
     a.out_up = out_up; a.out_dh = out_dh; a.out_dw = out_dw
     a.dtype = x.dt; a.max_ctas = max_ctas
-    check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
+    if CONV_TIMING is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
+        e1.record()
+        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * k * k * x.C))
+    else:
+        check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
     _count()
     return out
 
@@ -247,6 +256,19 @@ def latent_head(f4: Act, w_mu, b_mu, w_lv, b_lv, eps: Optional[torch.Tensor], te
           "vu_latent_head")
     _count()
     return mu, lv, z
+
+
+def reparameterize(mu: torch.Tensor, logvar: torch.Tensor, eps: torch.Tensor, temperature: float = 1.0) -> torch.Tensor:
+    """z = mu + eps * exp(.5 logvar) * T ; eps [..., *mu.shape] (leading sample dims broadcast over mu)."""
+    require_device()
+    mu = _f32(mu.contiguous()); logvar = _f32(logvar.contiguous()); eps = _f32(eps.contiguous())
+    n = mu.numel()
+    assert eps.numel() % n == 0 and eps.shape[-mu.dim():] == mu.shape
+    z = torch.empty_like(eps)
+    check(load().vu_reparameterize(mu.data_ptr(), logvar.data_ptr(), eps.data_ptr(), float(temperature), z.data_ptr(),
+                                   n, eps.numel() // n, _stream()), "vu_reparameterize")
+    _count()
+    return z
 
 
 def latent_project(z: torch.Tensor, w: torch.Tensor, scale: Optional[torch.Tensor], shift: Optional[torch.Tensor],

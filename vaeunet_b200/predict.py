@@ -1,0 +1,152 @@
+"""Drop-ins for the hot-path functions of the reference's visualize_vae.py:
+predict_full_image (:61-87), calculate_uncertainty_metrics (:90-117), predict_with_patches
+(:243-415) and the N-sample loop of get_segmentation_distribution_from_image (:578-652).
+
+B200 re-design: tiles are batched through the engine; blending, normalisation and the
+N-sample reduction stay on the device (the reference round-trips every tile through the CPU,
+:380-384, and re-runs the encoder for every sample, :324 — `segmentation_distribution` below runs
+the encoder ONCE per tile batch and decodes all N samples as one batched pass)."""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional
+
+import torch
+
+from . import ops
+
+
+def _z_vec(z: torch.Tensor) -> torch.Tensor:
+    return z.float().reshape(z.shape[0], z.shape[1]).contiguous()
+
+
+def predict_full_image(model, img, z):
+    """visualize_vae.py:61-87: encoder + decode one z -> upsample -> sigmoid. z [1,L,1,1] or [1,L]."""
+    model.eval()
+    eng = model.engine()
+    with torch.no_grad():
+        feats = eng.encode(img.float().contiguous())
+        lg = eng.decode(feats, _z_vec(z).expand(img.shape[0], -1).contiguous(), honour_use_skip=False)
+        B, C, h, w = lg.shape
+        out = ops.resize_logits(lg.reshape(B * C, h, w), img.shape[2], img.shape[3], ops.SIG_POST)
+        return out.reshape(B, C, img.shape[2], img.shape[3])
+
+
+def calculate_uncertainty_metrics(segmentations: torch.Tensor) -> Dict[str, torch.Tensor]:
+    """visualize_vae.py:90-117. segmentations [N,B,1,H,W] (or [N,1,H,W]) probabilities on the device."""
+    s = segmentations.float()
+    if s.dim() == 4:
+        s = s.unsqueeze(1)
+    N, B, C, H, W = s.shape
+    assert C == 1
+    x = s[:, :, 0].permute(1, 0, 2, 3).contiguous()   # [B,N,H,W]
+    return ops.uncertainty_reduce(x, H, W, input_is_prob=True)
+
+
+def patch_grid(H: int, W: int, patch_size: int, overlap: int):
+    """Tile coordinates, visualize_vae.py:253-288 (last row/col snapped to the image edge)."""
+    stride = patch_size - overlap
+    nh = math.ceil((H - overlap) / stride)
+    nw = math.ceil((W - overlap) / stride)
+    info = []
+    for i in range(nh):
+        for j in range(nw):
+            sh, sw = i * stride, j * stride
+            if i == nh - 1:
+                eh = H; sh = max(0, eh - patch_size)
+            else:
+                eh = min(sh + patch_size, H)
+            if j == nw - 1:
+                ew = W; sw = max(0, ew - patch_size)
+            else:
+                ew = min(sw + patch_size, W)
+            info.append((sh, eh, sw, ew))
+    return nh, nw, info
+
+
+def default_overlap(patch_size: int) -> int:
+    return max(min(int(patch_size * 0.2), 128), 32)   # visualize_vae.py:251
+
+
+def _tiles_probs(eng, img, z_dec_rows: torch.Tensor, info, idxs, Ns: int):
+    """Run a batch of equal-sized tiles: encoder once, Ns decodes each (sample-minor).
+    -> probabilities [T, Ns, ph, pw] (sigmoid at tile/2, THEN bilinear up: visualize_vae.py:345-358)."""
+    tiles = torch.cat([img[:, :, info[k][0]:info[k][1], info[k][2]:info[k][3]] for k in idxs], 0).contiguous()
+    T = tiles.shape[0]
+    feats = eng.encode(tiles)
+    z_dec = z_dec_rows.unsqueeze(0).expand(T, -1, -1).reshape(T * Ns, -1).contiguous()
+    lg = eng.decode(feats, z_dec, honour_use_skip=False)          # [T*Ns,1,h,w]
+    h, w = lg.shape[2:]
+    ph, pw = tiles.shape[2:]
+    return ops.resize_logits(lg.reshape(T * Ns, h, w), ph, pw, ops.SIG_PRE).reshape(T, Ns, ph, pw)
+
+
+def predict_with_patches(model, img, z, patch_size=512, overlap=None, batch_size=4):
+    """visualize_vae.py:243-415 for one z ([1,L,1,1]). -> [1,1,H,W] blended probabilities."""
+    out = blended_samples(model, img, _z_vec(z), patch_size, overlap, batch_size)
+    return out[:, None]
+
+
+def blended_samples(model, img, z_rows: torch.Tensor, patch_size=512, overlap=None, batch_size=4,
+                    tile_subset=None, finalize=True):
+    """All Ns samples of a tiled image in one sweep: z_rows [Ns, L] (every tile of a sample shares
+    its z, visualize_vae.py:328-334). -> [Ns,H,W] blended probabilities (or the raw
+    (acc, wsum) accumulators when finalize=False, for multi-GPU tile sharding)."""
+    model.eval()
+    eng = model.engine()
+    B, C, H, W = img.shape
+    assert B == 1, "the reference tiles one image at a time"
+    if overlap is None:
+        overlap = default_overlap(patch_size)
+    nh, nw, info = patch_grid(H, W, patch_size, overlap)
+    Ns = z_rows.shape[0]
+    img = img.float().contiguous()
+    acc = torch.zeros((Ns, H, W), dtype=torch.float32, device=img.device)
+    wsum = torch.zeros((Ns, H, W), dtype=torch.float32, device=img.device)
+    todo = list(range(len(info))) if tile_subset is None else list(tile_subset)
+    with torch.no_grad():
+        # group equal-sized tiles (ragged only when the image is smaller than a patch)
+        pos = 0
+        while pos < len(todo):
+            grp = [todo[pos]]
+            shp = (info[todo[pos]][1] - info[todo[pos]][0], info[todo[pos]][3] - info[todo[pos]][2])
+            pos += 1
+            while pos < len(todo) and len(grp) < batch_size and \
+                    (info[todo[pos]][1] - info[todo[pos]][0], info[todo[pos]][3] - info[todo[pos]][2]) == shp:
+                grp.append(todo[pos]); pos += 1
+            probs = _tiles_probs(eng, img, z_rows, info, grp, Ns)
+            for t, k in enumerate(grp):
+                sh, eh, sw, ew = info[k]
+                i, j = divmod(k, nw)
+                for n in range(Ns):
+                    ops.blend_accumulate(probs[t, n], sh, sw, i, j, nh, nw, overlap, acc[n], wsum[n])
+    if not finalize:
+        return acc, wsum
+    return ops.blend_finalize(acc, wsum)
+
+
+def segmentation_distribution(model, img, num_samples=32, patch_size=None, overlap=None, temperature=1.0,
+                              batch_size=4, eps: Optional[torch.Tensor] = None):
+    """Tensor part of get_segmentation_distribution_from_image (visualize_vae.py:578-652):
+    mu/logvar from the WHOLE image (:603), N samples z = mu + eps*exp(.5 logvar)*T (:620-623), each
+    decoded by patches or full image. -> (segmentations [N,1,H,W] on the device, mu, logvar)."""
+    model.eval()
+    with torch.no_grad():
+        mu, logvar = model.encode(img)
+        sample = getattr(model, "latent_injection", "all") not in ("none",)
+        if sample:
+            if eps is None:
+                eps = torch.randn(num_samples, *mu.shape, device=mu.device)
+            z = ops.reparameterize(mu, logvar, eps.float().contiguous(), temperature)   # [N,1,L]
+        else:
+            z = mu.unsqueeze(0).expand(num_samples, -1, -1).contiguous()
+        z_rows = z[:, 0].contiguous()
+        if patch_size is not None and patch_size > 0:
+            segs = blended_samples(model, img, z_rows, patch_size, overlap, batch_size)
+        else:
+            eng = model.engine()
+            feats = eng.encode(img.float().contiguous())
+            lg = eng.decode(feats, z_rows, honour_use_skip=False)
+            segs = ops.resize_logits(lg.reshape(num_samples, lg.shape[2], lg.shape[3]), img.shape[2], img.shape[3],
+                                     ops.SIG_POST)
+    return segs.unsqueeze(1), mu, logvar
