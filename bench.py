@@ -1,5 +1,6 @@
 """Headline benchmark (BASELINE.json): MC-uncertainty patches/s, 512x512 patches, T=1.0, N=10
-latent samples, mean/std/entropy maps, bf16, synthetic fundus patches, fixture weights.
+latent samples, mean/std/entropy maps, 16-bit tensor-core operands (f16 default, --dtype bf16), fp32
+accumulation, synthetic fundus patches, fixture weights.
 
   python bench.py --gpus N --steps K --warmup W            # this repo's B200 path
   python bench.py --impl reference ...                     # the reference algorithm on the host cores
@@ -131,7 +132,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="patches per step per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f16"])
+    ap.add_argument("--dtype", default="f16", choices=["bf16", "f16"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -107,8 +107,50 @@ def _bn(sd: SD, p: str, x: Tensor, st: Optional[BNState]) -> Tensor:
                         sd[p + "weight"], sd[p + "bias"], False, BN_MOMENTUM, BN_EPS)
 
 
-def _conv(sd: SD, p: str, x: Tensor, stride: int = 1, padding: int = 0) -> Tensor:
-    return F.conv2d(x, sd[p + "weight"], sd.get(p + "bias"), stride=stride, padding=padding)
+# --------------------------------------------------------------------------------------
+# optional emulation of 16-bit activation / weight STORAGE (tests only)
+# --------------------------------------------------------------------------------------
+# The B200 kernels keep activations and tensor-core filter banks as bf16 or fp16 and do all
+# arithmetic in fp32. With STORAGE_DTYPE set, `_q` rounds at exactly the points where the kernels
+# write a 16-bit buffer, so a GPU result can be checked against "the reference algorithm with the
+# same storage rounding" (kernel correctness) separately from "fp32 reference" (rounding budget).
+# The golden-vector tests always run with STORAGE_DTYPE = None.
+STORAGE_DTYPE: Optional[torch.dtype] = None
+
+
+class storage_rounding:
+    """with storage_rounding(torch.bfloat16): ... — round at the kernels' 16-bit storage points."""
+
+    def __init__(self, dtype: Optional[torch.dtype]):
+        self.dtype = dtype
+
+    def __enter__(self):
+        global STORAGE_DTYPE
+        self.prev = STORAGE_DTYPE
+        STORAGE_DTYPE = self.dtype
+        return self
+
+    def __exit__(self, *exc):
+        global STORAGE_DTYPE
+        STORAGE_DTYPE = self.prev
+        return False
+
+
+def _q(x: Tensor) -> Tensor:
+    return x if STORAGE_DTYPE is None else x.to(STORAGE_DTYPE).to(torch.float32)
+
+
+def _is_const_map(x: Tensor) -> bool:
+    return bool((x.amax(dim=(2, 3)) == x.amin(dim=(2, 3))).all())
+
+
+def _conv(sd: SD, p: str, x: Tensor, stride: int = 1, padding: int = 0, fp32: bool = False) -> Tensor:
+    """fp32=True marks the convs the kernels run with fp32 weights (stem, heads, output conv and the
+    1x1 convs on spatially constant latent maps); all others use 16-bit filter banks."""
+    w = sd[p + "weight"]
+    if not fp32:
+        w = _q(w)
+    return F.conv2d(x, w, sd.get(p + "bias"), stride=stride, padding=padding)
 
 
 def _up_ac(x: Tensor, size) -> Tensor:
@@ -123,7 +165,7 @@ def _up_ac(x: Tensor, size) -> Tensor:
 def resnet34_features(sd: SD, x: Tensor, prefix: str = "encoder.",
                       st: Optional[BNState] = None) -> List[Tensor]:
     p = prefix
-    x = F.relu(_bn(sd, p + "bn1.", _conv(sd, p + "conv1.", x, 2, 3), st))
+    x = _q(F.relu(_bn(sd, p + "bn1.", _conv(sd, p + "conv1.", x, 2, 3, fp32=True), st)))
     feats = [x]
     x = F.max_pool2d(x, 3, 2, 1)
     for li, nblk in enumerate(RESNET34_STAGES, start=1):
@@ -131,11 +173,11 @@ def resnet34_features(sd: SD, x: Tensor, prefix: str = "encoder.",
             q = f"{p}layer{li}.{b}."
             stride = 2 if (li > 1 and b == 0) else 1
             idt = x
-            y = F.relu(_bn(sd, q + "bn1.", _conv(sd, q + "conv1.", x, stride, 1), st))
+            y = _q(F.relu(_bn(sd, q + "bn1.", _conv(sd, q + "conv1.", x, stride, 1), st)))
             y = _bn(sd, q + "bn2.", _conv(sd, q + "conv2.", y, 1, 1), st)
             if (q + "downsample.0.weight") in sd:
-                idt = _bn(sd, q + "downsample.1.", _conv(sd, q + "downsample.0.", x, stride, 0), st)
-            x = F.relu(y + idt)
+                idt = _q(_bn(sd, q + "downsample.1.", _conv(sd, q + "downsample.0.", x, stride, 0), st))
+            x = _q(F.relu(y + idt))
         feats.append(x)
     return feats
 
@@ -144,14 +186,14 @@ def resnet34_features(sd: SD, x: Tensor, prefix: str = "encoder.",
 # attention gate / decoder block / heads
 # --------------------------------------------------------------------------------------
 def attention_gate(sd: SD, p: str, g: Tensor, x: Tensor, st: Optional[BNState] = None,
-                   return_psi: bool = False):
+                   return_psi: bool = False, g_fp32: bool = False):
     """x * sigmoid(BN(psi(ReLU(BN(W_g g) + BN(W_x x)))))
     unet/unet_parts.py:7-30 == unet/unet_resnet.py:6-29."""
-    g1 = _bn(sd, p + "W_g.1.", _conv(sd, p + "W_g.0.", g), st)
-    x1 = _bn(sd, p + "W_x.1.", _conv(sd, p + "W_x.0.", x), st)
+    g1 = _q(_bn(sd, p + "W_g.1.", _conv(sd, p + "W_g.0.", g, fp32=g_fp32), st))
+    x1 = _q(_bn(sd, p + "W_x.1.", _conv(sd, p + "W_x.0.", x), st))
     a = F.relu(g1 + x1)
-    psi = torch.sigmoid(_bn(sd, p + "psi.1.", _conv(sd, p + "psi.0.", a), st))
-    return (x * psi, psi) if return_psi else x * psi
+    psi = torch.sigmoid(_bn(sd, p + "psi.1.", _conv(sd, p + "psi.0.", a, fp32=True), st))
+    return (_q(x * psi), psi) if return_psi else _q(x * psi)
 
 
 def decoder_block(sd: SD, p: str, x: Tensor, skip: Optional[Tensor], z: Tensor,
@@ -162,26 +204,32 @@ def decoder_block(sd: SD, p: str, x: Tensor, skip: Optional[Tensor], z: Tensor,
         size = skip.shape[2:]
     else:
         size = (x.shape[2] * 2, x.shape[3] * 2)
+    # storage emulation: a spatially constant x (z_initial output) stays an fp32 vector in the
+    # kernels; it is rounded only where it is written into the concat buffer
+    x_const = STORAGE_DTYPE is not None and _is_const_map(x)
     x = _up_ac(x, size)
-    comps = [x]
+    g = x if x_const else _q(x)
+    comps = [_q(x)]
     if skip is not None and use_skip:
         if use_attention:
-            skip = attention_gate(sd, p + "attention.", x, skip, st)
+            skip = attention_gate(sd, p + "attention.", g, skip, st, g_fp32=x_const)
         comps.append(skip)
     if use_latent:
         zp = _up_ac(z, size)
-        zp = F.relu(_bn(sd, p + "z_proj.1.", _conv(sd, p + "z_proj.0.", zp), st))
+        z_const = STORAGE_DTYPE is not None and _is_const_map(zp)
+        zp = zp if (z_const or STORAGE_DTYPE is None) else _q(zp)
+        zp = _q(F.relu(_bn(sd, p + "z_proj.1.", _conv(sd, p + "z_proj.0.", zp, fp32=z_const), st)))
         comps.append(zp)
     x = torch.cat(comps, dim=1)
-    x = F.relu(_bn(sd, p + "conv1.1.", _conv(sd, p + "conv1.0.", x, 1, 1), st))
-    x = F.relu(_bn(sd, p + "conv2.1.", _conv(sd, p + "conv2.0.", x, 1, 1), st))
+    x = _q(F.relu(_bn(sd, p + "conv1.1.", _conv(sd, p + "conv1.0.", x, 1, 1), st)))
+    x = _q(F.relu(_bn(sd, p + "conv2.1.", _conv(sd, p + "conv2.0.", x, 1, 1), st)))
     return x
 
 
 def latent_heads(sd: SD, x_enc: Tensor) -> Tuple[Tensor, Tensor]:
     """mu/logvar = GAP(conv1x1(x_enc)); unet/unet_resnet.py:140-147,205-206."""
-    mu = F.adaptive_avg_pool2d(_conv(sd, "mu_head.0.", x_enc), 1).squeeze(-1).squeeze(-1)
-    lv = F.adaptive_avg_pool2d(_conv(sd, "logvar_head.0.", x_enc), 1).squeeze(-1).squeeze(-1)
+    mu = F.adaptive_avg_pool2d(_conv(sd, "mu_head.0.", x_enc, fp32=True), 1).squeeze(-1).squeeze(-1)
+    lv = F.adaptive_avg_pool2d(_conv(sd, "logvar_head.0.", x_enc, fp32=True), 1).squeeze(-1).squeeze(-1)
     return mu, lv
 
 
@@ -199,7 +247,7 @@ def decode_from_features(sd: SD, cfg: ResNetCfg, features: Sequence[Tensor], z: 
         z = z.unsqueeze(-1).unsqueeze(-1)
     z_sp = _up_ac(z, features[-1].shape[2:])
     if cfg.use_bottleneck:
-        x = F.relu(_bn(sd, "z_initial.1.", _conv(sd, "z_initial.0.", z_sp), st))
+        x = F.relu(_bn(sd, "z_initial.1.", _conv(sd, "z_initial.0.", z_sp, fp32=True), st))
     else:
         x = features[-1]
     ul = cfg.use_latent_list
@@ -208,7 +256,7 @@ def decode_from_features(sd: SD, cfg: ResNetCfg, features: Sequence[Tensor], z: 
         skip = features[-(i + 2)] if (i < len(features) - 1 and want_skip) else None
         x = decoder_block(sd, f"decoder_blocks.{i}.", x, skip, z_sp,
                           cfg.attention_on, cfg.use_skip, ul[i], st)
-    return _conv(sd, "final_conv.", x)
+    return _conv(sd, "final_conv.", x, fp32=True)
 
 
 # --------------------------------------------------------------------------------------
@@ -241,7 +289,7 @@ def unetresnet_decode(sd: SD, cfg: ResNetCfg, z: Tensor, input_size=None) -> Ten
     zz = z.unsqueeze(-1).unsqueeze(-1)
     z_sp = _up_ac(zz, feats[-1].shape[2:])
     if cfg.use_bottleneck:
-        x = F.relu(_bn(sd, "z_initial.1.", _conv(sd, "z_initial.0.", z_sp), None))
+        x = F.relu(_bn(sd, "z_initial.1.", _conv(sd, "z_initial.0.", z_sp, fp32=True), None))
     else:
         x = torch.zeros(z.size(0), 512, *feats[-1].shape[2:])
     ul = cfg.use_latent_list
@@ -249,7 +297,7 @@ def unetresnet_decode(sd: SD, cfg: ResNetCfg, z: Tensor, input_size=None) -> Ten
         skip = feats[-(i + 2)] if cfg.use_skip else None
         x = decoder_block(sd, f"decoder_blocks.{i}.", x, skip, z_sp,
                           cfg.attention_on, cfg.use_skip, ul[i], None)
-    out = _conv(sd, "final_conv.", x)
+    out = _conv(sd, "final_conv.", x, fp32=True)
     if input_size is not None:
         out = _up_ac(out, input_size)
     return out
@@ -619,8 +667,9 @@ def adamw_step(params: Dict[str, Tensor], grads: Dict[str, Tensor], state: Dict[
 # --------------------------------------------------------------------------------------
 def double_conv(sd: SD, p: str, x: Tensor, st: Optional[BNState] = None) -> Tensor:
     """DoubleConv, unet/unet_parts.py:32-49 (indices 0,1 / 3,4 of the Sequential)."""
-    x = F.relu(_bn(sd, p + "double_conv.1.", _conv(sd, p + "double_conv.0.", x, 1, 1), st))
-    x = F.relu(_bn(sd, p + "double_conv.4.", _conv(sd, p + "double_conv.3.", x, 1, 1), st))
+    small = sd[p + "double_conv.0.weight"].shape[1] <= 4      # direct fp32 kernel on the network input
+    x = _q(F.relu(_bn(sd, p + "double_conv.1.", _conv(sd, p + "double_conv.0.", x, 1, 1, fp32=small), st)))
+    x = _q(F.relu(_bn(sd, p + "double_conv.4.", _conv(sd, p + "double_conv.3.", x, 1, 1), st)))
     return x
 
 
@@ -628,9 +677,9 @@ def unet_up(sd: SD, p: str, x1: Tensor, x2: Tensor, bilinear: bool,
             st: Optional[BNState] = None) -> Tensor:
     """Up.forward, unet/unet_parts.py:82-95: up, pad to skip, gate the skip, cat([skip, up])."""
     if bilinear:
-        x1 = F.interpolate(x1, scale_factor=2, mode="bilinear", align_corners=True)
+        x1 = _q(F.interpolate(x1, scale_factor=2, mode="bilinear", align_corners=True))
     else:
-        x1 = F.conv_transpose2d(x1, sd[p + "up.weight"], sd[p + "up.bias"], stride=2)
+        x1 = _q(F.conv_transpose2d(x1, _q(sd[p + "up.weight"]), sd[p + "up.bias"], stride=2))
     dy = x2.size(2) - x1.size(2)
     dx = x2.size(3) - x1.size(3)
     x1 = F.pad(x1, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])
@@ -647,4 +696,4 @@ def unet_forward(sd: SD, x: Tensor, bilinear: bool = False, st: Optional[BNState
     y = xs[4]
     for k in range(1, 5):
         y = unet_up(sd, f"up{k}.", y, xs[4 - k], bilinear, st)
-    return _conv(sd, "outc.conv.", y)
+    return _conv(sd, "outc.conv.", y, fp32=True)

@@ -33,6 +33,7 @@ from vaeunet_b200.testing import seeded_state_dict  # noqa: E402
 OUT = Path(__file__).resolve().parent
 torch.set_num_threads(8)
 L = 32
+TRAIN_STEPS = 400
 
 
 def calibrate(model, run_train_forward):
@@ -59,7 +60,33 @@ def small_overlay(sd, extra_keys):
     return keep
 
 
-def make_resnet(mode="all", seed=0):
+def train_last_block(model, steps, log_every=50):
+    torch.manual_seed(4242)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    params = list(model.decoder_blocks[3].parameters()) + list(model.final_conv.parameters())
+    for p in params:
+        p.requires_grad_(True)
+    opt = torch.optim.Adam(params, lr=2e-3)
+    crit = ref_loss.CombinedLoss()
+    model.eval()                                      # BN uses the calibrated running stats throughout
+    sizes = [(6, 64), (4, 96), (4, 128), (2, 192)]
+    for it in range(steps):
+        B, S = sizes[it % len(sizes)]
+        x, m = synthetic_fundus(B, S, seed=5000 + it)
+        out, _, _ = model(x)                          # draws its own eps (torch.manual_seed above)
+        loss = crit(out, m)
+        opt.zero_grad(); loss.backward(); opt.step()
+        if it % log_every == 0 or it == steps - 1:
+            with torch.no_grad():
+                pos = (out > 0).float().mean().item()
+            print(f"  fixture train step {it}: loss {loss.item():.4f} pos {pos:.4f} target {m.mean().item():.4f}", flush=True)
+    for p in model.parameters():
+        p.requires_grad_(True)
+    model.zero_grad()
+
+
+def make_resnet(mode="all", seed=0, train_steps=0):
     model = RefUNetResNet(3, 1, pretrained=False, latent_injection=mode)
     model.load_state_dict(seeded_state_dict(model.state_dict(), seed))
     imgs, _ = synthetic_fundus(8, 128, seed=77)
@@ -81,14 +108,23 @@ def make_resnet(mode="all", seed=0):
     eps = torch.randn(8, L, generator=g)
     with ref_shim.inject_eps([eps]):
         calibrate(model, lambda: model(imgs))
-    with torch.no_grad():
-        with ref_shim.inject_eps([eps]):
-            out, _, _ = model(imgs)
-        s = out.std()
-        model.final_conv.weight.mul_(2.5 / s)
-        model.final_conv.bias.copy_((model.final_conv.bias - out.mean()) * (2.5 / s) - 1.0)
     extra = {"mu_head.0.weight", "mu_head.0.bias", "logvar_head.0.weight", "logvar_head.0.bias",
              "final_conv.weight", "final_conv.bias"}
+    if train_steps > 0:
+        # "trained-like" output stage: fit decoder_blocks.3 + final_conv (175 k parameters, the
+        # only trained tensors stored) to the synthetic lesion masks with the reference's own CombinedLoss,
+        # everything upstream frozen at its seeded init. Logits become bimodal with sharp lesion borders,
+        # as a trained network's are, so the >= 99.9 % mask-agreement bar measures the kernels and not the
+        # number of pixels a random network parks on the threshold.
+        train_last_block(model, train_steps)
+        extra |= {k for k in model.state_dict() if k.startswith("decoder_blocks.3.") and not k.endswith("num_batches_tracked")}
+    else:
+        with torch.no_grad():
+            with ref_shim.inject_eps([eps]):
+                out, _, _ = model(imgs)
+            s = out.std()
+            model.final_conv.weight.mul_(2.5 / s)
+            model.final_conv.bias.copy_((model.final_conv.bias - out.mean()) * (2.5 / s) - 4.0)   # lesion-like prior: few positive pixels
     name = "fixture_resnet" + ("" if mode == "all" else "_" + mode)
     torch.save(small_overlay(model.state_dict(), extra), OUT / f"{name}.pt")
     return model
@@ -96,7 +132,7 @@ def make_resnet(mode="all", seed=0):
 
 def golden_resnet():
     G = {}
-    model = make_resnet("all")
+    model = make_resnet("all", train_steps=TRAIN_STEPS)
     g = torch.Generator().manual_seed(101)
     # --- forward (eval), 2 x 3 x 96 x 96 and an odd size
     for tag, (B, H, W) in {"fwd96": (2, 96, 96), "fwd_odd": (1, 100, 76)}.items():
@@ -199,7 +235,7 @@ def golden_unet():
             out = model(imgs)
             s = out.std()
             model.outc.conv.weight.mul_(2.5 / s)
-            model.outc.conv.bias.copy_((model.outc.conv.bias - out.mean()) * (2.5 / s) - 1.0)
+            model.outc.conv.bias.copy_((model.outc.conv.bias - out.mean()) * (2.5 / s) - 4.0)   # lesion-like prior: few positive pixels
         name = "fixture_unet" + ("_bilinear" if bilinear else "")
         torch.save(small_overlay(model.state_dict(), {"outc.conv.weight", "outc.conv.bias"}), OUT / f"{name}.pt")
         x, _ = synthetic_fundus(2, 64, 80, seed=900)

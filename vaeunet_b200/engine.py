@@ -253,7 +253,7 @@ class FinalConvUnit:
 
 class ResNetVAEEngine:
     def __init__(self, sd: Dict[str, torch.Tensor], device, latent_injection="all", use_attention=True,
-                 use_skip=True, latent_dim=32, n_channels=3, n_classes=1, dtype=ops.BF16):
+                 use_skip=True, latent_dim=32, n_channels=3, n_classes=1, dtype=ops.DEFAULT_DTYPE):
         ops.require_device()
         self.dev = torch.device(device)
         self.dtype = dtype

@@ -94,7 +94,7 @@ class UpUnit:
 class UNetEngine:
     """UNet.forward, unet/unet_model.py:25-36."""
 
-    def __init__(self, sd, device, bilinear=False, dtype=ops.BF16):
+    def __init__(self, sd, device, bilinear=False, dtype=ops.DEFAULT_DTYPE):
         ops.require_device()
         dev = torch.device(device)
         self.dev, self.dtype = dev, dtype

@@ -17,6 +17,8 @@ from ._lib import ConvArgs, check, load, require_device
 
 BF16, F16 = 0, 1
 _TORCH_DT = {BF16: torch.bfloat16, F16: torch.float16}
+# default 16-bit storage type of activations / filter banks (see unet/_base.py KernelModule.compute_dtype)
+DEFAULT_DTYPE = F16
 
 # launch counter (bench.py reports it as gpu_launches)
 LAUNCHES = 0

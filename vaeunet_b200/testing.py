@@ -9,6 +9,10 @@ from typing import Dict
 import torch
 
 GOLDEN = Path(__file__).resolve().parent.parent / "tests" / "golden"
+# BN gamma of the last BatchNorm of every residual block. timm zero-initialises it (zero_init_last) and
+# trained ResNets keep it small; 0.25 keeps the seeded network from amplifying rounding noise the way
+# a fully random residual stack does (DESIGN.md "Fixtures").
+RESIDUAL_GAMMA = 0.25
 
 
 def seeded_state_dict(template: Dict[str, torch.Tensor], seed: int = 0) -> Dict[str, torch.Tensor]:
@@ -30,7 +34,7 @@ def seeded_state_dict(template: Dict[str, torch.Tensor], seed: int = 0) -> Dict[
                 fan_in = shp[1] * shp[2] * shp[3]
             v = torch.randn(shp, generator=g) * math.sqrt(2.0 / fan_in)
         elif k.endswith(".weight"):                      # BN gamma
-            base = 0.6 if (".bn2." in k) else 1.0
+            base = RESIDUAL_GAMMA if (".bn2." in k) else 1.0
             v = base + 0.1 * torch.randn(shp, generator=g)
         elif k.endswith(".bias"):
             v = 0.1 * torch.randn(shp, generator=g)

@@ -45,7 +45,7 @@ class Down(KernelModule):
 
     def forward(self, x):
         self._require_eval()
-        return from_act(self._unit()(to_act(x)))
+        return from_act(self._unit()(to_act(x, self.compute_dtype)))
 
 
 class Up(KernelModule):
@@ -67,7 +67,7 @@ class Up(KernelModule):
 
     def forward(self, x1, x2):
         self._require_eval()
-        a1, a2 = to_act(x1), to_act(x2)
+        a1, a2 = to_act(x1, self.compute_dtype), to_act(x2, self.compute_dtype)
         psi = torch.empty((a2.N, a2.H, a2.W), dtype=torch.float32, device=a2.t.device)
         out = self._unit()(a1, a2, psi)
         self.attention.psi._emit(psi.unsqueeze(1))
@@ -85,4 +85,4 @@ class OutConv(KernelModule):
         return FinalConvUnit(sd, "conv.", dev)
 
     def forward(self, x):
-        return self._unit()(to_act(x))
+        return self._unit()(to_act(x, self.compute_dtype))

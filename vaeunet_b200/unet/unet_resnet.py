@@ -40,7 +40,7 @@ class AttentionGate(KernelModule):
     def forward(self, g, x):
         self._require_eval()
         unit = self._unit()
-        ga, xa = to_act(g), to_act(x)
+        ga, xa = to_act(g, self.compute_dtype), to_act(x, self.compute_dtype)
         out = ops.new_act(ga.N, xa.H, xa.W, xa.C, ga.dt, ga.t.device)
         psi = torch.empty((ga.N, xa.H, xa.W), dtype=torch.float32, device=ga.t.device)
         unit(ga, xa, out, psi)
@@ -94,11 +94,11 @@ class DecoderBlock(KernelModule):
     def forward(self, x, skip, z):
         self._require_eval()
         unit = self._unit()
-        xa = to_act(x)
-        sa = to_act(skip) if skip is not None else None
+        xa = to_act(x, self.compute_dtype)
+        sa = to_act(skip, self.compute_dtype) if skip is not None else None
         za = None
         if self.use_latent:
-            za = ConstVec(z.float().reshape(z.shape[0], z.shape[1]).contiguous()) if z.shape[2:] == (1, 1) else to_act(z)
+            za = ConstVec(z.float().reshape(z.shape[0], z.shape[1]).contiguous()) if z.shape[2:] == (1, 1) else to_act(z, self.compute_dtype)
         psi = None
         if self.use_attention and sa is not None:
             psi = torch.empty((xa.N, sa.H, sa.W), dtype=torch.float32, device=xa.t.device)
@@ -167,7 +167,7 @@ class _LatentHead(KernelModule, nn.Sequential):
 
     def forward(self, x_enc):
         u = self._unit()
-        a = to_act(x_enc)
+        a = to_act(x_enc, self.compute_dtype)
         mu, _, _ = ops.latent_head(a, u.w, u.b, u.w, u.b, None, 1.0, 0)
         return mu.unsqueeze(-1).unsqueeze(-1)
 
@@ -183,7 +183,7 @@ class _ZInitial(KernelModule, nn.Sequential):
 
     def forward(self, z_spatial):
         self._require_eval()
-        return from_act(self._unit()(to_act(z_spatial)))
+        return from_act(self._unit()(to_act(z_spatial, self.compute_dtype)))
 
 
 class _FinalConv(KernelModule, nn.Conv2d):
@@ -196,7 +196,7 @@ class _FinalConv(KernelModule, nn.Conv2d):
         return FinalConvUnit(sd, "", dev)
 
     def forward(self, x):
-        return self._unit()(to_act(x))
+        return self._unit()(to_act(x, self.compute_dtype))
 
 
 class UNetResNet(KernelModule):
