@@ -132,6 +132,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="patches per step per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layers", default=None, help="write a per-conv-shape timing table (csv) to this path")
     ap.add_argument("--dtype", default="f16", choices=["bf16", "f16"])
     args = ap.parse_args()
     if args.impl == "reference":
@@ -218,9 +219,21 @@ def main():
     barrier()
     ev = ops.CONV_TIMING
     ops.CONV_TIMING = None
-    conv_ms = sum(a.elapsed_time(b) for a, b, _ in ev)
-    conv_flop = sum(f for _, _, f in ev)
+    conv_ms = sum(a.elapsed_time(b) for a, b, *_ in ev)
+    conv_flop = sum(f for _, _, f, _ in ev)
     n_conv = len(ev)
+    if args.layers and rank == 0:
+        agg = {}
+        for a, b, f, desc in ev:
+            t = agg.setdefault(desc, [0, 0.0, 0.0])
+            t[0] += 1; t[1] += a.elapsed_time(b); t[2] += f
+        rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
+        with open(args.layers, "w") as fh:
+            fh.write(f"# per-layer conv timing over 2 steps, batch {B}, dtype {args.dtype} (CUDA events around each launch)\n")
+            fh.write(f"# total conv {conv_ms / 2:.3f} ms/step, {conv_flop / 2 / 1e9:.1f} GF/step\n")
+            fh.write("shape,launches,ms_total,ms_share,tflops\n")
+            for desc, (n, ms_l, fl) in rows:
+                fh.write(f"{desc},{n},{ms_l:.4f},{ms_l / conv_ms:.4f},{fl / (ms_l / 1e3) / 1e12:.1f}\n")
 
     patches = B * world * args.steps
     value = patches / (ms / 1e3)

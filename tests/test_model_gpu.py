@@ -154,7 +154,9 @@ def test_mc_predict(model, cuda_dev, B, S, N, T):
     for k in ("std", "mutual_info"):
         err = (res[k].cpu() - ref[k]).abs().max().item()
         print(f"mc {S} N={N} {k}: max abs err {err:.5f} (ref max {ref[k].abs().max().item():.4f}) rel {rel(res[k], ref[k]):.4f}")
-        assert err < 2e-2, k
+        assert err < (2e-2 if m.dt_name == "f16" else 5e-2), k
+        if m.dt_name == "f16":
+            assert rel(res[k], ref[k]) < tol, k
     assert rel(res["samples"].permute(1, 0, 2, 3), ref["samples"]) < tol
     assert mask_agree(res["mean"], ref["mean"], 0.5) >= 0.999
     assert ref["std"].max() > 1e-3            # the fixture really has sample-to-sample variation

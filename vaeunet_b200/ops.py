@@ -133,7 +133,8 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
         e0.record()
         check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
         e1.record()
-        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * k * k * x.C))
+        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * k * k * x.C,
+                            f"N{x.N} {x.H}x{x.W} Cin{x.C} Cout{Cout} k{k} s{stride}"))
     else:
         check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
     _count()
