@@ -1,0 +1,10 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
+mkdir -p gpurun_out; rm -f gpurun_out/trip11_perf.log
+for cfg in "16 256 256 224 64" "16 256 256 64 64" "16 128 128 352 128"; do
+  for ex in 0 3 4; do
+    echo "VU_HALO_EXP=$ex" >> gpurun_out/trip11_perf.log
+    VU_HALO_EXP=$ex timeout 120 python scripts/prof_conv.py $cfg 3 4 >> gpurun_out/trip11_perf.log 2>&1
+  done
+done
+cat gpurun_out/trip11_perf.log

@@ -22,6 +22,13 @@ CASES = [
     ("3x3_22x22", 2, 22, 22, 256, 256, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
     ("3x3_1024", 1, 32, 32, 1024, 1024, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
     ("3x3_big_persistent", 4, 128, 128, 64, 64, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    # smem tap-reuse kernel (vu_conv_halo.cu): Cout 64/128, W >= 96
+    ("halo_64_ht4", 2, 64, 128, 64, 64, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("halo_64_ht2", 3, 6, 128, 64, 64, 3, 1, False, False, (0, 0), (0, 0), "bf16"),
+    ("halo_partialK_224_w256", 1, 40, 256, 224, 64, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("halo_128_res", 2, 32, 128, 128, 128, 3, 1, True, True, (0, 0), (0, 0), "bf16"),
+    ("halo_odd_slices", 2, 35, 175, 96, 64, 3, 1, True, True, (32, 160), (64, 192), "f16"),
+    ("halo_352_128_w128", 1, 128, 128, 352, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
 ]
 
 

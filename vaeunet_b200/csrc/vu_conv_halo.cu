@@ -1,0 +1,335 @@
+// 3x3 s1 p1 convolution for small Cout (64 / 128) on wide maps — tcgen05 implicit GEMM with the
+// nine taps served from ONE shared-memory copy of the input tile.
+//
+// Why a second kernel: conv_igemm_kernel fetches a fresh 128-pixel x 64-channel A tile from L2 for
+// every tap, i.e. every input pixel crosses the L2->SM crossbar 9 times. With Cout = 64 an A element
+// feeds only 64 MACs, so that kernel is bound by L2->SM bandwidth (profiles/r1a_conv_224to64_256sq:
+// 8.5 TB/s, tensor pipe 15 %). Here a CTA owns an output tile of HT rows x 128 pixels; per 64-channel
+// K block it loads the (HT+2) x 130-pixel halo'd input tile ONCE (one 4-D TMA box, zero padding = TMA
+// out-of-bounds fill) and issues the MMAs of all nine taps from it: the A operand of tap (r,s) for
+// output row j is the same smem tile with the descriptor start address advanced by
+// ((j+r)*130 + s) * 128 bytes. Rows are 128 B (64 channels, SWIZZLE_128B); the swizzle is a function of
+// the absolute smem address, so a start address that is 128-byte- but not 1024-byte-aligned still
+// reads the rows TMA wrote. L2->SM traffic per MMA drops 3x (HT=2) to 5x (HT=4).
+//
+//   GEMM view per tile:  HT accumulators [128 pixels x BN], BN = Cout, K = 9 taps x Cin.
+//   Warps:  0 = A (input tile) TMA producer, 1 = TMEM allocator + MMA issuer, 2 = B (filter tap) TMA
+//           producer, 3..6 = epilogue (TMEM -> scale/bias/residual/ReLU -> 16-bit NHWC channel slice).
+//   Rings:  A: 2 stages of (HT+2)*130 rows; B: one [BN x 64ch] filter tap per stage; TMEM: 2 sets of HT
+//           accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "vu_conv_common.cuh"
+#include <cstdlib>
+
+namespace vu {
+
+constexpr int kHaloWT = 128;               // output pixels per tile row = UMMA M
+constexpr int kHaloPitch = kHaloWT + 2;    // input pixels per tile row (1-pixel halo each side)
+constexpr int kHaloThreads = 224;
+
+struct HaloParams {
+    int n_img, h, w;
+    int tiles_w, tiles_h, num_tiles;
+    int kblocks, last_ksteps;
+    const float* scale; const float* bias;
+    const uint16_t* residual; int res_ctot, res_coff;
+    uint16_t* y; int y_ctot, y_coff;
+    int relu, dtype;
+    int exp_mode;   // perf experiments only (VU_HALO_EXP): 1 = skip B loads after the first ring fill, 2 = same for A
+};
+
+template <int BN, int HT> struct HaloCfg {
+    static constexpr int kARows = (HT + 2) * kHaloPitch;
+    static constexpr int kABytes = kARows * 128;                       // what one TMA box delivers
+    static constexpr int kAStride = (kABytes + 1023) / 1024 * 1024;   // stage pitch (1024-aligned: swizzle atom)
+    static constexpr int kAStages = 2;
+    static constexpr int kBBytes = BN * 128;
+    static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
+    static constexpr int kTmemCols = 2 * HT * BN;
+    static constexpr int kBarBytes = 256;
+    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 2 * BN * 4;
+    static_assert(kTmemCols <= 512, "TMEM budget");
+    static_assert(kSmemBytes <= 232448, "smem budget");
+};
+
+template <int BN, int HT>
+__global__ void __launch_bounds__(kHaloThreads, 1)
+conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                    const HaloParams p) {
+    using Cfg = HaloCfg<BN, HT>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t a_base = smem_base;
+    const uint32_t b_base = smem_base + Cfg::kAStages * Cfg::kAStride;
+    constexpr int kBarOff = Cfg::kAStages * Cfg::kAStride + Cfg::kBStages * Cfg::kBBytes;
+    const uint32_t bar_base = smem_base + kBarOff;
+    auto a_full = [&](int s) { return bar_base + 8u * s; };
+    auto a_empty = [&](int s) { return bar_base + 8u * (Cfg::kAStages + s); };
+    auto b_full = [&](int s) { return bar_base + 8u * (2 * Cfg::kAStages + s); };
+    auto b_empty = [&](int s) { return bar_base + 8u * (2 * Cfg::kAStages + Cfg::kBStages + s); };
+    auto t_full = [&](int a) { return bar_base + 8u * (2 * Cfg::kAStages + 2 * Cfg::kBStages + a); };
+    auto t_empty = [&](int a) { return bar_base + 8u * (2 * Cfg::kAStages + 2 * Cfg::kBStages + 2 + a); };
+    constexpr int kSlotIdx = 2 * Cfg::kAStages + 2 * Cfg::kBStages + 4;
+    static_assert(8 * (kSlotIdx + 1) <= Cfg::kBarBytes, "barrier area");
+    const uint32_t tmem_slot = bar_base + 8u * kSlotIdx;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + kBarOff + 8 * kSlotIdx);
+    float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
+    float* s_bias = s_scale + BN;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_x);
+        tma_prefetch_desc(&map_w);
+        for (int s = 0; s < Cfg::kAStages; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
+        for (int s = 0; s < Cfg::kBStages; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(t_full(a), 1); mbar_init(t_empty(a), 128); }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+        tmem_relinquish();
+    }
+    for (int c = threadIdx.x; c < BN; c += kHaloThreads) {
+        s_scale[c] = p.scale ? p.scale[c] : 1.0f;
+        s_bias[c] = p.bias ? p.bias[c] : 0.0f;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===================== A producer: one halo'd input tile per (tile, K block) =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                const int wb = tile % p.tiles_w;
+                const int hb = (tile / p.tiles_w) % p.tiles_h;
+                const int nb = tile / (p.tiles_w * p.tiles_h);
+                for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+                    const int s = it % Cfg::kAStages;
+                    const uint32_t ph = (it / Cfg::kAStages) & 1;
+                    mbar_wait(a_empty(s), ph ^ 1);
+                    if (p.exp_mode == 2 && it >= (uint32_t)Cfg::kAStages) { mbar_arrive(a_full(s)); continue; }
+                    mbar_arrive_expect_tx(a_full(s), Cfg::kABytes);
+                    // one TMA op per tile row: several ops in flight fill the tile ~4x faster than one big box
+#pragma unroll
+                    for (int i = 0; i < HT + 2; ++i)
+                        tma_load_4d(a_base + s * Cfg::kAStride + i * (kHaloPitch * 128), &map_x, a_full(s), kb * 64,
+                                    wb * kHaloWT - 1, hb * HT - 1 + i, nb);
+                }
+            }
+        }
+    } else if (warp == 2) {
+        // ===================== B producer: one [BN x 64ch] filter tap per stage =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+                for (int kb = 0; kb < p.kblocks; ++kb) {
+                    for (int tap = 0; tap < 9; ++tap, ++it) {
+                        const int s = it % Cfg::kBStages;
+                        const uint32_t ph = (it / Cfg::kBStages) & 1;
+                        mbar_wait(b_empty(s), ph ^ 1);
+                        if (p.exp_mode == 1 && it >= (uint32_t)Cfg::kBStages) { mbar_arrive(b_full(s)); continue; }
+                        mbar_arrive_expect_tx(b_full(s), Cfg::kBBytes);
+                        tma_load_3d(b_base + s * Cfg::kBBytes, &map_w, b_full(s), kb * 64, tap, 0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
+        // (issuing under elect.sync instead of `lane == 0` lets ptxas emit bare UTCHMMA without a per-MMA
+        //  uniform-branch loop; the tap loop is unrolled so descriptor offsets are immediates)
+        const uint32_t idesc = umma_idesc_f16(128, BN, p.dtype == 0 ? 1u : 0u);
+        uint32_t ita = 0, itb = 0, tcount = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            const int acc = tcount & 1;
+            const uint32_t accph = (tcount >> 1) & 1;
+            mbar_wait(t_empty(acc), accph ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * (HT * BN);
+            for (int kb = 0; kb < p.kblocks; ++kb, ++ita) {
+                const int sa = ita % Cfg::kAStages;
+                mbar_wait(a_full(sa), (ita / Cfg::kAStages) & 1);
+                tc_fence_after();
+                const uint64_t a0 = umma_desc_k_sw128(a_base + sa * Cfg::kAStride);
+                const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : 4;
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap, ++itb) {
+                    const int sb = itb % Cfg::kBStages;
+                    mbar_wait(b_full(sb), (itb / Cfg::kBStages) & 1);
+                    tc_fence_after();
+                    const uint64_t bdesc = umma_desc_k_sw128(b_base + sb * Cfg::kBBytes);
+                    const int r = tap / 3, s = tap - 3 * r;
+                    if (elect_one()) {
+                        // k outer, rows inner: consecutive MMAs go to different accumulators. Tap (r,s) of output
+                        // row j = the same smem tile, start advanced by ((j+r)*130+s) pixel rows of 128 B (>>4 = *8).
+                        if (nk == 4) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                                for (int j = 0; j < HT; ++j)
+                                    umma_f16_ss(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
+                                                bdesc + 2u * k, idesc, (kb | tap | k) != 0);
+                        } else {
+                            for (int k = 0; k < nk; ++k)
+#pragma unroll
+                                for (int j = 0; j < HT; ++j)
+                                    umma_f16_ss(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
+                                                bdesc + 2u * k, idesc, (kb | tap | k) != 0);
+                        }
+                        umma_commit(b_empty(sb));
+                        if (tap == 8) umma_commit(a_empty(sa));
+                    }
+                    __syncwarp();
+                }
+            }
+            if (elect_one()) umma_commit(t_full(acc));
+            __syncwarp();
+        }
+    } else {
+        // ===================== epilogue: warps 3..6 cover the four TMEM lane quarters =====================
+        const int q = warp & 3;
+        const int m = q * 32 + lane;              // pixel within the tile row
+        uint32_t tcount = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            const int acc = tcount & 1;
+            const uint32_t accph = (tcount >> 1) & 1;
+            const int wb = tile % p.tiles_w;
+            const int hb = (tile / p.tiles_w) % p.tiles_h;
+            const int nb = tile / (p.tiles_w * p.tiles_h);
+            const int wo = wb * kHaloWT + m;
+            mbar_wait(t_full(acc), accph);
+            tc_fence_after();
+#pragma unroll 1
+            for (int j = 0; j < (p.exp_mode == 4 ? 0 : HT); ++j) {
+                const int ho = hb * HT + j;
+                const bool valid = (wo < p.w) && (ho < p.h);
+                const size_t pix = (static_cast<size_t>(nb) * p.h + ho) * p.w + wo;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (HT * BN) + j * BN;
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(taddr + c * 32, r);
+                    tmem_ld_wait();
+                    const int ch0 = c * 32;
+                    uint32_t outw[16];
+                    uint4 rv[4];
+                    if (p.residual != nullptr && valid) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.res_ctot + p.res_coff + ch0);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) rv[i] = __ldg(rp + i);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) rv[i] = make_uint4(0, 0, 0, 0);
+                    }
+                    const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float v0 = __uint_as_float(r[2 * i]) * s_scale[ch0 + 2 * i] + s_bias[ch0 + 2 * i];
+                        float v1 = __uint_as_float(r[2 * i + 1]) * s_scale[ch0 + 2 * i + 1] + s_bias[ch0 + 2 * i + 1];
+                        if (p.residual != nullptr) {
+                            float2 rr = unpack2(rw[i], p.dtype);
+                            v0 += rr.x; v1 += rr.y;
+                        }
+                        if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
+                        outw[i] = pack2(v0, v1, p.dtype);
+                    }
+                    if (valid && p.exp_mode != 3) {
+                        uint4* op = reinterpret_cast<uint4*>(p.y + pix * p.y_ctot + p.y_coff + ch0);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            op[i] = make_uint4(outw[4 * i], outw[4 * i + 1], outw[4 * i + 2], outw[4 * i + 3]);
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(t_empty(acc));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
+template <int BN, int HT>
+static int launch_halo(const CUtensorMap& xm, const CUtensorMap& wm, const HaloParams& hp, int max_ctas,
+                       cudaStream_t stream) {
+    using Cfg = HaloCfg<BN, HT>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::kSmemBytes);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(halo): %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    int grid = hp.num_tiles;
+    const int cap = (max_ctas > 0) ? max_ctas : num_sms();
+    if (grid > cap) grid = cap;
+    conv3x3_halo_kernel<BN, HT><<<grid, kHaloThreads, Cfg::kSmemBytes, stream>>>(xm, wm, hp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv3x3_halo launch: %s", cudaGetErrorString(e));
+    return 1;
+}
+
+int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
+    const int up = a->out_up > 0 ? a->out_up : 1;
+    if (!(a->KH == 3 && a->KW == 3 && a->stride == 1 && a->pad == 1 && up == 1)) return 0;
+    if (!(a->Cout == 64 || a->Cout == 128)) return 0;
+    static const int disabled = getenv("VU_NO_HALO") ? atoi(getenv("VU_NO_HALO")) : 0;
+    if (disabled) return 0;
+    if (a->W < 96) return 0;   // narrow maps: the 128-pixel tile row would be mostly padding
+    // rows per tile: 4 for Cout 64 (TMEM 2 x 4 x 64 columns) unless that pads the height noticeably more than 2
+    int ht = 2;
+    if (a->Cout == 64) {
+        const int pad4 = (a->H + 3) / 4 * 4, pad2 = (a->H + 1) / 2 * 2;
+        ht = (pad4 * 10 <= pad2 * 11) ? 4 : 2;
+        static const int force_ht = getenv("VU_HALO_HT") ? atoi(getenv("VU_HALO_HT")) : 0;
+        if (force_ht == 2 || force_ht == 4) ht = force_ht;
+    }
+    HaloParams hp{};
+    hp.n_img = a->N; hp.h = a->H; hp.w = a->W;
+    hp.tiles_w = (a->W + kHaloWT - 1) / kHaloWT;
+    hp.tiles_h = (a->H + ht - 1) / ht;
+    hp.num_tiles = hp.tiles_w * hp.tiles_h * a->N;
+    hp.kblocks = (a->Cin + 63) / 64;
+    hp.last_ksteps = ((a->Cin - (hp.kblocks - 1) * 64) + 15) / 16;
+    hp.scale = a->scale; hp.bias = a->bias;
+    hp.residual = static_cast<const uint16_t*>(a->residual); hp.res_ctot = a->res_ctot; hp.res_coff = a->res_coff;
+    hp.y = static_cast<uint16_t*>(a->y); hp.y_ctot = a->y_ctot; hp.y_coff = a->y_coff;
+    hp.relu = a->relu; hp.dtype = a->dtype;
+    static const int exp_mode = getenv("VU_HALO_EXP") ? atoi(getenv("VU_HALO_EXP")) : 0;
+    hp.exp_mode = exp_mode;
+
+    CUtensorMap xm, wm;
+    {
+        const uint16_t* xb = static_cast<const uint16_t*>(a->x) + a->x_coff;
+        const uint64_t pix = (uint64_t)a->x_ctot * 2;
+        const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * a->W, pix * a->W * a->H};
+        const uint32_t box[4] = {64u, (uint32_t)kHaloPitch, 1u, 1u};
+        int rc = encode_map(&xm, a->dtype, 4, xb, dims, str, box);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[3] = {(uint64_t)a->Cin, 9u, (uint64_t)a->Cout};
+        const uint64_t str[2] = {(uint64_t)a->Cin * 2, (uint64_t)a->Cin * 2 * 9};
+        const uint32_t wbox[3] = {64u, 1u, (uint32_t)a->Cout};
+        int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
+        if (rc) return rc;
+    }
+    if (a->Cout == 64) {
+        if (ht == 4) return launch_halo<64, 4>(xm, wm, hp, a->max_ctas, stream);
+        return launch_halo<64, 2>(xm, wm, hp, a->max_ctas, stream);
+    }
+    return launch_halo<128, 2>(xm, wm, hp, a->max_ctas, stream);
+}
+
+}  // namespace vu

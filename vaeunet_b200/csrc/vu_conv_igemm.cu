@@ -13,10 +13,7 @@
 //               warps 2..5 = epilogue (TMEM -> regs -> scale/bias/residual/ReLU -> 16-bit NHWC slice).
 //   Pipelines:  smem full/empty ring (kStages), TMEM full/empty (2 accumulators) so the epilogue of
 //               tile i overlaps the MMAs of tile i+1.
-#include "vu_ptx.cuh"
-#include "vu_internal.h"
-#include <cuda_bf16.h>
-#include <cuda_fp16.h>
+#include "vu_conv_common.cuh"
 
 namespace vu {
 
@@ -51,25 +48,6 @@ template <int BN> struct ConvCfg {
     static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes +
                                       2 * kMaxCout * 4;
 };
-
-__device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
-    if (dtype == 0) {
-        __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-        return *reinterpret_cast<uint32_t*>(&v);
-    } else {
-        __half2 v = __floats2half2_rn(a, b);
-        return *reinterpret_cast<uint32_t*>(&v);
-    }
-}
-__device__ __forceinline__ float2 unpack2(uint32_t u, int dtype) {
-    if (dtype == 0) {
-        __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
-        return __bfloat1622float2(v);
-    } else {
-        __half2 v = *reinterpret_cast<__half2*>(&u);
-        return __half22float2(v);
-    }
-}
 
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -147,33 +125,40 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (one lane) =====================
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_f16(kTileM, BN, p.dtype == 0 ? 1u : 0u);
-            uint32_t it = 0, tcount = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-                const int acc = tcount & 1;
-                const uint32_t accph = (tcount >> 1) & 1;
-                mbar_wait(tempty_bar(acc), accph ^ 1);
+        // ===================== MMA issuer: warp-uniform control flow, one elected lane issues =====
+        // (elect.sync instead of `lane == 0`: ptxas then emits bare UTCHMMA, no per-MMA uniform-branch loop)
+        const uint32_t idesc = umma_idesc_f16(kTileM, BN, p.dtype == 0 ? 1u : 0u);
+        uint32_t it = 0, tcount = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+            const int acc = tcount & 1;
+            const uint32_t accph = (tcount >> 1) & 1;
+            mbar_wait(tempty_bar(acc), accph ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * BN;
+            for (int ki = 0; ki < k_iters; ++ki, ++it) {
+                const int s = it % Cfg::kStages;
+                const uint32_t ph = (it / Cfg::kStages) & 1;
+                mbar_wait(full_bar(s), ph);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int ki = 0; ki < k_iters; ++ki, ++it) {
-                    const int s = it % Cfg::kStages;
-                    const uint32_t ph = (it / Cfg::kStages) & 1;
-                    mbar_wait(full_bar(s), ph);
-                    tc_fence_after();
-                    const uint32_t sa = smem_base + s * Cfg::kStageBytes;
-                    const uint64_t adesc = umma_desc_k_sw128(sa);
-                    const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
-                    const int kb = ki % p.kblocks;
-                    const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
-                    for (int k = 0; k < nk; ++k) {
-                        // +32 B per K=16 step inside the 128 B swizzle row (encoded >> 4)
-                        umma_f16_ss(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
+                const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                const uint64_t adesc = umma_desc_k_sw128(sa);
+                const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
+                const int kb = ki % p.kblocks;
+                const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
+                if (elect_one()) {
+                    // +32 B per K=16 step inside the 128 B swizzle row (encoded >> 4)
+                    if (nk == 4) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_f16_ss(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
+                    } else {
+                        for (int k = 0; k < nk; ++k)
+                            umma_f16_ss(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
                     }
                     umma_commit(empty_bar(s));
+                    if (ki == k_iters - 1) umma_commit(tfull_bar(acc));
                 }
-                umma_commit(tfull_bar(acc));
+                __syncwarp();
             }
         }
     } else {
@@ -252,38 +237,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                    CUtensorMapFloatOOBfill);
-
-static PFN_encodeTiled get_encode_fn() {
-    static PFN_encodeTiled fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* f = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<PFN_encodeTiled>(f);
-    }
-    return fn;
-}
-
-static int encode_map(CUtensorMap* m, int dtype, int rank, const void* base, const uint64_t* dims,
-                      const uint64_t* strides_bytes, const uint32_t* box) {
-    PFN_encodeTiled fn = get_encode_fn();
-    if (!fn) return set_error(VU_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
-    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-    CUresult r = fn(m, dtype == 0 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
-                    rank, const_cast<void*>(base), dims, strides_bytes, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return set_error(VU_ERR_CUDA, "cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
-    return 0;
-}
-
 static int pow2_ge(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 // choose (wt, ht, nt), product 128, maximising the fraction of useful rows
@@ -342,6 +295,10 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         return set_error(VU_ERR_ALIGN, "conv: pointers must be 16-byte aligned");
     if (a->N < 1 || a->H < 1 || a->W < 1) return set_error(VU_ERR_INVALID, "conv: empty input");
     const int up = a->out_up > 0 ? a->out_up : 1;
+    {   // small-Cout 3x3 on wide maps: the smem tap-reuse kernel (vu_conv_halo.cu)
+        const int rc = conv3x3_halo_launch(a, stream);
+        if (rc != 0) return rc < 0 ? rc : 0;
+    }
 
     const int Ho = (a->H + 2 * P - KH) / S + 1, Wo = (a->W + 2 * P - KW) / S + 1;
     ConvKParams kp{};
