@@ -113,6 +113,18 @@ int vu_attention_gate(const void* g1, int g1_ctot, int g1_coff, const void* x1, 
                       float* psi, int Ng, int rep, int H, int W, int F, int Cl, int dtype,
                       vu_stream_t stream);
 
+/* The whole concat buffer of a DecoderBlock in one pass (unet/unet_resnet.py:71-98):
+ *   out[d,ho,wo,:] = [ bilinear_ac(x_low) | skip * sigmoid(psi_scale*<psi_w, relu(bilinear_ac(g1_low)+x1)> + psi_bias) | zvec[d,:] ]
+ * g1_low = BN(W_g x_low) is taken at the LOW resolution of x_low (a 1x1 conv + affine commutes with bilinear
+ * interpolation, whose weights sum to 1) and interpolated on the fly; a spatially constant x is a 1x1 map.
+ * x_low [D,hs,ws,Cx], g1_low [D,hs,ws,F], x1 [D/rep,H,W,F], skip [D/rep,H,W,Cs] 16-bit NHWC slices; zvec fp32 [D,Cz]
+ * or NULL (Cz = 0); out [D,H,W,out_ctot] receives channels [0, Cx+Cs+Cz); psi_out fp32 [D,H,W] or NULL. */
+int vu_decoder_concat(const void* x_low, int hs, int ws, int Cx, int x_ctot, int x_coff, const void* g1_low,
+                      int g1_ctot, int g1_coff, const void* x1, int x1_ctot, int x1_coff, const void* skip,
+                      int skip_ctot, int skip_coff, int F, int Cs, const float* psi_w, float psi_scale,
+                      float psi_bias, const float* zvec, int Cz, void* out, int out_ctot, float* psi_out,
+                      int D, int rep, int H, int W, int dtype, vu_stream_t stream);
+
 /* ---------------------------------------------------------------- latent head
  * mu/logvar = GAP(conv1x1(f4) + b) = W * mean_hw(f4) + b (unet/unet_resnet.py:140-147,205-206;
  * utils/vae_utils.py:13-25), then for every MC sample n: z[n,b,:] = mu + eps[n,b,:]*exp(.5 logvar)*T

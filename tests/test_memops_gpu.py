@@ -113,6 +113,47 @@ def test_attention_gate(cuda_dev, F_, Cl, rep):
     assert (_from_act(out) - ref).abs().max() <= 8e-3 * ref.abs().max()
 
 
+@pytest.mark.parametrize("hs,ws,H,W,Cx,Cs,F_,Cz,rep", [(8, 8, 16, 16, 128, 64, 32, 32, 2), (11, 9, 22, 17, 64, 128, 64, 0, 1),
+                                                        (1, 1, 6, 5, 256, 64, 128, 32, 3), (5, 7, 10, 14, 24, 8, 8, 8, 1)])
+@pytest.mark.parametrize("dt", ["bf16", "f16"])
+def test_decoder_concat(cuda_dev, hs, ws, H, W, Cx, Cs, F_, Cz, rep, dt):
+    """Fused concat producer vs. the reference order of operations (unet/unet_resnet.py:79-98): upsample x to the
+    skip size, g1 = affine(W_g(x_up)) at OUTPUT resolution, gate, concat [x_up | skip*psi | z]."""
+    from vaeunet_b200 import ops
+    g = torch.Generator().manual_seed(31)
+    tdt = torch.bfloat16 if dt == "bf16" else torch.float16
+    odt = ops.BF16 if dt == "bf16" else ops.F16
+    _q = lambda t: t.to(tdt).float()                                                   # noqa: E731
+    _to_act = lambda o, t, dv: o.Act(t.permute(0, 2, 3, 1).contiguous().to(tdt).to(dv))  # noqa: E731
+    Dp = 2
+    D = Dp * rep
+    x = _q(torch.randn(D, Cx, hs, ws, generator=g))
+    wg = torch.randn(F_, Cx, 1, 1, generator=g) * (1.0 / Cx ** 0.5)
+    bg = torch.randn(F_, generator=g) * 0.1
+    g1_low = _q(F.conv2d(x, wg, bg))                      # what the tensor-core conv stores at low resolution
+    x1 = _q(torch.randn(Dp, F_, H, W, generator=g))
+    skip = _q(torch.randn(Dp, Cs, H, W, generator=g))
+    pw = torch.randn(F_, generator=g) * 0.2
+    ps, pb = 0.8, 0.05
+    zv = torch.randn(D, Cz, generator=g) if Cz else None
+    x_up = F.interpolate(x, size=(H, W), mode="bilinear", align_corners=True)
+    g1_ref = F.conv2d(x_up, wg, bg)                       # reference order: conv after the upsample
+    psi = torch.sigmoid(ps * (F.relu(g1_ref + x1.repeat_interleave(rep, 0)) * pw.view(1, -1, 1, 1)).sum(1, keepdim=True) + pb)
+    parts = [x_up, skip.repeat_interleave(rep, 0) * psi]
+    if Cz:
+        parts.append(zv.view(D, Cz, 1, 1).expand(D, Cz, H, W))
+    ref = torch.cat(parts, 1)
+    d = cuda_dev
+    out = ops.new_act(D, H, W, Cx + Cs + Cz, odt)
+    psi_out = torch.empty(D, H, W, device=d)
+    ops.decoder_concat(_to_act(ops, x, d), _to_act(ops, g1_low, d), _to_act(ops, x1, d), _to_act(ops, skip, d),
+                       pw.to(d), ps, pb, zv.to(d) if Cz else None, out, psi_out)
+    assert (psi_out.cpu() - psi[:, 0]).abs().max() < 5e-3          # g1 stored in bf16 at low resolution
+    got = _from_act(out)
+    assert (got[:, :Cx] - x_up).abs().max() <= 8e-3 * x_up.abs().max()
+    assert (got - ref).abs().max() <= 1.2e-2 * ref.abs().max()
+
+
 def test_latent_head_and_project(cuda_dev):
     from vaeunet_b200 import ops
     g = torch.Generator().manual_seed(4)

@@ -48,6 +48,7 @@ SIGNATURES = {
     "vu_bilinear_ac_nhwc": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_broadcast_vec_nhwc": [p, p, i, i, i, i, i, i, i, p],
     "vu_attention_gate": [p, i, i, p, i, i, p, i, i, p, f, f, p, i, i, p, i, i, i, i, i, i, i, p],
+    "vu_decoder_concat": [p, i, i, i, i, i, p, i, i, p, i, i, p, i, i, i, i, p, f, f, p, i, p, i, p, i, i, i, i, i, p],
     "vu_latent_head": [p, i, i, i, i, i, i, p, p, p, p, p, f, i, i, p, p, p, i, p],
     "vu_reparameterize": [p, p, p, f, p, sz, i, p],
     "vu_latent_project": [p, p, p, p, p, i, i, i, i, p],

@@ -208,6 +208,20 @@ class DecoderBlockUnit:
         cs = skip.C if has_skip else 0
         cz = L if self.zproj is not None else 0
         cat = ops.new_act(D, H, W, cx + cs + cz, self.dtype, self.dev)
+        if has_skip and self.gate is not None and psi_out is None and (cz == 0 or isinstance(z, ConstVec)):
+            # fused producer: W_g runs at the LOW resolution of x, everything else is one pass over `cat`
+            gt = self.gate
+            if isinstance(x, ConstVec):
+                x_low = ops.broadcast_vec(x.v, ops.new_act(D, 1, 1, cx, self.dtype, self.dev))
+                g1_low = ops.broadcast_vec(gt.wg_vec(x.v, relu=False), ops.new_act(D, 1, 1, gt.fint, self.dtype, self.dev))
+            else:
+                x_low = x
+                g1_low = gt.wg(x, relu=False)
+            x1 = gt.wx(skip, relu=False)
+            zv = self.zproj(z.v, relu=True) if cz else None
+            ops.decoder_concat(x_low, g1_low, x1, skip, gt.psi_w, gt.psi_scale, gt.psi_bias, zv, cat)
+            y = self.conv1(cat, relu=True)
+            return self.conv2(y, relu=True)
         xs = cat.slice(0, cx)
         if isinstance(x, ConstVec):
             ops.broadcast_vec(x.v, xs)

@@ -242,6 +242,30 @@ def attention_gate(g1: Act, x1: Act, skip: Act, psi_w: torch.Tensor, psi_scale: 
     return out
 
 
+def decoder_concat(x_low: Act, g1_low: Act, x1: Act, skip: Act, psi_w: torch.Tensor, psi_scale: float, psi_bias: float,
+                   zvec: Optional[torch.Tensor], out: Act, psi_out: Optional[torch.Tensor] = None) -> Act:
+    """out[D,H,W,:] = [bilinear_ac(x_low) | skip * psi | zvec] with psi from bilinear_ac(g1_low) + x1 (one pass)."""
+    require_device()
+    D, H, W = out.N, out.H, out.W
+    Dp = skip.N
+    assert D % Dp == 0 and x1.N == Dp and x_low.N == D and g1_low.N == D and out.coff == 0
+    assert (x_low.H, x_low.W) == (g1_low.H, g1_low.W) and (skip.H, skip.W) == (x1.H, x1.W) == (H, W)
+    assert g1_low.C == x1.C == psi_w.numel()
+    cz = 0
+    if zvec is not None:
+        zvec = _f32(zvec)
+        assert zvec.shape[0] == D
+        cz = zvec.shape[1]
+    assert x_low.C + skip.C + cz == out.C, (x_low.C, skip.C, cz, out.C)
+    check(load().vu_decoder_concat(x_low.t.data_ptr(), x_low.H, x_low.W, x_low.C, x_low.ctot, x_low.coff,
+                                   g1_low.t.data_ptr(), g1_low.ctot, g1_low.coff, x1.t.data_ptr(), x1.ctot, x1.coff,
+                                   skip.t.data_ptr(), skip.ctot, skip.coff, g1_low.C, skip.C, _f32(psi_w).data_ptr(),
+                                   float(psi_scale), float(psi_bias), _ptr(zvec), cz, out.t.data_ptr(), out.ctot,
+                                   _ptr(psi_out), D, D // Dp, H, W, out.dt, _stream()), "vu_decoder_concat")
+    _count()
+    return out
+
+
 def latent_head(f4: Act, w_mu, b_mu, w_lv, b_lv, eps: Optional[torch.Tensor], temperature: float, Ns: int):
     """-> mu [B,L], logvar [B,L], z [Ns,B,L] (fp32)."""
     require_device()
