@@ -62,6 +62,11 @@ typedef struct vu_conv_args {
     int out_up, out_dh, out_dw;  /* 1,0,0 for ordinary convs */
     int dtype;                   /* vu_dtype */
     int max_ctas;                /* 0 = one persistent CTA per SM */
+    /* Optional fused output conv (final_conv unet_resnet.py:189,237 / OutConv unet_parts.py:97-103, n_classes = 1):
+     * fuse_out[n,ho,wo] = fuse_bias + sum_co fuse_w[co] * act(...)[co] in fp32, taken before the 16-bit rounding of
+     * y. Only for 3x3 s1 p1 convs with Cout in {64,128} on maps at least 96 wide (the smem tap-reuse kernel);
+     * y may then be NULL (activation not materialised). NULL = off. */
+    const float* fuse_w; float fuse_bias; float* fuse_out;
 } vu_conv_args;
 int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 

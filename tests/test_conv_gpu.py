@@ -95,3 +95,43 @@ def test_convT2x2_pixel_shuffle(cuda_dev):
     torch.cuda.synchronize()
     got = out.t.float().cpu().permute(0, 3, 1, 2)
     assert (got - ref).abs().max().item() <= 2e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("Cout,store", [(64, False), (64, True), (128, True)])
+def test_conv_fused_output_conv(cuda_dev, Cout, store):
+    """vu_conv_args.fuse_out: conv3x3 + BN + ReLU with the 1x1 Cout->1 output conv (final_conv) in the epilogue."""
+    from vaeunet_b200 import ops
+    g = torch.Generator().manual_seed(77)
+    N, H, W, Cin = 2, 10, 130, 64
+    x = torch.randn(N, Cin, H, W, generator=g)
+    w = torch.randn(Cout, Cin, 3, 3, generator=g) * (1.0 / (Cin * 9) ** 0.5)
+    scale = torch.rand(Cout, generator=g) + 0.5
+    bias = torch.randn(Cout, generator=g) * 0.1
+    fw = torch.randn(Cout, generator=g) * 0.2
+    fb = 0.3
+    xq, wq = x.half().float(), w.half().float()
+    act = F.relu(F.conv2d(xq, wq, None, 1, 1) * scale.view(1, -1, 1, 1) + bias.view(1, -1, 1, 1))
+    ref = (act * fw.view(1, -1, 1, 1)).sum(1) + fb
+    dev = cuda_dev
+    xa = ops.Act(xq.permute(0, 2, 3, 1).contiguous().half().to(dev))
+    wp = ops.pack_conv_weight(w.to(dev), ops.F16)
+    logits = torch.full((N, H, W), -9.0, device=dev)
+    y = ops.conv2d(xa, wp, 3, 1, 1, scale.to(dev), bias.to(dev), True, fuse_w=fw.to(dev), fuse_bias=fb,
+                   fuse_out=logits, store=store)
+    torch.cuda.synchronize()
+    assert (logits.cpu() - ref).abs().max().item() <= 5e-3 * ref.abs().max().item()
+    if store:
+        got = y.t.float().cpu().permute(0, 3, 1, 2)
+        assert (got - act).abs().max().item() <= 2e-3 * act.abs().max().item() + 1e-3
+    else:
+        assert y is None
+
+
+def test_conv_fused_output_rejected_off_path(cuda_dev):
+    from vaeunet_b200 import ops
+    from vaeunet_b200._lib import VaeUnetError
+    dev = cuda_dev
+    xa = ops.Act(torch.zeros(1, 8, 8, 64, dtype=torch.float16, device=dev))      # too narrow for the tap-reuse kernel
+    wp = ops.pack_conv_weight(torch.zeros(64, 64, 3, 3, device=dev), ops.F16)
+    with pytest.raises(VaeUnetError):
+        ops.conv2d(xa, wp, 3, 1, 1, None, None, True, fuse_w=torch.zeros(64, device=dev), fuse_out=torch.zeros(1, 8, 8, device=dev))

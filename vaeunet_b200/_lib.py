@@ -29,6 +29,7 @@ class ConvArgs(C.Structure):
         ("y", C.c_void_p), ("y_ctot", C.c_int), ("y_coff", C.c_int),
         ("out_up", C.c_int), ("out_dh", C.c_int), ("out_dw", C.c_int),
         ("dtype", C.c_int), ("max_ctas", C.c_int),
+        ("fuse_w", C.c_void_p), ("fuse_bias", C.c_float), ("fuse_out", C.c_void_p),
     ]
 
 

@@ -34,7 +34,7 @@ struct HaloParams {
     const uint16_t* residual; int res_ctot, res_coff;
     uint16_t* y; int y_ctot, y_coff;
     int relu, dtype;
-    int exp_mode;   // perf experiments only (VU_HALO_EXP): 1 = skip B loads after the first ring fill, 2 = same for A
+    const float* fuse_w; float fuse_bias; float* fuse_out;   // optional fused 1x1 Cout->1 output conv (fp32 [N,H,W])
 };
 
 template <int BN, int HT> struct HaloCfg {
@@ -46,7 +46,7 @@ template <int BN, int HT> struct HaloCfg {
     static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 2 * BN * 4;
+    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4;
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 232448, "smem budget");
 };
@@ -75,6 +75,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_al + kBarOff + 8 * kSlotIdx);
     float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
     float* s_bias = s_scale + BN;
+    float* s_fw = s_bias + BN;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -94,6 +95,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     for (int c = threadIdx.x; c < BN; c += kHaloThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
+        s_fw[c] = p.fuse_w ? p.fuse_w[c] : 0.0f;
     }
     tc_fence_before();
     __syncthreads();
@@ -112,7 +114,6 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     const int s = it % Cfg::kAStages;
                     const uint32_t ph = (it / Cfg::kAStages) & 1;
                     mbar_wait(a_empty(s), ph ^ 1);
-                    if (p.exp_mode == 2 && it >= (uint32_t)Cfg::kAStages) { mbar_arrive(a_full(s)); continue; }
                     mbar_arrive_expect_tx(a_full(s), Cfg::kABytes);
                     // one TMA op per tile row: several ops in flight fill the tile ~4x faster than one big box
 #pragma unroll
@@ -132,7 +133,6 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         const int s = it % Cfg::kBStages;
                         const uint32_t ph = (it / Cfg::kBStages) & 1;
                         mbar_wait(b_empty(s), ph ^ 1);
-                        if (p.exp_mode == 1 && it >= (uint32_t)Cfg::kBStages) { mbar_arrive(b_full(s)); continue; }
                         mbar_arrive_expect_tx(b_full(s), Cfg::kBBytes);
                         tma_load_3d(b_base + s * Cfg::kBBytes, &map_w, b_full(s), kb * 64, tap, 0);
                     }
@@ -194,6 +194,9 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // ===================== epilogue: warps 3..6 cover the four TMEM lane quarters =====================
         const int q = warp & 3;
         const int m = q * 32 + lane;              // pixel within the tile row
+        const bool has_res = p.residual != nullptr, relu = p.relu != 0, store_y = p.y != nullptr;
+        const bool fuse = p.fuse_out != nullptr;  // 1x1 Cout->1 output conv on the fp32 activations (final_conv)
+        const int dtype = p.dtype;
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
             const int acc = tcount & 1;
@@ -205,20 +208,19 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_wait(t_full(acc), accph);
             tc_fence_after();
 #pragma unroll 1
-            for (int j = 0; j < (p.exp_mode == 4 ? 0 : HT); ++j) {
+            for (int j = 0; j < HT; ++j) {
                 const int ho = hb * HT + j;
                 const bool valid = (wo < p.w) && (ho < p.h);
                 const size_t pix = (static_cast<size_t>(nb) * p.h + ho) * p.w + wo;
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * (HT * BN) + j * BN;
+                float dot = 0.0f;
 #pragma unroll 1
                 for (int c = 0; c < BN / 32; ++c) {
                     uint32_t r[32];
                     tmem_ld_32x32b_x32(taddr + c * 32, r);
-                    tmem_ld_wait();
                     const int ch0 = c * 32;
-                    uint32_t outw[16];
                     uint4 rv[4];
-                    if (p.residual != nullptr && valid) {
+                    if (has_res && valid) {
                         const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.res_ctot + p.res_coff + ch0);
 #pragma unroll
                         for (int i = 0; i < 4; ++i) rv[i] = __ldg(rp + i);
@@ -226,25 +228,42 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                         for (int i = 0; i < 4; ++i) rv[i] = make_uint4(0, 0, 0, 0);
                     }
+                    tmem_ld_wait();
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+                    float v[32];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        float v0 = __uint_as_float(r[2 * i]) * s_scale[ch0 + 2 * i] + s_bias[ch0 + 2 * i];
-                        float v1 = __uint_as_float(r[2 * i + 1]) * s_scale[ch0 + 2 * i + 1] + s_bias[ch0 + 2 * i + 1];
-                        if (p.residual != nullptr) {
-                            float2 rr = unpack2(rw[i], p.dtype);
-                            v0 += rr.x; v1 += rr.y;
+                    for (int i = 0; i < 32; ++i) v[i] = fmaf(__uint_as_float(r[i]), s_scale[ch0 + i], s_bias[ch0 + i]);
+                    if (has_res) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float2 rr = unpack2(rw[i], dtype);
+                            v[2 * i] += rr.x; v[2 * i + 1] += rr.y;
                         }
-                        if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
-                        outw[i] = pack2(v0, v1, p.dtype);
                     }
-                    if (valid && p.exp_mode != 3) {
+                    if (relu) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.0f);
+                    }
+                    if (fuse) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) dot = fmaf(v[i], s_fw[ch0 + i], dot);
+                    }
+                    if (valid && store_y) {
+                        uint32_t outw[16];
+                        if (dtype == 0) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) outw[i] = pack2(v[2 * i], v[2 * i + 1], 0);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) outw[i] = pack2(v[2 * i], v[2 * i + 1], 1);
+                        }
                         uint4* op = reinterpret_cast<uint4*>(p.y + pix * p.y_ctot + p.y_coff + ch0);
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
                             op[i] = make_uint4(outw[4 * i], outw[4 * i + 1], outw[4 * i + 2], outw[4 * i + 3]);
                     }
                 }
+                if (fuse && valid) p.fuse_out[pix] = dot + p.fuse_bias;
             }
             tc_fence_before();
             mbar_arrive(t_empty(acc));
@@ -303,10 +322,10 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     hp.last_ksteps = ((a->Cin - (hp.kblocks - 1) * 64) + 15) / 16;
     hp.scale = a->scale; hp.bias = a->bias;
     hp.residual = static_cast<const uint16_t*>(a->residual); hp.res_ctot = a->res_ctot; hp.res_coff = a->res_coff;
+    if (a->fuse_out && !a->fuse_w) return set_error(VU_ERR_INVALID, "conv: fuse_out without fuse_w");
     hp.y = static_cast<uint16_t*>(a->y); hp.y_ctot = a->y_ctot; hp.y_coff = a->y_coff;
     hp.relu = a->relu; hp.dtype = a->dtype;
-    static const int exp_mode = getenv("VU_HALO_EXP") ? atoi(getenv("VU_HALO_EXP")) : 0;
-    hp.exp_mode = exp_mode;
+    hp.fuse_w = a->fuse_w; hp.fuse_bias = a->fuse_bias; hp.fuse_out = a->fuse_out;
 
     CUtensorMap xm, wm;
     {

@@ -281,7 +281,7 @@ using namespace vu;
 
 extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (!a || !a->x || !a->w || !a->y) return set_error(VU_ERR_INVALID, "conv: null pointer");
+    if (!a || !a->x || !a->w || (!a->y && !a->fuse_out)) return set_error(VU_ERR_INVALID, "conv: null pointer");
     const int KH = a->KH, KW = a->KW, S = a->stride, P = a->pad;
     const bool ok_geom = (KH == KW) && ((KH == 3 && P == 1) || (KH == 1 && P == 0)) && (S == 1 || S == 2);
     if (!ok_geom) return set_error(VU_ERR_UNSUPPORTED, "conv: only 3x3 p1 / 1x1 p0, stride 1|2 (got k%d s%d p%d)", KH, S, P);
@@ -299,6 +299,8 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         const int rc = conv3x3_halo_launch(a, stream);
         if (rc != 0) return rc < 0 ? rc : 0;
     }
+    if (a->fuse_out || !a->y)
+        return set_error(VU_ERR_UNSUPPORTED, "conv: fused output conv needs 3x3 s1 p1, Cout 64/128, W >= 96");
 
     const int Ho = (a->H + 2 * P - KH) / S + 1, Wo = (a->W + 2 * P - KW) / S + 1;
     ConvKParams kp{};
@@ -317,11 +319,13 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     kp.out_h = Ho * up; kp.out_w = Wo * up;
     kp.relu = a->relu; kp.dtype = a->dtype;
 
-    // BN tile: largest of 256/128/64/32 dividing Cout that still yields >= ~1 wave of tiles
+    // BN tile: largest of 256/128/64/32 dividing Cout
     int bn = 256;
     while (bn > 32 && (a->Cout % bn)) bn >>= 1;
     const int sms = num_sms();
-    while (bn > 64 && (long)kp.num_m_tiles * (a->Cout / bn) < sms) bn >>= 1;
+    // a k-iteration costs about the same for every BN (it is L2->SM bound), so prefer wide tiles; only drop
+    // from 256 to 128 columns when that is needed to reach one wave of tiles
+    while (bn > 128 && (long)kp.num_m_tiles * (a->Cout / bn) < sms) bn >>= 1;
     kp.num_n_tiles = a->Cout / bn;
 
     // activation tensor maps

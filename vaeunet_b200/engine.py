@@ -71,9 +71,13 @@ class ConvUnit:
             self.scale = None
             self.bias = cb.detach().to(dev, torch.float32).contiguous() if cb is not None else None
 
-    def __call__(self, x: Act, relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None) -> Act:
+    def __call__(self, x: Act, relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None, **kw) -> Act:
         return ops.conv2d(x, self.w, self.k, self.stride, self.pad, self.scale, self.bias, relu, out=out,
-                          residual=residual)
+                          residual=residual, **kw)
+
+    def can_fuse_output(self, x: Act) -> bool:
+        """vu_conv_args.fuse_out: 3x3 s1 p1, Cout 64/128, map at least 96 wide."""
+        return self.k == 3 and self.stride == 1 and self.cout in (64, 128) and x.W >= 96
 
 
 class VecUnit:
@@ -193,7 +197,9 @@ class DecoderBlockUnit:
         self.zproj = VecUnit(sd, p + "z_proj.0.", p + "z_proj.1.", dev) if use_latent else None
         self.zproj_conv = None
 
-    def __call__(self, x: Union[Act, ConstVec], skip: Optional[Act], z: Union[ConstVec, Act, None], psi_out=None) -> Act:
+    def __call__(self, x: Union[Act, ConstVec], skip: Optional[Act], z: Union[ConstVec, Act, None], psi_out=None,
+                 final: Optional["FinalConvUnit"] = None):
+        """-> Act, or (with `final`, n_classes == 1) the fp32 logits [D,1,H,W] of final(conv2(...)) from the fused epilogue."""
         L = self.L
         if isinstance(x, ConstVec):
             D, cx = x.v.shape
@@ -220,8 +226,7 @@ class DecoderBlockUnit:
             x1 = gt.wx(skip, relu=False)
             zv = self.zproj(z.v, relu=True) if cz else None
             ops.decoder_concat(x_low, g1_low, x1, skip, gt.psi_w, gt.psi_scale, gt.psi_bias, zv, cat)
-            y = self.conv1(cat, relu=True)
-            return self.conv2(y, relu=True)
+            return self._convs(cat, final)
         xs = cat.slice(0, cx)
         if isinstance(x, ConstVec):
             ops.broadcast_vec(x.v, xs)
@@ -247,8 +252,16 @@ class DecoderBlockUnit:
                     self.zproj_conv = ConvUnit(self.sd, self.prefix + "z_proj.0.", self.prefix + "z_proj.1.", 1, 1, 0,
                                                self.dev, self.dtype)
                 self.zproj_conv(zu, relu=True, out=zs)
+        return self._convs(cat, final)
+
+    def _convs(self, cat: Act, final):
         y = self.conv1(cat, relu=True)
-        return self.conv2(y, relu=True)
+        if final is not None and final.n_classes == 1 and self.conv2.can_fuse_output(y):
+            logits = torch.empty((y.N, 1, y.H, y.W), dtype=torch.float32, device=self.dev)
+            self.conv2(y, relu=True, fuse_w=final.w[0], fuse_bias=final.b[0], fuse_out=logits, store=False)
+            return logits
+        x = self.conv2(y, relu=True)
+        return x if final is None else final(x)
 
 
 class FinalConvUnit:
@@ -305,8 +318,8 @@ class ResNetVAEEngine:
         for i in range(4):
             want = self.use_skip if honour_use_skip else True
             skip = feats[-(i + 2)] if want else None
-            x = self.dec[i](x, skip, z)
-        return self.final(x)
+            x = self.dec[i](x, skip, z, final=self.final if i == 3 else None)
+        return x
 
     # ------------------------------------------------------------------ end-to-end entry points
     def forward(self, images: torch.Tensor, eps: Optional[torch.Tensor] = None):

@@ -106,15 +106,21 @@ def pack_convT2x2_weight(w: torch.Tensor, dtype=BF16) -> torch.Tensor:
 # ------------------------------------------------------------------ conv
 def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale: Optional[torch.Tensor],
            bias: Optional[torch.Tensor], relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None,
-           out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0) -> Act:
+           out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0,
+           fuse_w: Optional[torch.Tensor] = None, fuse_bias: float = 0.0, fuse_out: Optional[torch.Tensor] = None,
+           store: bool = True) -> Optional[Act]:
+    """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y."""
     require_device()
     Cout = w_packed.shape[0]
     assert w_packed.shape[1] == k * k and w_packed.shape[2] == x.C, (tuple(w_packed.shape), k, x.C)
     Ho = (x.H + 2 * pad - k) // stride + 1
     Wo = (x.W + 2 * pad - k) // stride + 1
-    if out is None:
-        out = new_act(x.N, Ho * out_up, Wo * out_up, Cout, x.dt, x.t.device)
-    assert out.C == Cout and out.N == x.N and out.H == Ho * out_up and out.W == Wo * out_up, "conv output shape"
+    if not store:
+        assert fuse_out is not None and out is None
+    else:
+        if out is None:
+            out = new_act(x.N, Ho * out_up, Wo * out_up, Cout, x.dt, x.t.device)
+        assert out.C == Cout and out.N == x.N and out.H == Ho * out_up and out.W == Wo * out_up, "conv output shape"
     a = ConvArgs()
     a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
     a.w = w_packed.data_ptr(); a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad
@@ -125,7 +131,15 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
     else:
         a.residual = None
     a.relu = int(relu)
-    a.y = out.t.data_ptr(); a.y_ctot = out.ctot; a.y_coff = out.coff
+    if store:
+        a.y = out.t.data_ptr(); a.y_ctot = out.ctot; a.y_coff = out.coff
+    else:
+        a.y = None; a.y_ctot = Cout; a.y_coff = 0
+    if fuse_out is not None:
+        assert fuse_out.dtype == torch.float32 and fuse_out.is_contiguous() and fuse_out.numel() == x.N * Ho * Wo
+        a.fuse_w = _f32(fuse_w).data_ptr(); a.fuse_bias = float(fuse_bias); a.fuse_out = fuse_out.data_ptr()
+    else:
+        a.fuse_w = None; a.fuse_bias = 0.0; a.fuse_out = None
     a.out_up = out_up; a.out_dh = out_dh; a.out_dw = out_dw
     a.dtype = x.dt; a.max_ctas = max_ctas
     if CONV_TIMING is not None:
