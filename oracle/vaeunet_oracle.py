@@ -697,3 +697,36 @@ def unet_forward(sd: SD, x: Tensor, bilinear: bool = False, st: Optional[BNState
     for k in range(1, 5):
         y = unet_up(sd, f"up{k}.", y, xs[4 - k], bilinear, st)
     return _conv(sd, "outc.conv.", y, fp32=True)
+
+
+# --------------------------------------------------------------------------------------
+# sample-sharded moments (multi-GPU merge; CPU restatement of vu_moments_partial / vu_moments_finalize,
+# which themselves restate calculate_uncertainty_metrics, visualize_vae.py:90-117, in mergeable form)
+# --------------------------------------------------------------------------------------
+def _bin_entropy(p: Tensor) -> Tensor:
+    eps = 1e-7
+    return -(p * torch.log(p + eps) + (1 - p) * torch.log(1 - p + eps))
+
+
+def moments_partial(probs: Tensor) -> Tuple[Tensor, Tensor, Tensor]:
+    """probs [n, ...] -> (mean, M2 = sum (p - mean)^2, sum of per-sample entropies) of this shard."""
+    mean = probs.mean(0)
+    return mean, ((probs - mean) ** 2).sum(0), _bin_entropy(probs).sum(0)
+
+
+def moments_finalize(counts: Sequence[float], mean: Tensor, m2: Tensor, sh: Tensor) -> Dict[str, Tensor]:
+    """Chan et al. pairwise merge of shard moments [S, ...] -> the five maps of calculate_uncertainty_metrics."""
+    n = 0.0
+    m = torch.zeros_like(mean[0]); M2 = torch.zeros_like(mean[0]); H = torch.zeros_like(mean[0])
+    for k, nb in enumerate(counts):
+        if nb <= 0:
+            continue
+        nn = n + nb
+        d = mean[k] - m
+        m = m + d * (nb / nn)
+        M2 = M2 + m2[k] + d * d * (n * nb / nn)
+        H = H + sh[k]
+        n = nn
+    std = torch.sqrt((M2 / (n - 1)).clamp_min(0)) if n > 1 else torch.full_like(m, float("nan"))
+    ent = _bin_entropy(m)
+    return {"mean": m, "std": std, "entropy": ent, "mutual_info": ent - H / n, "coeff_var": std / (m + 1e-7)}

@@ -1,0 +1,80 @@
+"""Multi-GPU parity of the sharded MC paths over NCCL (run under torchrun on N GPUs of one box):
+  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 scripts/dist_parity.py
+Checks, on every rank, sample-sharded MC (BASELINE config 4 shape: 700x700, T=2.0, N=15) and the tiled
+full-image path (config 5 logic on a reduced 1100x1400 image, N=4) against the same computation done
+unsharded on this rank's GPU; times both with CUDA events (max over ranks)."""
+import os
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+import torch.distributed as dist
+
+from vaeunet_b200 import distributed as D, ops, predict, testing
+from vaeunet_b200.synthetic import synthetic_fundus
+from vaeunet_b200.unet import UNetResNet
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+sd, kw = testing.resnet_fixture()
+model = UNetResNet(**kw)
+model.load_state_dict(sd)
+model = model.to(dev).eval()
+
+
+def timed(fn, reps=3):
+    fn()
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
+    dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return out, t.item()
+
+
+def report(name, res, ref, ms, ms_ref):
+    keys = ("mean", "std", "entropy")
+    errs = torch.tensor([((res[k] - ref[k]).norm() / ref[k].norm().clamp_min(1e-12)).item() for k in keys]
+                        + [(res[k] - ref[k]).abs().max().item() for k in keys], device=dev)
+    dist.all_reduce(errs, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        e = errs.tolist()
+        # fp32 bar of BASELINE.json: 1e-4 relative on the maps. std is a difference of nearly equal fp32 numbers,
+        # so the re-associated tile sums of the sharded path show up there first: its bar is on max-abs.
+        ok = e[0] < 1e-4 and e[2] < 1e-4 and e[4] < 2e-6
+        print(f"{name}: world {world}: rel L2 vs unsharded mean {e[0]:.1e} std {e[1]:.1e} entropy {e[2]:.1e}; "
+              f"max-abs mean {e[3]:.1e} std {e[4]:.1e} entropy {e[5]:.1e} {'PASS' if ok else 'FAIL'}; "
+              f"sharded {ms:.2f} ms vs one GPU {ms_ref:.2f} ms -> speed-up {ms_ref / ms:.2f}x", flush=True)
+
+
+# ---- config 4: one 700x700 patch, T = 2.0, N = 15, samples sharded
+x, _ = synthetic_fundus(1, 700, seed=21)
+x = x.to(dev)
+eps = torch.randn(15, 1, 32, generator=torch.Generator().manual_seed(3)).to(dev)
+res, ms = timed(lambda: D.mc_predict_sample_sharded(model, x, 2.0, 15, eps))
+ref, ms_ref = timed(lambda: model.mc_predict(x, 2.0, 15, eps=eps))
+report("sample-sharded MC 700x700 T=2.0 N=15", res, ref, ms, ms_ref)
+
+# ---- config 5 logic: tiled image, N = 4, tiles dealt over ranks
+img, _ = synthetic_fundus(1, 1400, seed=22)
+img = img[:, :, :1100, :].contiguous().to(dev)
+eps5 = torch.randn(4, 1, 32, generator=torch.Generator().manual_seed(4)).to(dev)
+res5, ms5 = timed(lambda: D.tiled_image_mc(model, img, 4, 512, 100, 1.0, 4, eps5), reps=2)
+
+
+def unsharded():
+    segs, mu, lv = predict.segmentation_distribution(model, img, 4, 512, 100, 1.0, 4, eps=eps5)
+    return predict.calculate_uncertainty_metrics(segs)
+
+
+ref5, ms5_ref = timed(unsharded, reps=2)
+ref5 = {k: v[0] for k, v in ref5.items()}
+report("tiled image 1100x1400 patch 512 overlap 100 N=4", res5, ref5, ms5, ms5_ref)
+dist.destroy_process_group()
