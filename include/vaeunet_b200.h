@@ -70,6 +70,13 @@ typedef struct vu_conv_args {
 } vu_conv_args;
 int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 
+/* Weight gradient of the same convolution (training step, train.py:397-399 loss.backward()):
+ *   dw[co][r*KW+s][ci] += sum_{n,ho,wo} dy[n,ho,wo,dy_coff+co] * x[n, ho*stride+r-pad, wo*stride+s-pad, x_coff+ci]
+ * `a` gives x and the geometry (x, N,H,W,x_ctot,x_coff,Cin,Cout,KH,KW,stride,pad,dtype; other fields ignored);
+ * dy is the 16-bit NHWC gradient of the conv output [N,Ho,Wo,dy_ctot]. dw is fp32 in the PACKED order
+ * [Cout][KH*KW][Cin] and is ACCUMULATED into (K splits combine with atomics): zero it first. */
+int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
+
 /* OIHW fp32 -> [O][KH*KW][I] 16-bit. transpose_io: weight is IOHW (ConvTranspose2d). */
 int vu_pack_conv_weight(const float* w_oihw, void* w_packed, int O, int I, int KH, int KW,
                         int transpose_io, int dtype, vu_stream_t stream);

@@ -39,6 +39,7 @@ SIGNATURES = {
     "vu_version": [],
     "vu_device_check": [],
     "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
+    "vu_conv2d_wgrad": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_pack_conv_weight": [p, p, i, i, i, i, i, i, p],
     "vu_pack_convT2x2_weight": [p, p, i, i, i, p],
     "vu_nchw_to_nhwc": [p, p, i, i, i, i, i, i, i, p],

@@ -8,6 +8,8 @@
 
 namespace vu {
 
+constexpr int kMaxTapsCommon = 9;
+
 __device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
     if (dtype == 0) {
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);

@@ -1,0 +1,276 @@
+// Weight gradient of a convolution on tcgen05 (training):
+//
+//   dW[co][tap][ci] = sum over output pixels p of  dY[p, co] * X[p*stride + tap - pad, ci]
+//
+// GEMM view: M = Cout (tiles of 128), N = Cin (tiles of BN <= 128), K = output pixels, one (tap, M tile,
+// N tile, K split) per work item. Both operands are NHWC activation tensors, i.e. the contraction index
+// (pixels) is the SLOW axis of each tile: they are fed to the tensor cores as MN-major operands
+// (instruction-descriptor bits 15/16). A TMA box of (64 channels x 128 pixels) lands in shared memory as
+// 128 rows of 128 B with SWIZZLE_128B, which IS the canonical MN-major layout: 8 pixel rows x 64 channels per
+// swizzle atom, SBO = 1024 B between 8-pixel groups, LBO = 16 KB between 64-channel atoms. One k-iteration =
+// 128 pixels = 8 UMMA K steps (16 pixels = 2 KB of rows each). The X box is the dY box shifted by the tap
+// (zero padding = TMA out-of-bounds fill; stride-2 convs read the parity planes of X exactly as in
+// vu_conv_igemm.cu). Partial sums of the K splits are combined with fp32 atomics into a zeroed dW.
+#include "vu_conv_common.cuh"
+
+namespace vu {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgPix = 128;                       // pixels per k-iteration
+constexpr int kWgAtomBytes = kWgPix * 128;        // one 64-channel atom: 16 KB
+constexpr int kWgABytes = 2 * kWgAtomBytes;       // M = 128 output channels
+
+struct WgradParams {
+    int wt, ht, nt, tiles_w, tiles_h, tiles_n, num_pix_tiles;
+    int num_taps, num_m_tiles, num_n_tiles, ksplit, tiles_per_split;
+    int cout, cin;
+    int8_t tap_dh[kMaxTapsCommon], tap_dw[kMaxTapsCommon], tap_map[kMaxTapsCommon];
+    float* dw;                                    // [Cout][taps][Cin] fp32, accumulated atomically
+    int dtype;
+};
+
+template <int BN> struct WgCfg {
+    static constexpr int kBBytes = (BN / 64) * kWgAtomBytes;
+    static constexpr int kStageBytes = kWgABytes + kBBytes;
+    static constexpr int kStages = (BN == 128) ? 3 : 4;
+    static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 256;
+};
+
+// MN-major, 128-byte-swizzled operand: start>>4 [0,14), LBO>>4 [16,30) = stride between 64-element MN atoms,
+// SBO>>4 [32,46) = stride between 8-row K groups, version 1 [46,48), layout 2 (SWIZZLE_128B) [61,64).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFF);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_x0,
+                  const __grid_constant__ CUtensorMap map_x1, const __grid_constant__ CUtensorMap map_x2,
+                  const __grid_constant__ CUtensorMap map_x3, const WgradParams p) {
+    using Cfg = WgCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+    const uint32_t done_bar = bar_base + 8u * (2 * Cfg::kStages);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 1);
+    volatile uint32_t* tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 1));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_dy);
+        tma_prefetch_desc(&map_x0);
+        for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(done_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // work item = blockIdx.x -> (ksplit, n_tile, m_tile, tap), tap fastest (neighbouring CTAs share pixel tiles in L2)
+    int item = blockIdx.x;
+    const int tap = item % p.num_taps; item /= p.num_taps;
+    const int m_tile = item % p.num_m_tiles; item /= p.num_m_tiles;
+    const int n_tile = item % p.num_n_tiles; item /= p.num_n_tiles;
+    const int ks = item;
+    const int t_begin = ks * p.tiles_per_split;
+    const int t_end = min(p.num_pix_tiles, t_begin + p.tiles_per_split);
+    const int n_iters = max(0, t_end - t_begin);
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const CUtensorMap* maps[4] = {&map_x0, &map_x1, &map_x2, &map_x3};
+            const CUtensorMap* mx = maps[p.tap_map[tap]];
+            for (int i = 0; i < n_iters; ++i) {
+                const int t = t_begin + i;
+                const int wb = t % p.tiles_w;
+                const int hb = (t / p.tiles_w) % p.tiles_h;
+                const int nb = t / (p.tiles_w * p.tiles_h);
+                const int w0 = wb * p.wt, h0 = hb * p.ht, n0 = nb * p.nt;
+                const int s = i % Cfg::kStages;
+                mbar_wait(empty_bar(s), ((i / Cfg::kStages) & 1) ^ 1);
+                const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                mbar_arrive_expect_tx(full_bar(s), Cfg::kStageBytes);
+                tma_load_4d(sa, &map_dy, full_bar(s), m_tile * 128, w0, h0, n0);
+                tma_load_4d(sa + kWgAtomBytes, &map_dy, full_bar(s), m_tile * 128 + 64, w0, h0, n0);
+#pragma unroll
+                for (int a = 0; a < BN / 64; ++a)
+                    tma_load_4d(sa + kWgABytes + a * kWgAtomBytes, mx, full_bar(s), n_tile * BN + a * 64,
+                                w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // bits 15/16: A and B are MN-major
+        const uint32_t idesc = umma_idesc_f16(128, BN, p.dtype == 0 ? 1u : 0u) | (1u << 15) | (1u << 16);
+        for (int i = 0; i < n_iters; ++i) {
+            const int s = i % Cfg::kStages;
+            mbar_wait(full_bar(s), (i / Cfg::kStages) & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+            const uint64_t adesc = umma_desc_mn_sw128(sa, kWgAtomBytes);
+            const uint64_t bdesc = umma_desc_mn_sw128(sa + kWgABytes, kWgAtomBytes);
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < kWgPix / 16; ++k)       // 16 pixel rows = 2048 B per K step (>>4 = 128)
+                    umma_f16_ss(tmem_base, adesc + 128u * k, bdesc + 128u * k, idesc, (i | k) != 0);
+                umma_commit(empty_bar(s));
+                if (i == n_iters - 1) umma_commit(done_bar);
+            }
+            __syncwarp();
+        }
+    } else if (n_iters > 0) {
+        // epilogue: lane of TMEM = output channel, columns = input channels
+        const int q = warp & 3;
+        const int co = m_tile * 128 + q * 32 + lane;
+        mbar_wait(done_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + c * 32, r);
+            tmem_ld_wait();
+            const int ci0 = n_tile * BN + c * 32;
+            if (co < p.cout) {
+                float* dst = p.dw + (static_cast<size_t>(co) * p.num_taps + tap) * p.cin + ci0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (ci0 + j < p.cin) atomicAdd(dst + j, __uint_as_float(r[j]));
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+static void wg_choose_tile(int n, int h, int w, int* wt_o, int* ht_o, int* nt_o) {
+    double best = -1.0;
+    for (int wt = 128; wt >= 1; wt >>= 1)
+        for (int ht = 128 / wt; ht >= 1; ht >>= 1) {
+            const int nt = 128 / (wt * ht);
+            const double cover = (double)((w + wt - 1) / wt * wt) * ((h + ht - 1) / ht * ht) * ((n + nt - 1) / nt * nt);
+            const double eff = (double)w * h * n / cover;
+            if (eff > best + 1e-9) { best = eff; *wt_o = wt; *ht_o = ht; *nt_o = nt; }
+        }
+}
+
+template <int BN>
+static int launch_wgrad(const CUtensorMap& dym, const CUtensorMap* xm, const WgradParams& wp, int grid, cudaStream_t stream) {
+    using Cfg = WgCfg<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(wgrad): %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    conv_wgrad_kernel<BN><<<grid, kWgThreads, Cfg::kSmemBytes, stream>>>(dym, xm[0], xm[1], xm[2], xm[3], wp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_wgrad launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+extern "C" int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw,
+                               vu_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!a || !a->x || !dy || !dw) return set_error(VU_ERR_INVALID, "wgrad: null pointer");
+    const int KH = a->KH, KW = a->KW, S = a->stride, P = a->pad;
+    const bool ok_geom = (KH == KW) && ((KH == 3 && P == 1) || (KH == 1 && P == 0)) && (S == 1 || S == 2);
+    if (!ok_geom) return set_error(VU_ERR_UNSUPPORTED, "wgrad: only 3x3 p1 / 1x1 p0, stride 1|2 (got k%d s%d p%d)", KH, S, P);
+    if (a->Cin % 8 || a->x_ctot % 8 || a->x_coff % 8 || dy_ctot % 8 || dy_coff % 8 || a->Cout % 8)
+        return set_error(VU_ERR_ALIGN, "wgrad: channel counts/offsets must be multiples of 8");
+    if ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(dy)) & 15)
+        return set_error(VU_ERR_ALIGN, "wgrad: pointers must be 16-byte aligned");
+    const int Ho = (a->H + 2 * P - KH) / S + 1, Wo = (a->W + 2 * P - KW) / S + 1;
+
+    WgradParams wp{};
+    wg_choose_tile(a->N, Ho, Wo, &wp.wt, &wp.ht, &wp.nt);
+    wp.tiles_w = (Wo + wp.wt - 1) / wp.wt; wp.tiles_h = (Ho + wp.ht - 1) / wp.ht; wp.tiles_n = (a->N + wp.nt - 1) / wp.nt;
+    wp.num_pix_tiles = wp.tiles_w * wp.tiles_h * wp.tiles_n;
+    wp.num_taps = KH * KW;
+    wp.cout = a->Cout; wp.cin = a->Cin;
+    wp.dw = dw; wp.dtype = a->dtype;
+    const int bn = (a->Cin > 64) ? 128 : 64;
+    wp.num_m_tiles = (a->Cout + 127) / 128;
+    wp.num_n_tiles = (a->Cin + bn - 1) / bn;
+    const int base_items = wp.num_taps * wp.num_m_tiles * wp.num_n_tiles;
+    // K splits: fill ~2 waves of SMs, at least 4 k-iterations per item
+    int ksplit = (2 * num_sms() + base_items - 1) / base_items;
+    if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
+    if (ksplit < 1) ksplit = 1;
+    wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;
+    wp.ksplit = (wp.num_pix_tiles + wp.tiles_per_split - 1) / wp.tiles_per_split;
+
+    const uint32_t box[4] = {64u, (uint32_t)wp.wt, (uint32_t)wp.ht, (uint32_t)wp.nt};
+    CUtensorMap dym, xm[4];
+    {
+        const uint16_t* db = static_cast<const uint16_t*>(dy) + dy_coff;
+        const uint64_t pix = (uint64_t)dy_ctot * 2;
+        const uint64_t dims[4] = {(uint64_t)a->Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * Wo, pix * Wo * Ho};
+        int rc = encode_map(&dym, a->dtype, 4, db, dims, str, box);
+        if (rc) return rc;
+    }
+    const uint16_t* xb = static_cast<const uint16_t*>(a->x) + a->x_coff;
+    const uint64_t pix = (uint64_t)a->x_ctot * 2;
+    if (S == 1) {
+        const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * a->W, pix * a->W * a->H};
+        int rc = encode_map(&xm[0], a->dtype, 4, xb, dims, str, box);
+        if (rc) return rc;
+        xm[1] = xm[2] = xm[3] = xm[0];
+        int t = 0;
+        for (int r = 0; r < KH; ++r)
+            for (int s = 0; s < KW; ++s, ++t) {
+                wp.tap_dh[t] = (int8_t)(r - P); wp.tap_dw[t] = (int8_t)(s - P); wp.tap_map[t] = 0;
+            }
+    } else {
+        for (int pr = 0; pr < 2; ++pr)
+            for (int pc = 0; pc < 2; ++pc) {
+                const int hp = (a->H - pr + 1) / 2, wpn = (a->W - pc + 1) / 2;
+                const int id = pr * 2 + pc;
+                if (hp <= 0 || wpn <= 0) { xm[id] = xm[0]; continue; }
+                const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)wpn, (uint64_t)hp, (uint64_t)a->N};
+                const uint64_t str[3] = {pix * 2, pix * a->W * 2, pix * a->W * a->H};
+                int rc = encode_map(&xm[id], a->dtype, 4, xb + ((size_t)pr * a->W + pc) * a->x_ctot, dims, str, box);
+                if (rc) return rc;
+            }
+        int t = 0;
+        for (int r = 0; r < KH; ++r)
+            for (int s = 0; s < KW; ++s, ++t) {
+                const int ir = r - P, ic = s - P;
+                const int pr = ((ir % 2) + 2) % 2, pc = ((ic % 2) + 2) % 2;
+                wp.tap_dh[t] = (int8_t)((ir - pr) / 2); wp.tap_dw[t] = (int8_t)((ic - pc) / 2);
+                wp.tap_map[t] = (int8_t)(pr * 2 + pc);
+            }
+    }
+    const int grid = base_items * wp.ksplit;
+    if (bn == 128) return launch_wgrad<128>(dym, xm, wp, grid, stream);
+    return launch_wgrad<64>(dym, xm, wp, grid, stream);
+}

@@ -155,6 +155,77 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
     return out
 
 
+def conv2d_wgrad(x: Act, dy: Act, k: int, stride: int, pad: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dW of conv2d(x, W): fp32 [Cout, k*k, Cin] in the packed tap order (accumulates into `out` if given)."""
+    require_device()
+    Cout = dy.C
+    Ho = (x.H + 2 * pad - k) // stride + 1
+    Wo = (x.W + 2 * pad - k) // stride + 1
+    assert (dy.N, dy.H, dy.W) == (x.N, Ho, Wo) and dy.dt == x.dt, "wgrad: dy shape"
+    if out is None:
+        out = torch.zeros((Cout, k * k, x.C), dtype=torch.float32, device=x.t.device)
+    assert out.shape == (Cout, k * k, x.C) and out.dtype == torch.float32 and out.is_contiguous()
+    a = ConvArgs()
+    a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
+    a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad; a.dtype = x.dt
+    check(load().vu_conv2d_wgrad(C.byref(a), dy.t.data_ptr(), dy.ctot, dy.coff, out.data_ptr(), _stream()), "vu_conv2d_wgrad")
+    _count()
+    return out
+
+
+def unpack_wgrad(dw_packed: torch.Tensor, k: int) -> torch.Tensor:
+    """[Cout, k*k, Cin] -> OIHW."""
+    O, T, I = dw_packed.shape
+    return dw_packed.reshape(O, k, k, I).permute(0, 3, 1, 2).contiguous()
+
+
+def pack_dgrad_weights(w: torch.Tensor, stride: int, dtype=BF16):
+    """Filter banks for the data gradient of conv2d(x, w) (w OIHW, 3x3 p1 or 1x1 p0), run by vu_conv2d_fwd on dY:
+    stride 1: one bank = w rotated by 180 degrees with in/out swapped;
+    stride 2: one bank per output-pixel parity (ph, pc) of dX, written with the pixel-shuffle store (out_up = 2).
+    For 3x3 the parity banks are 3x3 p1 banks with the unused taps zero: dX[2k+ph] takes r = 1 at offset 0 (ph = 0)
+    or r = 2 at offset 0 and r = 0 at offset +1 (ph = 1)."""
+    O, I, k, _ = w.shape
+    wt = w.detach().float().transpose(0, 1)                    # [I, O, k, k]
+    if stride == 1:
+        return [pack_conv_weight(wt.flip(2, 3).contiguous(), dtype)]
+    assert stride == 2
+    if k == 1:
+        return [pack_conv_weight(wt.contiguous(), dtype)]       # only parity (0, 0) is non-zero
+    banks = []
+    taps = {0: [(1, 1)], 1: [(2, 1), (0, 2)]}                   # parity -> [(r of w, r' of the 3x3 p1 bank)]
+    for ph in range(2):
+        for pc in range(2):
+            b = torch.zeros((I, O, 3, 3), dtype=torch.float32, device=w.device)
+            for (r, rp) in taps[ph]:
+                for (s, sp) in taps[pc]:
+                    b[:, :, rp, sp] = wt[:, :, r, s]
+            banks.append(pack_conv_weight(b, dtype))
+    return banks
+
+
+def conv2d_dgrad(dy: Act, banks, k: int, stride: int, H: int, W: int, out: Optional[Act] = None,
+                 accumulate: bool = False) -> Act:
+    """dX [N,H,W,Cin] of conv2d(x, w) from dY; `banks` from pack_dgrad_weights. accumulate: dX += (stride 1 only)."""
+    require_device()
+    Cin = banks[0].shape[0]
+    if out is None:
+        assert not accumulate
+        out = new_act(dy.N, H, W, Cin, dy.dt, dy.t.device)
+    if stride == 1:
+        assert (dy.H, dy.W) == (H, W)
+        return conv2d(dy, banks[0], k, 1, k // 2, None, None, False, out=out, residual=out if accumulate else None)
+    assert not accumulate and H == 2 * dy.H and W == 2 * dy.W, "stride-2 dgrad needs even input sizes"
+    if k == 1:
+        out.t[..., out.coff:out.coff + out.C].zero_()
+        _count()
+        return conv2d(dy, banks[0], 1, 1, 0, None, None, False, out=out, out_up=2, out_dh=0, out_dw=0)
+    for ph in range(2):
+        for pc in range(2):
+            conv2d(dy, banks[ph * 2 + pc], 3, 1, 1, None, None, False, out=out, out_up=2, out_dh=ph, out_dw=pc)
+    return out
+
+
 # ------------------------------------------------------------------ layout / pooling / resize
 def nchw_to_nhwc(x: torch.Tensor, out: Optional[Act] = None, dtype=BF16) -> Act:
     require_device()
