@@ -96,6 +96,10 @@ int vu_nhwc_to_nchw(const void* x, float* y, int N, int C, int H, int W, int x_c
 int vu_stem_conv7x7s2(const float* x_nchw, const float* w_oihw, const float* scale, const float* bias,
                       void* y, int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff,
                       int dtype, vu_stream_t stream);
+/* Same with the activation selectable (relu = 0: the raw conv output that train-mode BatchNorm consumes). */
+int vu_stem_conv7x7s2_act(const float* x_nchw, const float* w_oihw, const float* scale, const float* bias,
+                          void* y, int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff, int relu,
+                          int dtype, vu_stream_t stream);
 /* Direct 3x3 s1 p1 conv for tiny Cin (basic UNet `inc`, unet/unet_parts.py:40 with Cin = n_channels). */
 int vu_conv3x3_small_cin(const float* x_nchw, const float* w_oihw, const float* scale, const float* bias,
                          void* y, int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff,
@@ -208,6 +212,72 @@ int vu_ece_hist(const float* p, const float* gt, size_t n, int num_bins, double*
  * counts[0..3] = tp, fp, tn, fn of (x > thr) vs (t > 0.5) as fp64. */
 int vu_confusion_counts(const float* x, const float* t, size_t n, float thr, double* counts,
                         vu_stream_t stream);
+
+/* ---------------------------------------------------------------- training step (train.py:385-411)
+ * Train-mode BatchNorm2d over an NHWC 16-bit slice (unet_parts.py:41,44; unet_resnet.py:61,67 and every timm BN):
+ * vu_bn_stats -> sums[0..C) = sum x, sums[C..2C) = sum x^2 (fp64); vu_bn_finalize -> mean / invstd (biased var, eps)
+ * and the running statistics update (momentum, unbiased var); vu_bn_apply -> y = act(gamma*(x-mean)*invstd + beta
+ * + residual). vu_bn_bwd: dz = dy * (y_relu > 0 if y_relu), sums <- (sum dz, sum dz*xhat) = (dbeta, dgamma) in fp64,
+ * dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dz_out (optional) receives dz (residual-branch gradient). */
+int vu_bn_stats(const void* x, size_t npix, int C, int x_ctot, int x_coff, double* sums, int dtype, vu_stream_t stream);
+int vu_bn_finalize(const double* sums, double count, int C, float eps, float momentum, float* mean, float* invstd,
+                   float* running_mean, float* running_var, vu_stream_t stream);
+int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const float* mean, const float* invstd,
+                const float* gamma, const float* beta, const void* residual, int res_ctot, int res_coff, int relu,
+                void* y, int y_ctot, int y_coff, int dtype, vu_stream_t stream);
+int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot, int dy_coff,
+              const void* y_relu, int y_ctot, int y_coff, const float* mean, const float* invstd, const float* gamma,
+              double* sums, void* dx, int dx_ctot, int dx_coff, void* dz_out, int dz_ctot, int dz_coff, int dtype,
+              vu_stream_t stream);
+/* dst += src (gradient accumulation over the consumers of an activation). */
+int vu_add_nhwc(void* dst, int d_ctot, int d_coff, const void* src, int s_ctot, int s_coff, size_t npix, int C,
+                int dtype, vu_stream_t stream);
+/* Backward of vu_maxpool_nhwc (first maximum wins, as ATen) and of vu_bilinear_ac_nhwc / vu_resize_logits (gathers). */
+int vu_maxpool_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, int x_ctot, int x_coff,
+                   int dy_ctot, int dy_coff, int dx_ctot, int dx_coff, int k, int s, int p, int dtype, vu_stream_t stream);
+int vu_bilinear_ac_bwd(const void* dy, void* dx, int N, int Hs, int Ws, int C, int Ho, int Wo, int dy_ctot, int dy_coff,
+                       int dx_ctot, int dx_coff, int accumulate, int dtype, vu_stream_t stream);
+int vu_resize_map_bwd(const float* dy, float* dx, int N, int Hs, int Ws, int Ho, int Wo, vu_stream_t stream);
+/* Per-pixel pieces of the attention gate / output conv and their gradients:
+ *   scale_by_map: out[p,c] (+)= a[p,c]*m[p];  channel_dot: out[p] = sum_c a[p,c]*b[p,c];
+ *   map_expand: out[p,c] = m[p]*w[c]*(mask[p,c] > 0 if mask);
+ *   weighted_channel_sum: sums[(img)*C + c] = sum_p (m ? m[p] : 1)*x[p,c] in fp64 (per image or over all images). */
+int vu_scale_by_map(const void* a, int a_ctot, int a_coff, const float* m, void* out, int o_ctot, int o_coff,
+                    size_t npix, int C, int accumulate, int dtype, vu_stream_t stream);
+int vu_channel_dot(const void* a, int a_ctot, int a_coff, const void* b, int b_ctot, int b_coff, float* out,
+                   size_t npix, int C, int dtype, vu_stream_t stream);
+int vu_map_expand(const float* m, const float* w, const void* mask, int k_ctot, int k_coff, void* out, int o_ctot,
+                  int o_coff, size_t npix, int C, int dtype, vu_stream_t stream);
+int vu_weighted_channel_sum(const void* x, int x_ctot, int x_coff, const float* m, int n_img, size_t pix_per_img, int C,
+                            int per_image, double* sums, int dtype, vu_stream_t stream);
+/* psi branch of the gate: single-channel train-mode BN + sigmoid on an fp32 map (unet_resnet.py:17-21) and its
+ * backward (dx w.r.t. the pre-BN map; grads[0] = dgamma, grads[1] = dbeta). stat = {mean, invstd}; sums: fp64[2]. */
+int vu_map_bn_sigmoid_fwd(const float* x, size_t n, float gamma, float beta, float eps, float momentum,
+                          float* running_mean, float* running_var, double* sums, float* stat, float* psi,
+                          vu_stream_t stream);
+int vu_map_bn_sigmoid_bwd(const float* x, const float* dpsi, const float* psi, const float* stat, float gamma, size_t n,
+                          double* sums, float* dx, float* grads, vu_stream_t stream);
+int vu_map_sum(const float* x, size_t n, double* sums, vu_stream_t stream);   /* sums[0] = sum x, sums[1] = sum x^2 */
+/* Dense layer on M <= 64 vectors = 1x1 conv (+ train-mode BN over the rows) (+ ReLU) on spatially constant maps or
+ * pooled features (z_initial, z_proj, mu/logvar heads). y_raw / mean / invstd are saved for the backward. */
+int vu_vec_layer_fwd(const float* z, const float* w, const float* b, int M, int L, int C, const float* gamma,
+                     const float* beta, float eps, float momentum, double stat_count, float* running_mean,
+                     float* running_var, int relu, float* y_raw, float* y, float* mean, float* invstd, vu_stream_t stream);
+int vu_vec_layer_bwd(const float* dy, const float* z, const float* w, const float* y_raw, const float* y, int M, int L,
+                     int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dz /* += */,
+                     float* dw, float* db, float* dgamma, float* dbeta, vu_stream_t stream);
+/* z = mu + eps*exp(.5 logvar)*T: dmu += sum_s dz, dlogvar += sum_s dz*eps*.5*exp(.5 logvar)*T. */
+int vu_reparam_bwd(const float* dz, const float* eps, const float* logvar, float temperature, float* dmu,
+                   float* dlogvar, size_t n_per_sample, int num_samples, vu_stream_t stream);
+/* Weight gradient of the ResNet stem conv 7x7 s2 p3 (Cin <= 4): dw [Cout][Cin][7][7] fp32, ACCUMULATED (zero it). */
+int vu_stem_wgrad(const float* x_nchw, const void* dy, int dy_ctot, int dy_coff, float* dw, int N, int Cin, int H, int W,
+                  int Cout, int dtype, vu_stream_t stream);
+/* clip_grad_norm_ + AdamW on flat fp32 buffers (train.py:403-408): out += sum g^2; the step derives the clip
+ * coefficient min(1, max_norm / (sqrt(sumsq)*grad_scale + 1e-6)) on the device (grad_sumsq NULL = no clipping). */
+int vu_sumsq(const float* g, size_t n, double* out, int zero_first, vu_stream_t stream);
+int vu_adamw_step(float* p, const float* g, float* m, float* v, size_t n, float lr, float beta1, float beta2, float eps,
+                  float weight_decay, int step, const double* grad_sumsq, float max_norm, float grad_scale,
+                  vu_stream_t stream);
 
 #ifdef __cplusplus
 }

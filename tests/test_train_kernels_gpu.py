@@ -64,3 +64,162 @@ def test_conv_dgrad(case, cuda_dev):
         got2 = ops.conv2d_dgrad(dya, banks, k, stride, H, W, out=got, accumulate=True)
         g2 = got2.t.float().cpu().permute(0, 3, 1, 2)
         assert ((g2 - 2 * ref).norm() / (2 * ref).norm()).item() < 8e-3
+
+
+# ---------------------------------------------------------------------------------------------------------
+# memory-bound training kernels vs torch CPU autograd (fp32 reference on the same bf16-rounded inputs)
+# ---------------------------------------------------------------------------------------------------------
+def _act(ops, t, dev):
+    return ops.Act(t.permute(0, 2, 3, 1).contiguous().bfloat16().to(dev))
+
+
+def _nchw(a):
+    return a.t[..., a.coff:a.coff + a.C].float().cpu().permute(0, 3, 1, 2)
+
+
+def _q(t):
+    return t.bfloat16().float()
+
+
+@pytest.mark.parametrize("C,relu,res", [(64, True, False), (224, True, True), (8, False, False), (512, True, True)])
+def test_bn_train_fwd_bwd(cuda_dev, C, relu, res):
+    from vaeunet_b200 import ops, train_ops as T
+    g = torch.Generator().manual_seed(C)
+    N, H, W = 3, 9, 7
+    x = _q(torch.randn(N, C, H, W, generator=g) * 2 + 0.5)
+    r = _q(torch.randn(N, C, H, W, generator=g)) if res else None
+    gamma = torch.rand(C, generator=g) + 0.5
+    beta = torch.randn(C, generator=g) * 0.2
+    dy = _q(torch.randn(N, C, H, W, generator=g))
+    xr = x.clone().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm, rv = torch.zeros(C), torch.ones(C)
+    y = F.batch_norm(xr, rm, rv, gr, br, True, 0.1, 1e-5)
+    if res:
+        y = y + r
+    if relu:
+        y = F.relu(y)
+    y.backward(dy)
+    d = cuda_dev
+    rm_g, rv_g = torch.zeros(C, device=d), torch.ones(C, device=d)
+    xa = _act(ops, x, d)
+    out, mean, invstd = T.bn_train_fwd(xa, gamma.to(d), beta.to(d), rm_g, rv_g, relu, _act(ops, r, d) if res else None)
+    assert (_nchw(out) - y.detach()).abs().max() <= 1.2e-2 * y.detach().abs().max()
+    assert (rm_g.cpu() - rm).abs().max() < 1e-5 and (rv_g.cpu() - rv).abs().max() < 1e-4
+    dx, dgam, dbet, dz = T.bn_train_bwd(xa, _act(ops, dy, d), out if relu else None, mean, invstd, gamma.to(d), want_dz=res)
+    # the GPU ReLU mask comes from the bf16-rounded output; compare away from the mask boundary through norms
+    assert ((_nchw(dx) - xr.grad).norm() / xr.grad.norm()).item() < 1.5e-2
+    assert ((dgam.cpu() - gr.grad).norm() / gr.grad.norm()).item() < 5e-3
+    assert ((dbet.cpu() - br.grad).norm() / br.grad.norm()).item() < 5e-3
+    if res:
+        mask = (y.detach() > 0).float() if relu else torch.ones_like(dy)
+        assert ((_nchw(dz) - dy * mask).norm() / (dy * mask).norm()).item() < 5e-3
+
+
+def test_maxpool_bilinear_bwd(cuda_dev):
+    from vaeunet_b200 import ops, train_ops as T
+    g = torch.Generator().manual_seed(9)
+    d = cuda_dev
+    x = _q(torch.randn(2, 16, 12, 14, generator=g))
+    xr = x.clone().requires_grad_(True)
+    y = F.max_pool2d(xr, 3, 2, 1)
+    dy = _q(torch.randn(y.shape, generator=g))
+    y.backward(dy)
+    dx = T.maxpool_bwd(_act(ops, x, d), _act(ops, dy, d), 3, 2, 1)
+    assert (_nchw(dx) - xr.grad).abs().max() <= 1e-2 * xr.grad.abs().max()
+    for (hs, ws, ho, wo) in [(8, 8, 16, 16), (11, 9, 22, 17), (1, 1, 5, 6), (16, 16, 32, 32)]:
+        x = torch.randn(2, 24, hs, ws, generator=g).requires_grad_(True)
+        y = F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
+        dy = _q(torch.randn(y.shape, generator=g))
+        y.backward(dy)
+        dx = T.bilinear_ac_bwd(_act(ops, dy, d), hs, ws)
+        assert ((_nchw(dx) - x.grad).norm() / x.grad.norm()).item() < 5e-3, (hs, ws, ho, wo)
+        m = torch.randn(3, ho, wo, generator=g)
+        xm = torch.randn(3, 1, hs, ws, generator=g).requires_grad_(True)
+        F.interpolate(xm, size=(ho, wo), mode="bilinear", align_corners=True).backward(m.unsqueeze(1))
+        got = T.resize_map_bwd(m.to(d), hs, ws).cpu()
+        assert (got - xm.grad[:, 0]).abs().max() < 1e-5
+
+
+def test_gate_pieces_and_vec_layers(cuda_dev):
+    from vaeunet_b200 import ops, train_ops as T
+    g = torch.Generator().manual_seed(10)
+    d = cuda_dev
+    N, C, H, W = 2, 64, 6, 5
+    a, b = _q(torch.randn(N, C, H, W, generator=g)), _q(torch.randn(N, C, H, W, generator=g))
+    m = torch.rand(N, H, W, generator=g)
+    out = ops.new_act(N, H, W, C)
+    T.scale_by_map(_act(ops, a, d), m.to(d), out)
+    assert (_nchw(out) - a * m.unsqueeze(1)).abs().max() < 2e-2
+    assert (T.channel_dot(_act(ops, a, d), _act(ops, b, d)).cpu() - (a * b).sum(1)).abs().max() < 1e-3
+    w = torch.randn(C, generator=g)
+    T.map_expand(m.to(d), w.to(d), _act(ops, a, d), out)
+    ref = m.unsqueeze(1) * w.view(1, -1, 1, 1) * (a > 0)
+    assert (_nchw(out) - ref).abs().max() <= 1e-2 * ref.abs().max()
+    s = T.weighted_channel_sum(_act(ops, a, d), m.to(d), per_image=False).cpu()
+    assert (s - (a * m.unsqueeze(1)).sum((0, 2, 3))).abs().max() < 1e-3
+    s = T.weighted_channel_sum(_act(ops, a, d), None, per_image=True).cpu()
+    assert (s - a.sum((2, 3))).abs().max() < 1e-3
+    # psi branch: BN(1 channel) + sigmoid
+    p_raw = torch.randn(N, H, W, generator=g) * 2 + 1
+    pr = p_raw.clone().requires_grad_(True)
+    gam = torch.tensor([1.3], requires_grad=True); bet = torch.tensor([-0.2], requires_grad=True)
+    rm, rv = torch.zeros(1), torch.ones(1)
+    psi_ref = torch.sigmoid(F.batch_norm(pr.unsqueeze(1), rm, rv, gam, bet, True, 0.1, 1e-5))[:, 0]
+    dpsi = torch.randn(N, H, W, generator=g)
+    psi_ref.backward(dpsi)
+    rm_g, rv_g = torch.zeros(1, device=d), torch.ones(1, device=d)
+    psi, stat = T.map_bn_sigmoid_fwd(p_raw.to(d), 1.3, -0.2, rm_g, rv_g)
+    assert (psi.cpu() - psi_ref.detach()).abs().max() < 1e-5 and (rv_g.cpu() - rv).abs().max() < 1e-5
+    dx, grads = T.map_bn_sigmoid_bwd(p_raw.to(d), dpsi.to(d), psi, stat, 1.3)
+    assert (dx.cpu() - pr.grad).abs().max() < 1e-5
+    assert abs(grads[0].item() - gam.grad.item()) < 1e-4 and abs(grads[1].item() - bet.grad.item()) < 1e-4
+    # dense vector layer with train-mode BN over the rows (z_initial / z_proj on constant maps)
+    M, L, Cc = 6, 32, 80
+    z = torch.randn(M, L, generator=g).requires_grad_(True)
+    wv = (torch.randn(Cc, L, generator=g) * 0.3).requires_grad_(True)
+    bv = torch.randn(Cc, generator=g).requires_grad_(True)
+    gam = (torch.rand(Cc, generator=g) + 0.5).requires_grad_(True); bet = torch.randn(Cc, generator=g).requires_grad_(True)
+    rm, rv = torch.zeros(Cc), torch.ones(Cc)
+    y_ref = F.relu(F.batch_norm(F.linear(z, wv, bv), rm, rv, gam, bet, True, 0.1, 1e-5))
+    dy = torch.randn(M, Cc, generator=g)
+    y_ref.backward(dy)
+    rm_g, rv_g = torch.zeros(Cc, device=d), torch.ones(Cc, device=d)
+    y, saved = T.vec_layer_fwd(z.detach().to(d), wv.detach().to(d), bv.detach().to(d), gam.detach().to(d), bet.detach().to(d),
+                               rm_g, rv_g, True, float(M))
+    assert (y.cpu() - y_ref.detach()).abs().max() < 1e-4 and (rv_g.cpu() - rv).abs().max() < 1e-4
+    dz = torch.zeros(M, L, device=d)
+    dw, db, dg, dbt = T.vec_layer_bwd(dy.to(d), saved, wv.detach().to(d), gam.detach().to(d), True, dz, True)
+    assert (dz.cpu() - z.grad).abs().max() < 1e-4 and (dw.cpu() - wv.grad).abs().max() < 1e-4
+    assert (dg.cpu() - gam.grad).abs().max() < 1e-4 and (dbt.cpu() - bet.grad).abs().max() < 1e-4
+    assert db.abs().max().item() < 1e-4          # a bias in front of train-mode BN has zero gradient
+
+
+def test_stem_wgrad_and_adamw(cuda_dev):
+    from vaeunet_b200 import ops, train_ops as T
+    g = torch.Generator().manual_seed(11)
+    d = cuda_dev
+    x = torch.rand(2, 3, 40, 36, generator=g)
+    w = (torch.randn(64, 3, 7, 7, generator=g) * 0.1).requires_grad_(True)
+    y = F.conv2d(x, w, None, 2, 3)
+    dy = _q(torch.randn(y.shape, generator=g))
+    y.backward(dy)
+    raw = T.stem_conv_raw(x.to(d), w.detach().to(d), ops.BF16)
+    assert (_nchw(raw) - y.detach()).abs().max() <= 1e-2 * y.detach().abs().max()
+    dw = T.stem_wgrad(x.to(d), _act(ops, dy, d), 64).cpu()
+    assert ((dw - w.grad).norm() / w.grad.norm()).item() < 1e-4
+    # AdamW with gradient clipping, two steps
+    n = 1000
+    p0 = torch.randn(n, generator=g); g1 = torch.randn(n, generator=g) * 3
+    pt = p0.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([pt], lr=1e-3, weight_decay=1e-2)
+    p, m, v = p0.clone().to(d), torch.zeros(n, device=d), torch.zeros(n, device=d)
+    ss = torch.zeros(1, dtype=torch.float64, device=d)
+    for step in (1, 2):
+        gi = g1 * step
+        pt.grad = gi.clone()
+        torch.nn.utils.clip_grad_norm_([pt], 1.0)
+        opt.step()
+        T.sumsq(gi.to(d), ss, True)
+        T.adamw_step(p, gi.to(d), m, v, 1e-3, (0.9, 0.999), 1e-8, 1e-2, step, ss, 1.0)
+    assert (p.cpu() - pt.detach()).abs().max() < 1e-5

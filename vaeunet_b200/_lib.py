@@ -45,6 +45,7 @@ SIGNATURES = {
     "vu_nchw_to_nhwc": [p, p, i, i, i, i, i, i, i, p],
     "vu_nhwc_to_nchw": [p, p, i, i, i, i, i, i, i, p],
     "vu_stem_conv7x7s2": [p, p, p, p, p, i, i, i, i, i, i, i, i, p],
+    "vu_stem_conv7x7s2_act": [p, p, p, p, p, i, i, i, i, i, i, i, i, i, p],
     "vu_conv3x3_small_cin": [p, p, p, p, p, i, i, i, i, i, i, i, i, i, p],
     "vu_maxpool_nhwc": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_bilinear_ac_nhwc": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
@@ -66,6 +67,28 @@ SIGNATURES = {
     "vu_kl_free_bits": [p, p, i, i, f, p, p, p, f, p],
     "vu_ece_hist": [p, p, sz, i, p, p],
     "vu_confusion_counts": [p, p, sz, f, p, p],
+    # ---- training step
+    "vu_bn_stats": [p, sz, i, i, i, p, i, p],
+    "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
+    "vu_bn_apply": [p, sz, i, i, i, p, p, p, p, p, i, i, i, p, i, i, i, p],
+    "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, i, p],
+    "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],
+    "vu_maxpool_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_bilinear_ac_bwd": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_resize_map_bwd": [p, p, i, i, i, i, i, p],
+    "vu_scale_by_map": [p, i, i, p, p, i, i, sz, i, i, i, p],
+    "vu_channel_dot": [p, i, i, p, i, i, p, sz, i, i, p],
+    "vu_map_expand": [p, p, p, i, i, p, i, i, sz, i, i, p],
+    "vu_weighted_channel_sum": [p, i, i, p, i, sz, i, i, p, i, p],
+    "vu_map_bn_sigmoid_fwd": [p, sz, f, f, f, f, p, p, p, p, p, p],
+    "vu_map_bn_sigmoid_bwd": [p, p, p, p, f, sz, p, p, p, p],
+    "vu_map_sum": [p, sz, p, p],
+    "vu_vec_layer_fwd": [p, p, p, i, i, i, p, p, f, f, C.c_double, p, p, i, p, p, p, p, p],
+    "vu_vec_layer_bwd": [p, p, p, p, p, i, i, i, p, p, p, i, p, p, p, p, p, p],
+    "vu_reparam_bwd": [p, p, p, f, p, p, sz, i, p],
+    "vu_stem_wgrad": [p, p, i, i, p, i, i, i, i, i, i, p],
+    "vu_sumsq": [p, sz, p, i, p],
+    "vu_adamw_step": [p, p, p, p, sz, f, f, f, f, f, i, p, f, f, p],
 }
 
 _lib = None

@@ -286,6 +286,13 @@ extern "C" int vu_stem_conv7x7s2(const float* x, const float* w, const float* sc
     return launch_small_cin<7, 2>(x, w, scale, bias, y, N, Cin, H, W, Cout, 3, y_ctot, y_coff, 1, dtype, (cudaStream_t)st);
 }
 
+extern "C" int vu_stem_conv7x7s2_act(const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
+                                     int Cin, int H, int W, int Cout, int y_ctot, int y_coff, int relu, int dtype,
+                                     vu_stream_t st) {
+    if (!x || !w || !y) return set_error(VU_ERR_INVALID, "stem: null");
+    return launch_small_cin<7, 2>(x, w, scale, bias, y, N, Cin, H, W, Cout, 3, y_ctot, y_coff, relu, dtype, (cudaStream_t)st);
+}
+
 extern "C" int vu_conv3x3_small_cin(const float* x, const float* w, const float* scale, const float* bias, void* y,
                                     int N, int Cin, int H, int W, int Cout, int y_ctot, int y_coff, int relu, int dtype,
                                     vu_stream_t st) {

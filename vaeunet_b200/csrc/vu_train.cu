@@ -1,0 +1,243 @@
+// Memory-bound kernels of the training step (train.py:385-411): train-mode BatchNorm2d forward /
+// backward over NHWC 16-bit maps, gradient accumulation, and the backward passes of max-pool, bilinear
+// resize, attention gate, output conv and the small latent-vector layers. All arithmetic is fp32 (fp64 for the
+// cross-block accumulation of batch statistics); activations and activation gradients are 16-bit NHWC slices.
+#include "vu_half.cuh"
+#include "vu_internal.h"
+
+namespace vu {
+
+static int tr_grid(size_t items, int per_block, int mult = 8) {
+    size_t g = (items + per_block - 1) / per_block;
+    const size_t cap = (size_t)num_sms() * mult;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+// ---------------------------------------------------------------- per-channel sums over pixels
+// Block = 256 threads = (256 / C8) pixel lanes x C8 channel chunks (C8 = C/8 <= 128). Each thread accumulates
+// its 8 channels over a strided set of pixels in fp32, lanes are combined through smem, and one thread per
+// channel adds the block's partial to the global fp64 accumulator.
+// MODE 0: sums[c] += x, sums[C+c] += x^2                                    (BN forward statistics)
+// MODE 1: dz = dy * (y > 0 if y), xh = (x - mean) * invstd: sums[c] += dz, sums[C+c] += dz * xh   (BN backward)
+template <int MODE>
+__global__ void __launch_bounds__(256)
+channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy,
+                    int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, size_t npix, int C8,
+                    double* __restrict__ sums, int dtype) {
+    extern __shared__ float sm[];   // [2][lanes][C8*8]
+    const int lanes = 256 / C8;
+    const int c8 = threadIdx.x % C8, pl = threadIdx.x / C8;
+    const int C = C8 * 8;
+    float a0[8], a1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
+    float mu[8], is[8];
+    if (MODE == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { mu[j] = mean[c8 * 8 + j]; is[j] = invstd[c8 * 8 + j]; }
+    }
+    if (pl < lanes) {
+        for (size_t p = (size_t)blockIdx.x * lanes + pl; p < npix; p += (size_t)gridDim.x * lanes) {
+            float f[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
+            if (MODE == 0) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a0[j] += f[j]; a1[j] = fmaf(f[j], f[j], a1[j]); }
+            } else {
+                float g[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8), g, dtype);
+                if (y != nullptr) {
+                    float o[8];
+                    unpack8(__ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8), o, dtype);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a0[j] += g[j]; a1[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], a1[j]); }
+            }
+        }
+    }
+    float* s0 = sm;
+    float* s1 = sm + lanes * C;
+    if (pl < lanes) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0[pl * C + c8 * 8 + j] = a0[j]; s1[pl * C + c8 * 8 + j] = a1[j]; }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 256) {
+        float t0 = 0.f, t1 = 0.f;
+        for (int l = 0; l < lanes; ++l) { t0 += s0[l * C + c]; t1 += s1[l * C + c]; }
+        atomicAdd(&sums[c], (double)t0);
+        atomicAdd(&sums[C + c], (double)t1);
+    }
+}
+
+// mean / invstd from the fp64 sums; running statistics updated like nn.BatchNorm2d (momentum, unbiased var).
+__global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, int C, float eps, float momentum,
+                                   float* __restrict__ mean, float* __restrict__ invstd,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const double m = sums[c] / count;
+    double var = sums[C + c] / count - m * m;
+    if (var < 0.0) var = 0.0;
+    mean[c] = (float)m;
+    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean != nullptr) {
+        const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+}
+
+// y = act(gamma * (x - mean) * invstd + beta + residual)
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const float* __restrict__ mean,
+                const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
+                const uint16_t* __restrict__ res, int res_ctot, int res_coff, int relu, uint16_t* __restrict__ y,
+                int y_ctot, int y_coff, size_t npix, int C8, int dtype) {
+    const size_t total = npix * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t p = idx / C8;
+        float f[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
+        float r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (res != nullptr) unpack8(__ldg(reinterpret_cast<const uint4*>(res + p * res_ctot + res_coff) + c8), r, dtype);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = c8 * 8 + j;
+            float v = (f[j] - mean[c]) * invstd[c] * gamma[c] + beta[c] + r[j];
+            f[j] = relu ? fmaxf(v, 0.f) : v;
+        }
+        *(reinterpret_cast<uint4*>(y + p * y_ctot + y_coff) + c8) = pack8(f, dtype);
+    }
+}
+
+// dx = gamma * invstd * (dz - mean(dz) - xh * mean(dz * xh)),  dz = dy * (y > 0 if y). dz_out (optional) = dz
+// (the gradient of a residual branch added before the ReLU).
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy,
+                    int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const double* __restrict__ sums, double count, uint16_t* __restrict__ dx, int dx_ctot, int dx_coff,
+                    uint16_t* __restrict__ dz_out, int dz_ctot, int dz_coff, size_t npix, int C8, int dtype) {
+    const size_t total = npix * C8;
+    const int C = C8 * 8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t p = idx / C8;
+        float f[8], g[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
+        unpack8(__ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8), g, dtype);
+        if (y != nullptr) {
+            float o[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8), o, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+        }
+        if (dz_out != nullptr) *(reinterpret_cast<uint4*>(dz_out + p * dz_ctot + dz_coff) + c8) = pack8(g, dtype);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = c8 * 8 + j;
+            const float m_dz = (float)(sums[c] / count), m_dzx = (float)(sums[C + c] / count);
+            const float xh = (f[j] - mean[c]) * invstd[c];
+            o[j] = gamma[c] * invstd[c] * (g[j] - m_dz - xh * m_dzx);
+        }
+        *(reinterpret_cast<uint4*>(dx + p * dx_ctot + dx_coff) + c8) = pack8(o, dtype);
+    }
+}
+
+// dst += src (gradient accumulation over the consumers of an activation)
+__global__ void __launch_bounds__(256)
+add_nhwc_kernel(uint16_t* __restrict__ dst, int d_ctot, int d_coff, const uint16_t* __restrict__ src, int s_ctot,
+                int s_coff, size_t npix, int C8, int dtype) {
+    const size_t total = npix * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t p = idx / C8;
+        uint4* dp = reinterpret_cast<uint4*>(dst + p * d_ctot + d_coff) + c8;
+        float a[8], b[8];
+        unpack8(*dp, a, dtype);
+        unpack8(__ldg(reinterpret_cast<const uint4*>(src + p * s_ctot + s_coff) + c8), b, dtype);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] += b[j];
+        *dp = pack8(a, dtype);
+    }
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+#define VU_TR_ALIGN(cond, what) if (cond) return set_error(VU_ERR_ALIGN, what ": channel counts/offsets must be multiples of 8")
+
+extern "C" int vu_bn_stats(const void* x, size_t npix, int C, int x_ctot, int x_coff, double* sums, int dtype, vu_stream_t st) {
+    if (!x || !sums || C < 8 || C > 1024) return set_error(VU_ERR_INVALID, "bn_stats: bad args (8 <= C <= 1024)");
+    VU_TR_ALIGN((C | x_ctot | x_coff) % 8, "bn_stats");
+    const int C8 = C / 8, lanes = 256 / C8;
+    cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), (cudaStream_t)st);
+    channel_sums_kernel<0><<<tr_grid(npix, lanes * 16, 4), 256, 2 * lanes * C * sizeof(float), (cudaStream_t)st>>>(
+        (const uint16_t*)x, x_ctot, x_coff, nullptr, 0, 0, nullptr, 0, 0, nullptr, nullptr, npix, C8, sums, dtype);
+    VU_CHECK_LAUNCH("bn_stats");
+    return 0;
+}
+
+extern "C" int vu_bn_finalize(const double* sums, double count, int C, float eps, float momentum, float* mean,
+                              float* invstd, float* running_mean, float* running_var, vu_stream_t st) {
+    if (!sums || !mean || !invstd || C < 1 || count < 1) return set_error(VU_ERR_INVALID, "bn_finalize: bad args");
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)st>>>(sums, count, C, eps, momentum, mean, invstd,
+                                                                       running_mean, running_var);
+    VU_CHECK_LAUNCH("bn_finalize");
+    return 0;
+}
+
+extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const float* mean,
+                           const float* invstd, const float* gamma, const float* beta, const void* residual,
+                           int res_ctot, int res_coff, int relu, void* y, int y_ctot, int y_coff, int dtype,
+                           vu_stream_t st) {
+    if (!x || !y || !mean || !invstd || !gamma || !beta) return set_error(VU_ERR_INVALID, "bn_apply: null");
+    VU_TR_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff | res_ctot | res_coff) % 8, "bn_apply");
+    bn_apply_kernel<<<tr_grid(npix * (C / 8), 256), 256, 0, (cudaStream_t)st>>>(
+        (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
+        (uint16_t*)y, y_ctot, y_coff, npix, C / 8, dtype);
+    VU_CHECK_LAUNCH("bn_apply");
+    return 0;
+}
+
+extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot,
+                         int dy_coff, const void* y_relu, int y_ctot, int y_coff, const float* mean,
+                         const float* invstd, const float* gamma, double* sums, void* dx, int dx_ctot, int dx_coff,
+                         void* dz_out, int dz_ctot, int dz_coff, int dtype, vu_stream_t st) {
+    if (!x || !dy || !mean || !invstd || !gamma || !sums || !dx || C < 8 || C > 1024)
+        return set_error(VU_ERR_INVALID, "bn_bwd: bad args");
+    VU_TR_ALIGN((C | x_ctot | x_coff | dy_ctot | dy_coff | y_ctot | y_coff | dx_ctot | dx_coff | dz_ctot | dz_coff) % 8, "bn_bwd");
+    const int C8 = C / 8, lanes = 256 / C8;
+    cudaStream_t s = (cudaStream_t)st;
+    cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), s);
+    channel_sums_kernel<1><<<tr_grid(npix, lanes * 16, 4), 256, 2 * lanes * C * sizeof(float), s>>>(
+        (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
+        mean, invstd, npix, C8, sums, dtype);
+    VU_CHECK_LAUNCH("bn_bwd_reduce");
+    bn_bwd_apply_kernel<<<tr_grid(npix * C8, 256), 256, 0, s>>>(
+        (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
+        mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
+        C8, dtype);
+    VU_CHECK_LAUNCH("bn_bwd_apply");
+    return 0;
+}
+
+extern "C" int vu_add_nhwc(void* dst, int d_ctot, int d_coff, const void* src, int s_ctot, int s_coff, size_t npix,
+                           int C, int dtype, vu_stream_t st) {
+    if (!dst || !src) return set_error(VU_ERR_INVALID, "add_nhwc: null");
+    VU_TR_ALIGN((C | d_ctot | d_coff | s_ctot | s_coff) % 8, "add_nhwc");
+    add_nhwc_kernel<<<tr_grid(npix * (C / 8), 256), 256, 0, (cudaStream_t)st>>>((uint16_t*)dst, d_ctot, d_coff,
+                                                                               (const uint16_t*)src, s_ctot, s_coff, npix,
+                                                                               C / 8, dtype);
+    VU_CHECK_LAUNCH("add_nhwc");
+    return 0;
+}

@@ -1,0 +1,327 @@
+// Backward passes of the memory-bound forward ops (training step): max-pool, bilinear
+// align_corners resize (16-bit NHWC maps and fp32 single-channel maps), and the per-pixel pieces of the
+// attention gate / output conv (scale by a map, channel dot product, outer product with a vector,
+// map-weighted channel sums, per-image channel sums). Gather formulations: deterministic, no 16-bit atomics.
+#include "vu_half.cuh"
+#include "vu_internal.h"
+
+namespace vu {
+
+static int tb_grid(size_t items, int per_block = 256, int mult = 8) {
+    size_t g = (items + per_block - 1) / per_block;
+    const size_t cap = (size_t)num_sms() * mult;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+// ---------------------------------------------------------------- max-pool backward
+// dx[n,ih,iw,c] = sum over the windows (ho,wo) containing (ih,iw) whose FIRST maximum (row-major scan, as ATen)
+// is at (ih,iw) of dy[n,ho,wo,c].
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy, int dy_ctot,
+                   int dy_coff, uint16_t* __restrict__ dx, int dx_ctot, int dx_coff, int N, int H, int W, int C8, int k,
+                   int s, int p, int Ho, int Wo, int dtype) {
+    const size_t total = (size_t)N * H * W * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int iw = (idx / C8) % W;
+        const int ih = (idx / ((size_t)C8 * W)) % H;
+        const int n = idx / ((size_t)C8 * W * H);
+        const uint16_t* xb = x + ((size_t)n * H * W) * x_ctot + x_coff;
+        float me[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        unpack8(__ldg(reinterpret_cast<const uint4*>(xb + ((size_t)ih * W + iw) * x_ctot) + c8), me, dtype);
+        const int ho_lo = max(0, (ih + p - k + s) / s), ho_hi = min(Ho - 1, (ih + p) / s);
+        const int wo_lo = max(0, (iw + p - k + s) / s), wo_hi = min(Wo - 1, (iw + p) / s);
+        for (int ho = ho_lo; ho <= ho_hi; ++ho)
+            for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+                bool win[8] = {true, true, true, true, true, true, true, true};
+                for (int r = 0; r < k; ++r) {
+                    const int h2 = ho * s - p + r;
+                    if (h2 < 0 || h2 >= H) continue;
+                    for (int q = 0; q < k; ++q) {
+                        const int w2 = wo * s - p + q;
+                        if (w2 < 0 || w2 >= W || (h2 == ih && w2 == iw)) continue;
+                        float o[8];
+                        unpack8(__ldg(reinterpret_cast<const uint4*>(xb + ((size_t)h2 * W + w2) * x_ctot) + c8), o, dtype);
+                        const bool before = (h2 < ih) || (h2 == ih && w2 < iw);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) win[j] = win[j] && (before ? me[j] > o[j] : me[j] >= o[j]);
+                    }
+                }
+                float g[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(dy + (((size_t)n * Ho + ho) * Wo + wo) * dy_ctot + dy_coff) + c8), g, dtype);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += win[j] ? g[j] : 0.f;
+            }
+        *(reinterpret_cast<uint4*>(dx + (((size_t)n * H + ih) * W + iw) * dx_ctot + dx_coff) + c8) = pack8(acc, dtype);
+    }
+}
+
+// ---------------------------------------------------------------- bilinear (align_corners=True) backward
+// Adjoint of vu_bilinear_ac_nhwc as a gather: source pixel (hs,ws) collects w(ho;hs) * w(wo;ws) * dy[ho,wo] over the
+// few destination rows / columns whose interpolation footprint contains it (same fp32 index arithmetic as forward).
+__device__ __forceinline__ float lerp_weight(int d, int s, float scale, int in_size) {
+    const float r = scale * d;
+    const int i0 = (int)r;
+    const int ip = (i0 < in_size - 1) ? 1 : 0;
+    const float l1 = r - i0;
+    float w = 0.f;
+    if (i0 == s) w += 1.0f - l1;
+    if (i0 + ip == s) w += l1;
+    return w;
+}
+__device__ __forceinline__ void dst_range(int s, float scale, int out_size, int& lo, int& hi) {
+    if (scale <= 0.f) { lo = 0; hi = out_size - 1; return; }
+    lo = max(0, (int)floorf((s - 1) / scale) - 1);
+    hi = min(out_size - 1, (int)ceilf((s + 1) / scale) + 1);
+}
+
+__global__ void __launch_bounds__(256)
+bilinear_bwd_kernel(const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff, uint16_t* __restrict__ dx, int dx_ctot,
+                    int dx_coff, int N, int Hs, int Ws, int Ho, int Wo, int C8, float sh, float sw, int accumulate,
+                    int dtype) {
+    const size_t total = (size_t)N * Hs * Ws * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int ws = (idx / C8) % Ws;
+        const int hs = (idx / ((size_t)C8 * Ws)) % Hs;
+        const int n = idx / ((size_t)C8 * Ws * Hs);
+        int hlo, hhi, wlo, whi;
+        dst_range(hs, sh, Ho, hlo, hhi);
+        dst_range(ws, sw, Wo, wlo, whi);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int ho = hlo; ho <= hhi; ++ho) {
+            const float wh = lerp_weight(ho, hs, sh, Hs);
+            if (wh == 0.f) continue;
+            for (int wo = wlo; wo <= whi; ++wo) {
+                const float ww = lerp_weight(wo, ws, sw, Ws);
+                if (ww == 0.f) continue;
+                float g[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(dy + (((size_t)n * Ho + ho) * Wo + wo) * dy_ctot + dy_coff) + c8), g, dtype);
+                const float w = wh * ww;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] = fmaf(w, g[j], acc[j]);
+            }
+        }
+        uint4* dp = reinterpret_cast<uint4*>(dx + (((size_t)n * Hs + hs) * Ws + ws) * dx_ctot + dx_coff) + c8;
+        if (accumulate) {
+            float o[8];
+            unpack8(*dp, o, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += o[j];
+        }
+        *dp = pack8(acc, dtype);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+resize_map_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int N, int Hs, int Ws, int Ho, int Wo,
+                      float sh, float sw) {
+    const size_t total = (size_t)N * Hs * Ws;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int ws = idx % Ws, hs = (idx / Ws) % Hs, n = idx / ((size_t)Ws * Hs);
+        int hlo, hhi, wlo, whi;
+        dst_range(hs, sh, Ho, hlo, hhi);
+        dst_range(ws, sw, Wo, wlo, whi);
+        float acc = 0.f;
+        for (int ho = hlo; ho <= hhi; ++ho) {
+            const float wh = lerp_weight(ho, hs, sh, Hs);
+            if (wh == 0.f) continue;
+            for (int wo = wlo; wo <= whi; ++wo)
+                acc = fmaf(wh * lerp_weight(wo, ws, sw, Ws), __ldg(dy + ((size_t)n * Ho + ho) * Wo + wo), acc);
+        }
+        dx[idx] = acc;
+    }
+}
+
+// ---------------------------------------------------------------- per-pixel pieces (attention gate, output conv)
+// out[p,c] = a[p / rep ...] * m[p]: a has Na = N / rep images (MC / none in training: rep = 1), m fp32 [N*HW]
+__global__ void __launch_bounds__(256)
+scale_by_map_kernel(const uint16_t* __restrict__ a, int a_ctot, int a_coff, const float* __restrict__ m,
+                    uint16_t* __restrict__ out, int o_ctot, int o_coff, size_t npix, int C8, int accumulate, int dtype) {
+    const size_t total = npix * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t p = idx / C8;
+        float f[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(a + p * a_ctot + a_coff) + c8), f, dtype);
+        const float s = __ldg(m + p);
+        uint4* op = reinterpret_cast<uint4*>(out + p * o_ctot + o_coff) + c8;
+        float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (accumulate) unpack8(*op, o, dtype);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fmaf(f[j], s, o[j]);
+        *op = pack8(o, dtype);
+    }
+}
+
+// out[p] = sum_c a[p,c] * b[p,c]   (8 lanes per pixel)
+__global__ void __launch_bounds__(256)
+channel_dot_kernel(const uint16_t* __restrict__ a, int a_ctot, int a_coff, const uint16_t* __restrict__ b, int b_ctot,
+                   int b_coff, float* __restrict__ out, size_t npix, int C8, int dtype) {
+    const int sub = threadIdx.x & 7;
+    const size_t gid = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 3;
+    const size_t gstride = ((size_t)gridDim.x * blockDim.x) >> 3;
+    const size_t gl = (threadIdx.x & 31) >> 3;
+    for (size_t p_ = gid; p_ - gl < npix; p_ += gstride) {
+        const bool valid = p_ < npix;
+        const size_t p = valid ? p_ : npix - 1;
+        float d = 0.f;
+        for (int c8 = sub; c8 < C8; c8 += 8) {
+            float fa[8], fb[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(a + p * a_ctot + a_coff) + c8), fa, dtype);
+            unpack8(__ldg(reinterpret_cast<const uint4*>(b + p * b_ctot + b_coff) + c8), fb, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) d = fmaf(fa[j], fb[j], d);
+        }
+        d += __shfl_xor_sync(0xffffffffu, d, 4, 8);
+        d += __shfl_xor_sync(0xffffffffu, d, 2, 8);
+        d += __shfl_xor_sync(0xffffffffu, d, 1, 8);
+        if (valid && sub == 0) out[p] = d;
+    }
+}
+
+// out[p,c] = m[p] * w[c] * (mask[p,c] > 0 if mask)      (d of a C->1 1x1 conv w.r.t. its input, through a ReLU)
+__global__ void __launch_bounds__(256)
+map_expand_kernel(const float* __restrict__ m, const float* __restrict__ w, const uint16_t* __restrict__ mask, int k_ctot,
+                  int k_coff, uint16_t* __restrict__ out, int o_ctot, int o_coff, size_t npix, int C8, int dtype) {
+    const size_t total = npix * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const size_t p = idx / C8;
+        const float s = __ldg(m + p);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = s * __ldg(w + c8 * 8 + j);
+        if (mask != nullptr) {
+            float k[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(mask + p * k_ctot + k_coff) + c8), k, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = k[j] > 0.f ? o[j] : 0.f;
+        }
+        *(reinterpret_cast<uint4*>(out + p * o_ctot + o_coff) + c8) = pack8(o, dtype);
+    }
+}
+
+// sums[img*C + c] += sum over the pixels p of image img of (m ? m[p] : 1) * x[p,c]; per_image = 0 folds all images
+// (d of the C->1 conv weight; global-average-pool; gradient of a spatially constant map).
+__global__ void __launch_bounds__(256)
+weighted_channel_sum_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const float* __restrict__ m,
+                            size_t pix_per_img, int C8, int per_image, int blocks_per_img, double* __restrict__ sums,
+                            int dtype) {
+    extern __shared__ float sm[];
+    const int lanes = 256 / C8;
+    const int c8 = threadIdx.x % C8, pl = threadIdx.x / C8;
+    const int C = C8 * 8;
+    const int img = blockIdx.x / blocks_per_img, bi = blockIdx.x % blocks_per_img;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (pl < lanes) {
+        for (size_t q = (size_t)bi * lanes + pl; q < pix_per_img; q += (size_t)blocks_per_img * lanes) {
+            const size_t p = (size_t)img * pix_per_img + q;
+            float f[8];
+            unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
+            const float s = m ? __ldg(m + p) : 1.0f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = fmaf(s, f[j], a[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sm[pl * C + c8 * 8 + j] = a[j];
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 256) {
+        float t = 0.f;
+        for (int l = 0; l < lanes; ++l) t += sm[l * C + c];
+        atomicAdd(&sums[(per_image ? (size_t)img * C : 0) + c], (double)t);
+    }
+}
+
+}  // namespace vu
+
+using namespace vu;
+
+#define VU_TB_ALIGN(cond, what) if (cond) return set_error(VU_ERR_ALIGN, what ": channel counts/offsets must be multiples of 8")
+
+extern "C" int vu_maxpool_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, int x_ctot, int x_coff,
+                              int dy_ctot, int dy_coff, int dx_ctot, int dx_coff, int k, int s, int p, int dtype,
+                              vu_stream_t st) {
+    if (!x || !dy || !dx) return set_error(VU_ERR_INVALID, "maxpool_bwd: null");
+    VU_TB_ALIGN((C | x_ctot | x_coff | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "maxpool_bwd");
+    const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+    maxpool_bwd_kernel<<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+        (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W,
+        C / 8, k, s, p, Ho, Wo, dtype);
+    VU_CHECK_LAUNCH("maxpool_bwd");
+    return 0;
+}
+
+extern "C" int vu_bilinear_ac_bwd(const void* dy, void* dx, int N, int Hs, int Ws, int C, int Ho, int Wo, int dy_ctot,
+                                  int dy_coff, int dx_ctot, int dx_coff, int accumulate, int dtype, vu_stream_t st) {
+    if (!dy || !dx) return set_error(VU_ERR_INVALID, "bilinear_bwd: null");
+    VU_TB_ALIGN((C | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "bilinear_bwd");
+    const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
+    const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
+    bilinear_bwd_kernel<<<tb_grid((size_t)N * Hs * Ws * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+        (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, C / 8, sh, sw, accumulate,
+        dtype);
+    VU_CHECK_LAUNCH("bilinear_bwd");
+    return 0;
+}
+
+extern "C" int vu_resize_map_bwd(const float* dy, float* dx, int N, int Hs, int Ws, int Ho, int Wo, vu_stream_t st) {
+    if (!dy || !dx) return set_error(VU_ERR_INVALID, "resize_map_bwd: null");
+    const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
+    const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
+    resize_map_bwd_kernel<<<tb_grid((size_t)N * Hs * Ws), 256, 0, (cudaStream_t)st>>>(dy, dx, N, Hs, Ws, Ho, Wo, sh, sw);
+    VU_CHECK_LAUNCH("resize_map_bwd");
+    return 0;
+}
+
+extern "C" int vu_scale_by_map(const void* a, int a_ctot, int a_coff, const float* m, void* out, int o_ctot, int o_coff,
+                               size_t npix, int C, int accumulate, int dtype, vu_stream_t st) {
+    if (!a || !m || !out) return set_error(VU_ERR_INVALID, "scale_by_map: null");
+    VU_TB_ALIGN((C | a_ctot | a_coff | o_ctot | o_coff) % 8, "scale_by_map");
+    scale_by_map_kernel<<<tb_grid(npix * (C / 8)), 256, 0, (cudaStream_t)st>>>((const uint16_t*)a, a_ctot, a_coff, m,
+                                                                              (uint16_t*)out, o_ctot, o_coff, npix, C / 8,
+                                                                              accumulate, dtype);
+    VU_CHECK_LAUNCH("scale_by_map");
+    return 0;
+}
+
+extern "C" int vu_channel_dot(const void* a, int a_ctot, int a_coff, const void* b, int b_ctot, int b_coff, float* out,
+                              size_t npix, int C, int dtype, vu_stream_t st) {
+    if (!a || !b || !out) return set_error(VU_ERR_INVALID, "channel_dot: null");
+    VU_TB_ALIGN((C | a_ctot | a_coff | b_ctot | b_coff) % 8, "channel_dot");
+    channel_dot_kernel<<<tb_grid(npix * 8), 256, 0, (cudaStream_t)st>>>((const uint16_t*)a, a_ctot, a_coff,
+                                                                       (const uint16_t*)b, b_ctot, b_coff, out, npix, C / 8,
+                                                                       dtype);
+    VU_CHECK_LAUNCH("channel_dot");
+    return 0;
+}
+
+extern "C" int vu_map_expand(const float* m, const float* w, const void* mask, int k_ctot, int k_coff, void* out,
+                             int o_ctot, int o_coff, size_t npix, int C, int dtype, vu_stream_t st) {
+    if (!m || !w || !out) return set_error(VU_ERR_INVALID, "map_expand: null");
+    VU_TB_ALIGN((C | k_ctot | k_coff | o_ctot | o_coff) % 8, "map_expand");
+    map_expand_kernel<<<tb_grid(npix * (C / 8)), 256, 0, (cudaStream_t)st>>>(m, w, (const uint16_t*)mask, k_ctot, k_coff,
+                                                                            (uint16_t*)out, o_ctot, o_coff, npix, C / 8, dtype);
+    VU_CHECK_LAUNCH("map_expand");
+    return 0;
+}
+
+extern "C" int vu_weighted_channel_sum(const void* x, int x_ctot, int x_coff, const float* m, int n_img, size_t pix_per_img,
+                                       int C, int per_image, double* sums, int dtype, vu_stream_t st) {
+    if (!x || !sums || C < 8 || C > 1024 || n_img < 1) return set_error(VU_ERR_INVALID, "weighted_channel_sum: bad args");
+    VU_TB_ALIGN((C | x_ctot | x_coff) % 8, "weighted_channel_sum");
+    const int C8 = C / 8, lanes = 256 / C8;
+    cudaStream_t s = (cudaStream_t)st;
+    cudaMemsetAsync(sums, 0, (size_t)(per_image ? n_img : 1) * C * sizeof(double), s);
+    int bpi = (int)((pix_per_img + (size_t)lanes * 16 - 1) / ((size_t)lanes * 16));
+    const int cap = (num_sms() * 4 + n_img - 1) / n_img;
+    if (bpi > cap) bpi = cap;
+    if (bpi < 1) bpi = 1;
+    weighted_channel_sum_kernel<<<n_img * bpi, 256, lanes * C * sizeof(float), s>>>((const uint16_t*)x, x_ctot, x_coff, m,
+                                                                                  pix_per_img, C8, per_image, bpi, sums, dtype);
+    VU_CHECK_LAUNCH("weighted_channel_sum");
+    return 0;
+}
