@@ -76,6 +76,13 @@ int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
  * dy is the 16-bit NHWC gradient of the conv output [N,Ho,Wo,dy_ctot]. dw is fp32 in the PACKED order
  * [Cout][KH*KW][Cin] and is ACCUMULATED into (K splits combine with atomics): zero it first. */
 int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
+/* Same, accumulated straight into the parameter's own OIHW layout dw[co][ci][r][s] (the .grad of nn.Conv2d.weight). */
+int vu_conv2d_wgrad_oihw(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
+/* Filter banks for the DATA gradient of conv2d(x, w) (w OIHW fp32; 3x3 p1 or 1x1 p0; stride 1|2), to be run by
+ * vu_conv2d_fwd on dY: stride 1 -> one bank [I][K*K][O] (taps rotated 180 degrees); stride 2, 1x1 -> one bank [I][1][O]
+ * (written to dX parity (0,0) with out_up = 2); stride 2, 3x3 -> four 3x3 p1 banks [ph*2+pc][I][9][O], one per parity of
+ * the dX pixel (out_up = 2, out_dh = ph, out_dw = pc). */
+int vu_pack_dgrad_weight(const float* w_oihw, void* banks, int O, int I, int K, int stride, int dtype, vu_stream_t stream);
 
 /* OIHW fp32 -> [O][KH*KW][I] 16-bit. transpose_io: weight is IOHW (ConvTranspose2d). */
 int vu_pack_conv_weight(const float* w_oihw, void* w_packed, int O, int I, int KH, int KW,
@@ -161,9 +168,10 @@ int vu_latent_project(const float* z, const float* w, const float* scale, const 
 
 /* ---------------------------------------------------------------- output head + uncertainty
  * final_conv 1x1 C->1 + bias on NHWC 16-bit -> fp32 logits [N,H,W] (unet_resnet.py:189,237;
- * OutConv unet/unet_parts.py:97-103 for n_classes = 1). */
+ * OutConv unet/unet_parts.py:97-103 for n_classes = 1). bias_dev (optional, device fp32[1]) is added to `bias`:
+ * the training step reads the live parameter without a host round trip. */
 int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_ctot, int x_coff,
-                   const float* w, float bias, float* logits, int dtype, vu_stream_t stream);
+                   const float* w, float bias, const float* bias_dev, float* logits, int dtype, vu_stream_t stream);
 /* bilinear (align_corners=True) resize of fp32 maps [N,Hs,Ws] -> [N,Ho,Wo], optional sigmoid
  * before (predict_with_patches order, visualize_vae.py:345-358) or after (forward /
  * predict_full_image order, unet_resnet.py:238; visualize_vae.py:81-83). mode: 0 none, 1 pre, 2 post */
@@ -227,8 +235,8 @@ int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const
                 void* y, int y_ctot, int y_coff, int dtype, vu_stream_t stream);
 int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot, int dy_coff,
               const void* y_relu, int y_ctot, int y_coff, const float* mean, const float* invstd, const float* gamma,
-              double* sums, void* dx, int dx_ctot, int dx_coff, void* dz_out, int dz_ctot, int dz_coff, int dtype,
-              vu_stream_t stream);
+              double* sums, void* dx, int dx_ctot, int dx_coff, void* dz_out, int dz_ctot, int dz_coff,
+              float* dgamma /* += , optional */, float* dbeta /* += */, int dtype, vu_stream_t stream);
 /* dst += src (gradient accumulation over the consumers of an activation). */
 int vu_add_nhwc(void* dst, int d_ctot, int d_coff, const void* src, int s_ctot, int s_coff, size_t npix, int C,
                 int dtype, vu_stream_t stream);
@@ -251,12 +259,13 @@ int vu_map_expand(const float* m, const float* w, const void* mask, int k_ctot, 
 int vu_weighted_channel_sum(const void* x, int x_ctot, int x_coff, const float* m, int n_img, size_t pix_per_img, int C,
                             int per_image, double* sums, int dtype, vu_stream_t stream);
 /* psi branch of the gate: single-channel train-mode BN + sigmoid on an fp32 map (unet_resnet.py:17-21) and its
- * backward (dx w.r.t. the pre-BN map; grads[0] = dgamma, grads[1] = dbeta). stat = {mean, invstd}; sums: fp64[2]. */
-int vu_map_bn_sigmoid_fwd(const float* x, size_t n, float gamma, float beta, float eps, float momentum,
+ * backward (dx w.r.t. the pre-BN map; dgamma[0] / dbeta[0] are accumulated into). stat = {mean, invstd}; sums: fp64[2];
+ * gamma / beta are device pointers to the live fp32 parameters (no host round trip inside a step). */
+int vu_map_bn_sigmoid_fwd(const float* x, size_t n, const float* gamma, const float* beta, float eps, float momentum,
                           float* running_mean, float* running_var, double* sums, float* stat, float* psi,
                           vu_stream_t stream);
-int vu_map_bn_sigmoid_bwd(const float* x, const float* dpsi, const float* psi, const float* stat, float gamma, size_t n,
-                          double* sums, float* dx, float* grads, vu_stream_t stream);
+int vu_map_bn_sigmoid_bwd(const float* x, const float* dpsi, const float* psi, const float* stat, const float* gamma, size_t n,
+                          double* sums, float* dx, float* dgamma /* += */, float* dbeta /* += */, vu_stream_t stream);
 int vu_map_sum(const float* x, size_t n, double* sums, vu_stream_t stream);   /* sums[0] = sum x, sums[1] = sum x^2 */
 /* Dense layer on M <= 64 vectors = 1x1 conv (+ train-mode BN over the rows) (+ ReLU) on spatially constant maps or
  * pooled features (z_initial, z_proj, mu/logvar heads). y_raw / mean / invstd are saved for the backward. */
@@ -265,7 +274,7 @@ int vu_vec_layer_fwd(const float* z, const float* w, const float* b, int M, int 
                      float* running_var, int relu, float* y_raw, float* y, float* mean, float* invstd, vu_stream_t stream);
 int vu_vec_layer_bwd(const float* dy, const float* z, const float* w, const float* y_raw, const float* y, int M, int L,
                      int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dz /* += */,
-                     float* dw, float* db, float* dgamma, float* dbeta, vu_stream_t stream);
+                     float* dw /* += */, float* db /* += */, float* dgamma /* += */, float* dbeta /* += */, vu_stream_t stream);
 /* z = mu + eps*exp(.5 logvar)*T: dmu += sum_s dz, dlogvar += sum_s dz*eps*.5*exp(.5 logvar)*T. */
 int vu_reparam_bwd(const float* dz, const float* eps, const float* logvar, float temperature, float* dmu,
                    float* dlogvar, size_t n_per_sample, int num_samples, vu_stream_t stream);

@@ -169,11 +169,12 @@ def test_gate_pieces_and_vec_layers(cuda_dev):
     dpsi = torch.randn(N, H, W, generator=g)
     psi_ref.backward(dpsi)
     rm_g, rv_g = torch.zeros(1, device=d), torch.ones(1, device=d)
-    psi, stat = T.map_bn_sigmoid_fwd(p_raw.to(d), 1.3, -0.2, rm_g, rv_g)
+    gam_d, bet_d = torch.tensor([1.3], device=d), torch.tensor([-0.2], device=d)
+    psi, stat = T.map_bn_sigmoid_fwd(p_raw.to(d), gam_d, bet_d, rm_g, rv_g)
     assert (psi.cpu() - psi_ref.detach()).abs().max() < 1e-5 and (rv_g.cpu() - rv).abs().max() < 1e-5
-    dx, grads = T.map_bn_sigmoid_bwd(p_raw.to(d), dpsi.to(d), psi, stat, 1.3)
+    dx, dgam, dbet = T.map_bn_sigmoid_bwd(p_raw.to(d), dpsi.to(d), psi, stat, gam_d)
     assert (dx.cpu() - pr.grad).abs().max() < 1e-5
-    assert abs(grads[0].item() - gam.grad.item()) < 1e-4 and abs(grads[1].item() - bet.grad.item()) < 1e-4
+    assert abs(dgam.item() - gam.grad.item()) < 1e-4 and abs(dbet.item() - bet.grad.item()) < 1e-4
     # dense vector layer with train-mode BN over the rows (z_initial / z_proj on constant maps)
     M, L, Cc = 6, 32, 80
     z = torch.randn(M, L, generator=g).requires_grad_(True)

@@ -40,6 +40,8 @@ SIGNATURES = {
     "vu_device_check": [],
     "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
     "vu_conv2d_wgrad": [C.POINTER(ConvArgs), p, i, i, p, p],
+    "vu_conv2d_wgrad_oihw": [C.POINTER(ConvArgs), p, i, i, p, p],
+    "vu_pack_dgrad_weight": [p, p, i, i, i, i, i, p],
     "vu_pack_conv_weight": [p, p, i, i, i, i, i, i, p],
     "vu_pack_convT2x2_weight": [p, p, i, i, i, p],
     "vu_nchw_to_nhwc": [p, p, i, i, i, i, i, i, i, p],
@@ -55,7 +57,7 @@ SIGNATURES = {
     "vu_latent_head": [p, i, i, i, i, i, i, p, p, p, p, p, f, i, i, p, p, p, i, p],
     "vu_reparameterize": [p, p, p, f, p, sz, i, p],
     "vu_latent_project": [p, p, p, p, p, i, i, i, i, p],
-    "vu_final_conv1": [p, i, i, i, i, i, i, p, f, p, i, p],
+    "vu_final_conv1": [p, i, i, i, i, i, i, p, f, p, p, i, p],
     "vu_resize_logits": [p, p, i, i, i, i, i, i, p],
     "vu_uncertainty_reduce": [p, i, i, i, i, i, i, i, p, p, p, p, p, p, p],
     "vu_moments_partial": [p, i, sz, p, p, p, p],
@@ -71,7 +73,7 @@ SIGNATURES = {
     "vu_bn_stats": [p, sz, i, i, i, p, i, p],
     "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
     "vu_bn_apply": [p, sz, i, i, i, p, p, p, p, p, i, i, i, p, i, i, i, p],
-    "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, i, p],
+    "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, i, p],
     "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],
     "vu_maxpool_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_bilinear_ac_bwd": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
@@ -80,8 +82,8 @@ SIGNATURES = {
     "vu_channel_dot": [p, i, i, p, i, i, p, sz, i, i, p],
     "vu_map_expand": [p, p, p, i, i, p, i, i, sz, i, i, p],
     "vu_weighted_channel_sum": [p, i, i, p, i, sz, i, i, p, i, p],
-    "vu_map_bn_sigmoid_fwd": [p, sz, f, f, f, f, p, p, p, p, p, p],
-    "vu_map_bn_sigmoid_bwd": [p, p, p, p, f, sz, p, p, p, p],
+    "vu_map_bn_sigmoid_fwd": [p, sz, p, p, f, f, p, p, p, p, p, p],
+    "vu_map_bn_sigmoid_bwd": [p, p, p, p, p, sz, p, p, p, p, p],
     "vu_map_sum": [p, sz, p, p],
     "vu_vec_layer_fwd": [p, p, p, i, i, i, p, p, f, f, C.c_double, p, p, i, p, p, p, p, p],
     "vu_vec_layer_bwd": [p, p, p, p, p, i, i, i, p, p, p, i, p, p, p, p, p, p],

@@ -25,7 +25,8 @@ struct WgradParams {
     int num_taps, num_m_tiles, num_n_tiles, ksplit, tiles_per_split;
     int cout, cin;
     int8_t tap_dh[kMaxTapsCommon], tap_dw[kMaxTapsCommon], tap_map[kMaxTapsCommon];
-    float* dw;                                    // [Cout][taps][Cin] fp32, accumulated atomically
+    float* dw;                                    // fp32, accumulated atomically: dw[co*co_stride + tap*tap_stride + ci*ci_stride]
+    int co_stride, tap_stride, ci_stride;         // packed [Cout][taps][Cin] or OIHW [Cout][Cin][taps]
     int dtype;
 };
 
@@ -150,10 +151,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
             tmem_ld_wait();
             const int ci0 = n_tile * BN + c * 32;
             if (co < p.cout) {
-                float* dst = p.dw + (static_cast<size_t>(co) * p.num_taps + tap) * p.cin + ci0;
+                float* dst = p.dw + static_cast<size_t>(co) * p.co_stride + tap * p.tap_stride + static_cast<size_t>(ci0) * p.ci_stride;
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    if (ci0 + j < p.cin) atomicAdd(dst + j, __uint_as_float(r[j]));
+                    if (ci0 + j < p.cin) atomicAdd(dst + j * p.ci_stride, __uint_as_float(r[j]));
             }
         }
     }
@@ -196,8 +197,8 @@ static int launch_wgrad(const CUtensorMap& dym, const CUtensorMap* xm, const Wgr
     return 0;
 }
 
-extern "C" int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw,
-                               vu_stream_t stream_) {
+static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, bool oihw,
+                      vu_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (!a || !a->x || !dy || !dw) return set_error(VU_ERR_INVALID, "wgrad: null pointer");
     const int KH = a->KH, KW = a->KW, S = a->stride, P = a->pad;
@@ -216,6 +217,8 @@ extern "C" int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_cto
     wp.num_taps = KH * KW;
     wp.cout = a->Cout; wp.cin = a->Cin;
     wp.dw = dw; wp.dtype = a->dtype;
+    if (oihw) { wp.co_stride = a->Cin * KH * KW; wp.tap_stride = 1; wp.ci_stride = KH * KW; }
+    else { wp.co_stride = KH * KW * a->Cin; wp.tap_stride = a->Cin; wp.ci_stride = 1; }
     const int bn = (a->Cin > 64) ? 128 : 64;
     wp.num_m_tiles = (a->Cout + 127) / 128;
     wp.num_n_tiles = (a->Cin + bn - 1) / bn;
@@ -273,4 +276,12 @@ extern "C" int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_cto
     const int grid = base_items * wp.ksplit;
     if (bn == 128) return launch_wgrad<128>(dym, xm, wp, grid, stream);
     return launch_wgrad<64>(dym, xm, wp, grid, stream);
+}
+
+extern "C" int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream) {
+    return wgrad_impl(a, dy, dy_ctot, dy_coff, dw, false, stream);
+}
+
+extern "C" int vu_conv2d_wgrad_oihw(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream) {
+    return wgrad_impl(a, dy, dy_ctot, dy_coff, dw, true, stream);
 }

@@ -132,7 +132,8 @@ __global__ void latent_project_kernel(const float* __restrict__ z, const float* 
 template <int G>
 __global__ void __launch_bounds__(256)
 final_conv1_kernel(const uint16_t* __restrict__ x, size_t npix, int x_ctot, int x_coff, const float* __restrict__ w,
-                   float bias, float* __restrict__ logits, int C8, int dtype) {
+                   float bias, const float* __restrict__ bias_dev, float* __restrict__ logits, int C8, int dtype) {
+    if (bias_dev) bias += bias_dev[0];
     const int sub = threadIdx.x % G;
     const size_t gid = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) / G;
     const size_t gstride = ((size_t)gridDim.x * blockDim.x) / G;
@@ -226,18 +227,18 @@ extern "C" int vu_latent_project(const float* z, const float* w, const float* sc
 }
 
 extern "C" int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_ctot, int x_coff, const float* w,
-                              float bias, float* logits, int dtype, vu_stream_t st) {
+                              float bias, const float* bias_dev, float* logits, int dtype, vu_stream_t st) {
     if (!x || !w || !logits) return set_error(VU_ERR_INVALID, "final_conv1: null");
     if (C % 8 || x_ctot % 8 || x_coff % 8) return set_error(VU_ERR_ALIGN, "final_conv1: channels %% 8");
     const size_t npix = (size_t)N * H * W;
     const int c8 = C / 8;
     cudaStream_t s = (cudaStream_t)st;
     if (c8 <= 4)
-        final_conv1_kernel<4><<<grid_cap((npix * 4 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+        final_conv1_kernel<4><<<grid_cap((npix * 4 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, bias_dev, logits, c8, dtype);
     else if (c8 <= 8)
-        final_conv1_kernel<8><<<grid_cap((npix * 8 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+        final_conv1_kernel<8><<<grid_cap((npix * 8 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, bias_dev, logits, c8, dtype);
     else
-        final_conv1_kernel<16><<<grid_cap((npix * 16 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, logits, c8, dtype);
+        final_conv1_kernel<16><<<grid_cap((npix * 16 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, bias_dev, logits, c8, dtype);
     VU_CHECK_LAUNCH("final_conv1");
     return 0;
 }

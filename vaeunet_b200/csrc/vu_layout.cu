@@ -17,6 +17,33 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, uint16_t* _
     }
 }
 
+// Filter banks of the DATA gradient of conv2d(x, w) (w OIHW, K x K, pad K/2), consumed by the forward conv kernels run on dY:
+//   stride 1: one bank [I][K*K][O], taps rotated by 180 degrees;  stride 2, K = 1: one bank [I][1][O];
+//   stride 2, K = 3: four 3x3 p1 banks [ph*2+pc][I][9][O], one per parity of the dX pixel (written by the pixel-shuffle
+//   store): row parity 0 takes filter row r = 1 at bank row 1; parity 1 takes r = 2 at bank row 1 and r = 0 at bank row 2.
+__device__ __forceinline__ int dgrad_s2_src(int parity, int bank_pos) {
+    if (parity == 0) return bank_pos == 1 ? 1 : -1;
+    return bank_pos == 1 ? 2 : (bank_pos == 2 ? 0 : -1);
+}
+__global__ void pack_dgrad_weight_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int O, int I, int K,
+                                         int stride, int nbanks, int dtype) {
+    const int T = K * K;
+    const size_t per_bank = (size_t)I * T * O;
+    const size_t total = per_bank * nbanks;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int o = idx % O;
+        const int t = (idx / O) % T;
+        const int i = (idx / ((size_t)O * T)) % I;
+        const int bank = idx / per_bank;
+        int r, s2;
+        if (stride == 1) { r = K - 1 - t / K; s2 = K - 1 - t % K; }
+        else if (K == 1) { r = 0; s2 = 0; }
+        else { r = dgrad_s2_src(bank >> 1, t / 3); s2 = dgrad_s2_src(bank & 1, t % 3); }
+        const float v = (r < 0 || s2 < 0) ? 0.f : w[(((size_t)o * I + i) * K + r) * K + s2];
+        out[idx] = f2h(v, dtype);
+    }
+}
+
 // ConvTranspose2d k2 s2: w [I][O][2][2] -> [4 (a*2+b)][O][I]
 __global__ void pack_convT_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int I, int O, int dtype) {
     const size_t total = (size_t)4 * O * I;
@@ -252,6 +279,17 @@ extern "C" int vu_pack_conv_weight(const float* w, void* out, int O, int I, int 
     pack_conv_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, KH * KW,
                                                                                transpose_io, dtype);
     VU_CHECK_LAUNCH("pack_conv_weight");
+    return 0;
+}
+
+extern "C" int vu_pack_dgrad_weight(const float* w, void* banks, int O, int I, int K, int stride, int dtype, vu_stream_t st) {
+    if (!w || !banks || O < 1 || I < 1) return set_error(VU_ERR_INVALID, "pack_dgrad_weight: bad args");
+    if (!((K == 3 || K == 1) && (stride == 1 || stride == 2)))
+        return set_error(VU_ERR_UNSUPPORTED, "pack_dgrad_weight: only 3x3 / 1x1, stride 1|2 (got k%d s%d)", K, stride);
+    const int nbanks = (stride == 2 && K == 3) ? 4 : 1;
+    const size_t total = (size_t)nbanks * O * I * K * K;
+    pack_dgrad_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)banks, O, I, K, stride, nbanks, dtype);
+    VU_CHECK_LAUNCH("pack_dgrad_weight");
     return 0;
 }
 

@@ -124,9 +124,12 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
                     int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const double* __restrict__ sums, double count, uint16_t* __restrict__ dx, int dx_ctot, int dx_coff,
-                    uint16_t* __restrict__ dz_out, int dz_ctot, int dz_coff, size_t npix, int C8, int dtype) {
+                    uint16_t* __restrict__ dz_out, int dz_ctot, int dz_coff, size_t npix, int C8, int dtype,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta) {
     const size_t total = npix * C8;
     const int C = C8 * 8;
+    if (blockIdx.x == 0 && dgamma != nullptr)      // parameter gradients, accumulated (gradient accumulation steps)
+        for (int c = threadIdx.x; c < C; c += blockDim.x) { dgamma[c] += (float)sums[C + c]; dbeta[c] += (float)sums[c]; }
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
         const int c8 = idx % C8;
         const size_t p = idx / C8;
@@ -212,8 +215,8 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
 extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot,
                          int dy_coff, const void* y_relu, int y_ctot, int y_coff, const float* mean,
                          const float* invstd, const float* gamma, double* sums, void* dx, int dx_ctot, int dx_coff,
-                         void* dz_out, int dz_ctot, int dz_coff, int dtype, vu_stream_t st) {
-    if (!x || !dy || !mean || !invstd || !gamma || !sums || !dx || C < 8 || C > 1024)
+                         void* dz_out, int dz_ctot, int dz_coff, float* dgamma, float* dbeta, int dtype, vu_stream_t st) {
+    if (!x || !dy || !mean || !invstd || !gamma || !sums || !dx || C < 8 || C > 1024 || (!dgamma != !dbeta))
         return set_error(VU_ERR_INVALID, "bn_bwd: bad args");
     VU_TR_ALIGN((C | x_ctot | x_coff | dy_ctot | dy_coff | y_ctot | y_coff | dx_ctot | dx_coff | dz_ctot | dz_coff) % 8, "bn_bwd");
     const int C8 = C / 8, lanes = 256 / C8;
@@ -226,7 +229,7 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
     bn_bwd_apply_kernel<<<tr_grid(npix * C8, 256), 256, 0, s>>>(
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
         mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
-        C8, dtype);
+        C8, dtype, dgamma, dbeta);
     VU_CHECK_LAUNCH("bn_bwd_apply");
     return 0;
 }

@@ -51,21 +51,23 @@ __global__ void map_bn_finalize_kernel(const double* sums, double count, float e
     }
 }
 
-__global__ void map_bn_sigmoid_apply_kernel(const float* __restrict__ x, const float* __restrict__ stat, float gamma,
-                                            float beta, float* __restrict__ psi, size_t n) {
-    const float mean = stat[0], invstd = stat[1];
+__global__ void map_bn_sigmoid_apply_kernel(const float* __restrict__ x, const float* __restrict__ stat,
+                                            const float* __restrict__ gamma_p, const float* __restrict__ beta_p,
+                                            float* __restrict__ psi, size_t n) {
+    const float mean = stat[0], invstd = stat[1], gamma = gamma_p[0], beta = beta_p[0];
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         psi[i] = 1.0f / (1.0f + expf(-((x[i] - mean) * invstd * gamma + beta)));
 }
 
 // dx = gamma * invstd * (dp - mean(dp) - ph * mean(dp * ph));  grads[0] = dgamma = sum dp*ph, grads[1] = dbeta = sum dp
 __global__ void map_bn_sigmoid_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dpsi,
-                                          const float* __restrict__ psi, const float* __restrict__ stat, float gamma,
+                                          const float* __restrict__ psi, const float* __restrict__ stat,
+                                          const float* __restrict__ gamma_p,
                                           const double* __restrict__ sums, double count, float* __restrict__ dx,
-                                          float* __restrict__ grads, size_t n) {
-    const float mean = stat[0], invstd = stat[1];
+                                          float* __restrict__ dgamma, float* __restrict__ dbeta, size_t n) {
+    const float mean = stat[0], invstd = stat[1], gamma = gamma_p[0];
     const float m0 = (float)(sums[0] / count), m1 = (float)(sums[1] / count);
-    if (blockIdx.x == 0 && threadIdx.x == 0) { grads[0] = (float)sums[1]; grads[1] = (float)sums[0]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { dgamma[0] += (float)sums[1]; dbeta[0] += (float)sums[0]; }
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const float s = psi[i], dp = dpsi[i] * s * (1.f - s);
         dx[i] = gamma * invstd * (dp - m0 - (x[i] - mean) * invstd * m1);
@@ -120,8 +122,8 @@ vec_layer_fwd_kernel(const float* __restrict__ z, const float* __restrict__ w, c
     }
 }
 
-// dy -> (ReLU mask from y) -> BN backward over the M rows -> dy_raw; dw[c,l] = sum_m dy_raw z, db[c] = sum_m dy_raw,
-// dgamma / dbeta; dz[m,l] += sum_c dy_raw[m,c] w[c,l] (atomics across the channel blocks).
+// dy -> (ReLU mask from y) -> BN backward over the M rows -> dy_raw; dw[c,l] += sum_m dy_raw z, db[c] += sum_m dy_raw,
+// dgamma / dbeta += (parameter gradients accumulate); dz[m,l] += sum_c dy_raw[m,c] w[c,l] (atomics across the channel blocks).
 __global__ void __launch_bounds__(256)
 vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ w,
                      const float* __restrict__ y_raw, const float* __restrict__ y, int M, int L, int C,
@@ -148,7 +150,7 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
                 const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
                 s0 += s_d[m][cl]; s1 += (double)s_d[m][cl] * xh;
             }
-            if (dgamma) { dgamma[c] = (float)s1; dbeta[c] = (float)s0; }
+            if (dgamma) { dgamma[c] += (float)s1; dbeta[c] += (float)s0; }
             const float m0 = (float)(s0 / M), m1 = (float)(s1 / M);
             for (int m = 0; m < M; ++m) {
                 const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
@@ -158,7 +160,7 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
         if (db) {
             float s = 0.f;
             for (int m = 0; m < M; ++m) s += s_d[m][cl];
-            db[c] = s;
+            db[c] += s;
         }
     }
     __syncthreads();
@@ -168,7 +170,7 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
             if (c >= C) continue;
             float acc = 0.f;
             for (int m = 0; m < M; ++m) acc = fmaf(s_d[m][cl], z[(size_t)m * L + l], acc);
-            dw[(size_t)c * L + l] = acc;
+            dw[(size_t)c * L + l] += acc;
         }
     if (dz != nullptr)
         for (int i = threadIdx.x; i < M * L; i += 256) {
@@ -275,10 +277,10 @@ static int ts_grid(size_t n) {
 
 using namespace vu;
 
-extern "C" int vu_map_bn_sigmoid_fwd(const float* x, size_t n, float gamma, float beta, float eps, float momentum,
+extern "C" int vu_map_bn_sigmoid_fwd(const float* x, size_t n, const float* gamma, const float* beta, float eps, float momentum,
                                      float* running_mean, float* running_var, double* sums, float* stat, float* psi,
                                      vu_stream_t st) {
-    if (!x || !sums || !stat || !psi || n < 1) return set_error(VU_ERR_INVALID, "map_bn_sigmoid_fwd: bad args");
+    if (!x || !sums || !stat || !psi || !gamma || !beta || n < 1) return set_error(VU_ERR_INVALID, "map_bn_sigmoid_fwd: bad args");
     cudaStream_t s = (cudaStream_t)st;
     cudaMemsetAsync(sums, 0, 2 * sizeof(double), s);
     map_sums_kernel<0><<<ts_grid(n), 256, 0, s>>>(x, nullptr, nullptr, nullptr, n, sums);
@@ -288,13 +290,13 @@ extern "C" int vu_map_bn_sigmoid_fwd(const float* x, size_t n, float gamma, floa
     return 0;
 }
 
-extern "C" int vu_map_bn_sigmoid_bwd(const float* x, const float* dpsi, const float* psi, const float* stat, float gamma,
-                                     size_t n, double* sums, float* dx, float* grads, vu_stream_t st) {
-    if (!x || !dpsi || !psi || !stat || !sums || !dx || !grads) return set_error(VU_ERR_INVALID, "map_bn_sigmoid_bwd: null");
+extern "C" int vu_map_bn_sigmoid_bwd(const float* x, const float* dpsi, const float* psi, const float* stat, const float* gamma,
+                                     size_t n, double* sums, float* dx, float* dgamma, float* dbeta, vu_stream_t st) {
+    if (!x || !dpsi || !psi || !stat || !gamma || !sums || !dx || !dgamma || !dbeta) return set_error(VU_ERR_INVALID, "map_bn_sigmoid_bwd: null");
     cudaStream_t s = (cudaStream_t)st;
     cudaMemsetAsync(sums, 0, 2 * sizeof(double), s);
     map_sums_kernel<1><<<ts_grid(n), 256, 0, s>>>(x, dpsi, psi, stat, n, sums);
-    map_bn_sigmoid_bwd_kernel<<<ts_grid(n), 256, 0, s>>>(x, dpsi, psi, stat, gamma, sums, (double)n, dx, grads, n);
+    map_bn_sigmoid_bwd_kernel<<<ts_grid(n), 256, 0, s>>>(x, dpsi, psi, stat, gamma, sums, (double)n, dx, dgamma, dbeta, n);
     VU_CHECK_LAUNCH("map_bn_sigmoid_bwd");
     return 0;
 }

@@ -155,20 +155,32 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
     return out
 
 
-def conv2d_wgrad(x: Act, dy: Act, k: int, stride: int, pad: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """dW of conv2d(x, W): fp32 [Cout, k*k, Cin] in the packed tap order (accumulates into `out` if given)."""
+def conv2d_wgrad(x: Act, dy: Act, k: int, stride: int, pad: int, out: Optional[torch.Tensor] = None,
+                 oihw: bool = False) -> torch.Tensor:
+    """dW of conv2d(x, W), fp32, ACCUMULATED into `out` if given: packed tap order [Cout, k*k, Cin], or (oihw) the
+    parameter's own layout [Cout, Cin, k, k]."""
     require_device()
     Cout = dy.C
     Ho = (x.H + 2 * pad - k) // stride + 1
     Wo = (x.W + 2 * pad - k) // stride + 1
     assert (dy.N, dy.H, dy.W) == (x.N, Ho, Wo) and dy.dt == x.dt, "wgrad: dy shape"
+    shape = (Cout, x.C, k, k) if oihw else (Cout, k * k, x.C)
     if out is None:
-        out = torch.zeros((Cout, k * k, x.C), dtype=torch.float32, device=x.t.device)
-    assert out.shape == (Cout, k * k, x.C) and out.dtype == torch.float32 and out.is_contiguous()
+        out = torch.zeros(shape, dtype=torch.float32, device=x.t.device)
+    assert tuple(out.shape) == shape and out.dtype == torch.float32 and out.is_contiguous()
     a = ConvArgs()
     a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
     a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad; a.dtype = x.dt
-    check(load().vu_conv2d_wgrad(C.byref(a), dy.t.data_ptr(), dy.ctot, dy.coff, out.data_ptr(), _stream()), "vu_conv2d_wgrad")
+    fn = load().vu_conv2d_wgrad_oihw if oihw else load().vu_conv2d_wgrad
+    if CONV_TIMING is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(fn(C.byref(a), dy.t.data_ptr(), dy.ctot, dy.coff, out.data_ptr(), _stream()), "vu_conv2d_wgrad")
+        e1.record()
+        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * k * k * x.C,
+                            f"wgrad N{x.N} {x.H}x{x.W} Cin{x.C} Cout{Cout} k{k} s{stride}"))
+    else:
+        check(fn(C.byref(a), dy.t.data_ptr(), dy.ctot, dy.coff, out.data_ptr(), _stream()), "vu_conv2d_wgrad")
     _count()
     return out
 
@@ -179,29 +191,21 @@ def unpack_wgrad(dw_packed: torch.Tensor, k: int) -> torch.Tensor:
     return dw_packed.reshape(O, k, k, I).permute(0, 3, 1, 2).contiguous()
 
 
-def pack_dgrad_weights(w: torch.Tensor, stride: int, dtype=BF16):
-    """Filter banks for the data gradient of conv2d(x, w) (w OIHW, 3x3 p1 or 1x1 p0), run by vu_conv2d_fwd on dY:
-    stride 1: one bank = w rotated by 180 degrees with in/out swapped;
-    stride 2: one bank per output-pixel parity (ph, pc) of dX, written with the pixel-shuffle store (out_up = 2).
-    For 3x3 the parity banks are 3x3 p1 banks with the unused taps zero: dX[2k+ph] takes r = 1 at offset 0 (ph = 0)
-    or r = 2 at offset 0 and r = 0 at offset +1 (ph = 1)."""
+def pack_dgrad_weights(w: torch.Tensor, stride: int, dtype=BF16, out: Optional[torch.Tensor] = None):
+    """Filter banks for the data gradient of conv2d(x, w) (w OIHW fp32, 3x3 p1 or 1x1 p0), run by vu_conv2d_fwd on dY
+    (vu_pack_dgrad_weight): stride 1 -> one bank (w rotated by 180 degrees, in/out swapped); stride 2 -> one bank per
+    output-pixel parity (ph, pc) of dX, written with the pixel-shuffle store (out_up = 2). Returns the list of banks
+    (views of one [nbanks, I, k*k, O] tensor, `out` if given)."""
+    require_device()
+    w = _f32(w.detach())
     O, I, k, _ = w.shape
-    wt = w.detach().float().transpose(0, 1)                    # [I, O, k, k]
-    if stride == 1:
-        return [pack_conv_weight(wt.flip(2, 3).contiguous(), dtype)]
-    assert stride == 2
-    if k == 1:
-        return [pack_conv_weight(wt.contiguous(), dtype)]       # only parity (0, 0) is non-zero
-    banks = []
-    taps = {0: [(1, 1)], 1: [(2, 1), (0, 2)]}                   # parity -> [(r of w, r' of the 3x3 p1 bank)]
-    for ph in range(2):
-        for pc in range(2):
-            b = torch.zeros((I, O, 3, 3), dtype=torch.float32, device=w.device)
-            for (r, rp) in taps[ph]:
-                for (s, sp) in taps[pc]:
-                    b[:, :, rp, sp] = wt[:, :, r, s]
-            banks.append(pack_conv_weight(b, dtype))
-    return banks
+    nb = 4 if (stride == 2 and k == 3) else 1
+    if out is None:
+        out = torch.empty((nb, I, k * k, O), dtype=_TORCH_DT[dtype], device=w.device)
+    assert tuple(out.shape) == (nb, I, k * k, O)
+    check(load().vu_pack_dgrad_weight(w.data_ptr(), out.data_ptr(), O, I, k, stride, dtype, _stream()), "vu_pack_dgrad_weight")
+    _count()
+    return [out[b] for b in range(nb)]
 
 
 def conv2d_dgrad(dy: Act, banks, k: int, stride: int, H: int, W: int, out: Optional[Act] = None,
@@ -396,12 +400,14 @@ def latent_project(z: torch.Tensor, w: torch.Tensor, scale: Optional[torch.Tenso
     return v
 
 
-def final_conv1(x: Act, w: torch.Tensor, bias: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+def final_conv1(x: Act, w: torch.Tensor, bias: float, out: Optional[torch.Tensor] = None,
+                bias_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bias_dev: device fp32[1] added to `bias` (training reads the live parameter without a host sync)."""
     require_device()
     if out is None:
         out = torch.empty((x.N, x.H, x.W), dtype=torch.float32, device=x.t.device)
     check(load().vu_final_conv1(x.t.data_ptr(), x.N, x.H, x.W, x.C, x.ctot, x.coff, _f32(w).data_ptr(), float(bias),
-                                out.data_ptr(), x.dt, _stream()), "vu_final_conv1")
+                                _ptr(bias_dev), out.data_ptr(), x.dt, _stream()), "vu_final_conv1")
     _count()
     return out
 

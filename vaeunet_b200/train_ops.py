@@ -45,23 +45,26 @@ def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, res
 
 
 def bn_train_bwd(x_raw: Act, dy: Act, y_relu: Optional[Act], mean, invstd, gamma, want_dz: bool = False,
-                 dx: Optional[Act] = None):
-    """-> (dx_raw, dgamma, dbeta, dz or None). y_relu: the post-ReLU output (mask) or None when there was no ReLU."""
+                 dx: Optional[Act] = None, dgamma: Optional[torch.Tensor] = None, dbeta: Optional[torch.Tensor] = None):
+    """-> (dx_raw, dgamma, dbeta, dz or None). y_relu: the post-ReLU output (mask) or None when there was no ReLU.
+    dgamma / dbeta (fp32 [C]) are ACCUMULATED into when given (the parameters' .grad), else returned fresh."""
     require_device()
     Cc, dev = x_raw.C, x_raw.t.device
     sums = _sums(dev, 2 * Cc)
     if dx is None:
         dx = ops.new_act(x_raw.N, x_raw.H, x_raw.W, Cc, x_raw.dt, dev)
+    if dgamma is None:
+        dgamma = torch.zeros(Cc, dtype=torch.float32, device=dev)
+        dbeta = torch.zeros(Cc, dtype=torch.float32, device=dev)
     dz = ops.new_act(x_raw.N, x_raw.H, x_raw.W, Cc, x_raw.dt, dev) if want_dz else None
     y = y_relu
     check(load().vu_bn_bwd(x_raw.t.data_ptr(), _npix(x_raw), Cc, x_raw.ctot, x_raw.coff, dy.t.data_ptr(), dy.ctot, dy.coff,
                            y.t.data_ptr() if y else None, y.ctot if y else 8, y.coff if y else 0, mean.data_ptr(),
                            invstd.data_ptr(), _f32(gamma).data_ptr(), sums.data_ptr(), dx.t.data_ptr(), dx.ctot, dx.coff,
-                           dz.t.data_ptr() if dz else None, dz.ctot if dz else 8, dz.coff if dz else 0, x_raw.dt, _stream()),
-          "vu_bn_bwd")
+                           dz.t.data_ptr() if dz else None, dz.ctot if dz else 8, dz.coff if dz else 0,
+                           _f32(dgamma).data_ptr(), _f32(dbeta).data_ptr(), x_raw.dt, _stream()), "vu_bn_bwd")
     _count(3)
-    s = sums[:2 * Cc].float()
-    return dx, s[Cc:].contiguous(), s[:Cc].contiguous(), dz
+    return dx, dgamma, dbeta, dz
 
 
 def add_(dst: Act, src: Act) -> Act:
@@ -141,30 +144,34 @@ def weighted_channel_sum(x: Act, m: Optional[torch.Tensor], per_image: bool) -> 
     return out.reshape(x.N, x.C) if per_image else out
 
 
-def map_bn_sigmoid_fwd(x: torch.Tensor, gamma: float, beta: float, running_mean, running_var):
+def map_bn_sigmoid_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, running_mean, running_var):
+    """gamma / beta: device fp32[1] (the live psi.1 parameters)."""
     require_device()
     x = _f32(x)
     sums = _sums(x.device, 2)
     stat = torch.empty(2, dtype=torch.float32, device=x.device)
     psi = torch.empty_like(x)
-    check(load().vu_map_bn_sigmoid_fwd(x.data_ptr(), x.numel(), float(gamma), float(beta), BN_EPS, BN_MOMENTUM,
+    check(load().vu_map_bn_sigmoid_fwd(x.data_ptr(), x.numel(), _f32(gamma).data_ptr(), _f32(beta).data_ptr(), BN_EPS, BN_MOMENTUM,
                                        _ptr(running_mean), _ptr(running_var), sums.data_ptr(), stat.data_ptr(), psi.data_ptr(),
                                        _stream()), "vu_map_bn_sigmoid_fwd")
     _count(4)
     return psi, stat
 
 
-def map_bn_sigmoid_bwd(x, dpsi, psi, stat, gamma: float):
-    """-> (dx, grads[2] = (dgamma, dbeta))."""
+def map_bn_sigmoid_bwd(x, dpsi, psi, stat, gamma: torch.Tensor, dgamma: Optional[torch.Tensor] = None,
+                       dbeta: Optional[torch.Tensor] = None):
+    """-> (dx, dgamma[1], dbeta[1]); dgamma / dbeta are accumulated into when given."""
     require_device()
     sums = _sums(x.device, 2)
     dx = torch.empty_like(x)
-    grads = torch.empty(2, dtype=torch.float32, device=x.device)
+    if dgamma is None:
+        dgamma = torch.zeros(1, dtype=torch.float32, device=x.device)
+        dbeta = torch.zeros(1, dtype=torch.float32, device=x.device)
     check(load().vu_map_bn_sigmoid_bwd(_f32(x).data_ptr(), _f32(dpsi).data_ptr(), _f32(psi).data_ptr(), stat.data_ptr(),
-                                       float(gamma), x.numel(), sums.data_ptr(), dx.data_ptr(), grads.data_ptr(), _stream()),
-          "vu_map_bn_sigmoid_bwd")
+                                       _f32(gamma).data_ptr(), x.numel(), sums.data_ptr(), dx.data_ptr(),
+                                       _f32(dgamma).data_ptr(), _f32(dbeta).data_ptr(), _stream()), "vu_map_bn_sigmoid_bwd")
     _count(3)
-    return dx, grads
+    return dx, dgamma, dbeta
 
 
 def map_sum(x: torch.Tensor) -> torch.Tensor:
@@ -193,17 +200,22 @@ def vec_layer_fwd(z, w, b, gamma, beta, running_mean, running_var, relu: bool, s
     return y, (z, y_raw, y, mean, invstd)
 
 
-def vec_layer_bwd(dy, saved, w, gamma, relu: bool, dz: Optional[torch.Tensor], want_bias: bool):
-    """-> (dw [C,L], db or None, dgamma or None, dbeta or None); dz (if given) is accumulated into."""
+def vec_layer_bwd(dy, saved, w, gamma, relu: bool, dz: Optional[torch.Tensor], want_bias: bool, dw=None, db=None, dg=None,
+                  dbeta=None):
+    """-> (dw [C,L], db or None, dgamma or None, dbeta or None); dz and any gradient buffer passed in are accumulated into."""
     require_device()
     z, y_raw, y, mean, invstd = saved
     M, L = z.shape
     Cc = w.shape[0]
     dev = z.device
-    dw = torch.empty((Cc, L), dtype=torch.float32, device=dev)
-    db = torch.empty(Cc, dtype=torch.float32, device=dev) if want_bias else None
-    dg = torch.empty(Cc, dtype=torch.float32, device=dev) if gamma is not None else None
-    dbeta = torch.empty(Cc, dtype=torch.float32, device=dev) if gamma is not None else None
+    zeros = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+    if dw is None:
+        dw = zeros(Cc, L)
+    if db is None and want_bias:
+        db = zeros(Cc)
+    if gamma is not None and dg is None:
+        dg, dbeta = zeros(Cc), zeros(Cc)
+    assert dw.numel() == Cc * L and dw.is_contiguous()
     check(load().vu_vec_layer_bwd(_f32(dy.contiguous()).data_ptr(), z.data_ptr(), _f32(w).data_ptr(), y_raw.data_ptr(),
                                   y.data_ptr(), M, L, Cc, _ptr(gamma), _ptr(mean), _ptr(invstd), int(relu), _ptr(dz),
                                   dw.data_ptr(), _ptr(db), _ptr(dg), _ptr(dbeta), _stream()), "vu_vec_layer_bwd")
@@ -234,11 +246,13 @@ def stem_conv_raw(x: torch.Tensor, w: torch.Tensor, dtype) -> Act:
     return out
 
 
-def stem_wgrad(x: torch.Tensor, dy: Act, Cout: int) -> torch.Tensor:
+def stem_wgrad(x: torch.Tensor, dy: Act, out) -> torch.Tensor:
+    """dW [Cout, Cin, 7, 7] of the stem conv, ACCUMULATED into `out` (an fp32 tensor; an int Cout allocates zeros)."""
     require_device()
     x = _f32(x.float().contiguous())
     N, Cin, H, W = x.shape
-    dw = torch.zeros((Cout, Cin, 7, 7), dtype=torch.float32, device=x.device)
+    dw = torch.zeros((out, Cin, 7, 7), dtype=torch.float32, device=x.device) if isinstance(out, int) else _f32(out)
+    Cout = dw.shape[0]
     check(load().vu_stem_wgrad(x.data_ptr(), dy.t.data_ptr(), dy.ctot, dy.coff, dw.data_ptr(), N, Cin, H, W, Cout, dy.dt,
                                _stream()), "vu_stem_wgrad")
     _count()
