@@ -243,6 +243,12 @@ int vu_add_nhwc(void* dst, int d_ctot, int d_coff, const void* src, int s_ctot, 
 /* Backward of vu_maxpool_nhwc (first maximum wins, as ATen) and of vu_bilinear_ac_nhwc / vu_resize_logits (gathers). */
 int vu_maxpool_bwd(const void* x, const void* dy, void* dx, int N, int H, int W, int C, int x_ctot, int x_coff,
                    int dy_ctot, int dy_coff, int dx_ctot, int dx_coff, int k, int s, int p, int dtype, vu_stream_t stream);
+/* Max-pool that also saves, per output element, the window position r*k+q of its first maximum (uint8 [N,Ho,Wo,C]),
+ * and the backward as a gather over those codes (training fast path; same results as vu_maxpool_nhwc / vu_maxpool_bwd). */
+int vu_maxpool_idx_fwd(const void* x, void* y, void* code, int N, int H, int W, int C, int x_ctot, int x_coff,
+                       int y_ctot, int y_coff, int k, int s, int p, int dtype, vu_stream_t stream);
+int vu_maxpool_idx_bwd(const void* code, const void* dy, void* dx, int N, int H, int W, int C, int dy_ctot, int dy_coff,
+                       int dx_ctot, int dx_coff, int k, int s, int p, int dtype, vu_stream_t stream);
 int vu_bilinear_ac_bwd(const void* dy, void* dx, int N, int Hs, int Ws, int C, int Ho, int Wo, int dy_ctot, int dy_coff,
                        int dx_ctot, int dx_coff, int accumulate, int dtype, vu_stream_t stream);
 int vu_resize_map_bwd(const float* dy, float* dx, int N, int Hs, int Ws, int Ho, int Wo, vu_stream_t stream);
@@ -278,6 +284,13 @@ int vu_vec_layer_bwd(const float* dy, const float* z, const float* w, const floa
 /* z = mu + eps*exp(.5 logvar)*T: dmu += sum_s dz, dlogvar += sum_s dz*eps*.5*exp(.5 logvar)*T. */
 int vu_reparam_bwd(const float* dz, const float* eps, const float* logvar, float temperature, float* dmu,
                    float* dlogvar, size_t n_per_sample, int num_samples, vu_stream_t stream);
+/* Training path of the ResNet stem on the tensor cores: patch matrix out[n,ho,wo, ci*K*K + r*K + s] (16-bit NHWC with
+ * Kp >= Cin*K*K channels, Kp % 8 == 0, zero padded) of an NCHW fp32 image, so that the 7x7 s2 conv is vu_conv2d_fwd
+ * (1x1) over it with the filter rows from vu_pack_rows_padded ([O][I] fp32 -> [O][I_pad] 16-bit), and its weight
+ * gradient is vu_conv2d_wgrad (1x1) of (patches, dY). */
+int vu_im2col_small_cin(const float* x_nchw, void* out, int N, int Cin, int H, int W, int K, int S, int P, int Kp,
+                        int dtype, vu_stream_t stream);
+int vu_pack_rows_padded(const float* w, void* out, int O, int I, int I_pad, int dtype, vu_stream_t stream);
 /* Weight gradient of the ResNet stem conv 7x7 s2 p3 (Cin <= 4): dw [Cout][Cin][7][7] fp32, ACCUMULATED (zero it). */
 int vu_stem_wgrad(const float* x_nchw, const void* dy, int dy_ctot, int dy_coff, float* dw, int N, int Cin, int H, int W,
                   int Cout, int dtype, vu_stream_t stream);

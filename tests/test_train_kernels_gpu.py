@@ -127,6 +127,16 @@ def test_maxpool_bilinear_bwd(cuda_dev):
     y.backward(dy)
     dx = T.maxpool_bwd(_act(ops, x, d), _act(ops, dy, d), 3, 2, 1)
     assert (_nchw(dx) - xr.grad).abs().max() <= 1e-2 * xr.grad.abs().max()
+    # saved-argmax variant (training fast path), with ties: ReLU'd input has many all-zero windows
+    xz = _q(torch.relu(torch.randn(2, 16, 13, 14, generator=g) - 0.8))
+    xzr = xz.clone().requires_grad_(True)
+    yz = F.max_pool2d(xzr, 3, 2, 1)
+    dyz = _q(torch.randn(yz.shape, generator=g))
+    yz.backward(dyz)
+    y2, code = T.maxpool_idx_fwd(_act(ops, xz, d), 3, 2, 1)
+    assert (_nchw(y2) - yz.detach()).abs().max() == 0
+    dx2 = T.maxpool_idx_bwd(code, _act(ops, dyz, d), 13, 14, 3, 2, 1)
+    assert (_nchw(dx2) - xzr.grad).abs().max() <= 1e-2 * xzr.grad.abs().max()
     for (hs, ws, ho, wo) in [(8, 8, 16, 16), (11, 9, 22, 17), (1, 1, 5, 6), (16, 16, 32, 32)]:
         x = torch.randn(2, 24, hs, ws, generator=g).requires_grad_(True)
         y = F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
@@ -209,6 +219,19 @@ def test_stem_wgrad_and_adamw(cuda_dev):
     assert (_nchw(raw) - y.detach()).abs().max() <= 1e-2 * y.detach().abs().max()
     dw = T.stem_wgrad(x.to(d), _act(ops, dy, d), 64).cpu()
     assert ((dw - w.grad).norm() / w.grad.norm()).item() < 1e-4
+    # tensor-core route: im2col patches (147 -> 152 columns) x 1x1 bank, forward and weight gradient
+    xq = _q(x)
+    yq = F.conv2d(xq, _q(w.detach()), None, 2, 3)
+    wq = _q(w.detach()).clone().requires_grad_(True)
+    F.conv2d(xq, wq, None, 2, 3).backward(dy)
+    xcol = T.im2col_small_cin(x.to(d), 7, 2, 3, ops.BF16)
+    assert xcol.C == 152
+    w16 = T.pack_rows_padded(w.detach().to(d), 152, ops.BF16)
+    y_tc = ops.conv2d(xcol, w16, 1, 1, 0, None, None, False)
+    assert ((_nchw(y_tc) - yq).norm() / yq.norm()).item() < 4e-3
+    dw_tc = ops.conv2d_wgrad(xcol, _act(ops, dy, d), 1, 1, 0).cpu().view(64, 152)
+    assert dw_tc[:, 147:].abs().max().item() == 0
+    assert ((dw_tc[:, :147].reshape(64, 3, 7, 7) - wq.grad).norm() / wq.grad.norm()).item() < 2e-4
     # AdamW with gradient clipping, two steps
     n = 1000
     p0 = torch.randn(n, generator=g); g1 = torch.randn(n, generator=g) * 3

@@ -76,6 +76,8 @@ SIGNATURES = {
     "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, i, p],
     "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],
     "vu_maxpool_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_maxpool_idx_fwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
+    "vu_maxpool_idx_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_bilinear_ac_bwd": [p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_resize_map_bwd": [p, p, i, i, i, i, i, p],
     "vu_scale_by_map": [p, i, i, p, p, i, i, sz, i, i, i, p],
@@ -88,6 +90,8 @@ SIGNATURES = {
     "vu_vec_layer_fwd": [p, p, p, i, i, i, p, p, f, f, C.c_double, p, p, i, p, p, p, p, p],
     "vu_vec_layer_bwd": [p, p, p, p, p, i, i, i, p, p, p, i, p, p, p, p, p, p],
     "vu_reparam_bwd": [p, p, p, f, p, p, sz, i, p],
+    "vu_im2col_small_cin": [p, p, i, i, i, i, i, i, i, i, i, p],
+    "vu_pack_rows_padded": [p, p, i, i, i, i, p],
     "vu_stem_wgrad": [p, p, i, i, p, i, i, i, i, i, i, p],
     "vu_sumsq": [p, sz, p, i, p],
     "vu_adamw_step": [p, p, p, p, sz, f, f, f, f, f, i, p, f, f, p],

@@ -187,10 +187,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
+                const int ch0 = n_tile * BN + c * 32;
+                if (ch0 >= p.cout) break;             // partial last N tile (Cout is a multiple of 32; warp-uniform)
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(taddr + c * 32, r);
                 tmem_ld_wait();
-                const int ch0 = n_tile * BN + c * 32;
                 uint32_t outw[16];
                 uint4 rv[4];
                 if (p.residual != nullptr && valid) {
@@ -319,14 +320,19 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     kp.out_h = Ho * up; kp.out_w = Wo * up;
     kp.relu = a->relu; kp.dtype = a->dtype;
 
-    // BN tile: largest of 256/128/64/32 dividing Cout
-    int bn = 256;
-    while (bn > 32 && (a->Cout % bn)) bn >>= 1;
+    // BN tile of 256/128/64/32 columns; the last N tile may be partial (filter rows beyond Cout are TMA zero fill, the
+    // epilogue skips them). A k-iteration is L2->SM bound, so pick the width that moves the fewest operand rows:
+    // n_tiles * (128 pixel rows + BN filter rows); ties go to the narrower tile (fewer wasted MMA columns).
+    int bn = 32;
+    long best = -1;
+    for (int cand = 32; cand <= 256; cand <<= 1) {
+        const long cost = (long)((a->Cout + cand - 1) / cand) * (128 + cand);
+        if (best < 0 || cost < best) { best = cost; bn = cand; }
+    }
     const int sms = num_sms();
-    // a k-iteration costs about the same for every BN (it is L2->SM bound), so prefer wide tiles; only drop
-    // from 256 to 128 columns when that is needed to reach one wave of tiles
-    while (bn > 128 && (long)kp.num_m_tiles * (a->Cout / bn) < sms) bn >>= 1;
-    kp.num_n_tiles = a->Cout / bn;
+    // only drop from 256 to 128 columns when that is needed to reach one wave of tiles
+    while (bn > 128 && (long)kp.num_m_tiles * ((a->Cout + bn - 1) / bn) < sms) bn >>= 1;
+    kp.num_n_tiles = (a->Cout + bn - 1) / bn;
 
     // activation tensor maps
     CUtensorMap am[4];

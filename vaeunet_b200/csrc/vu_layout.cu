@@ -44,6 +44,44 @@ __global__ void pack_dgrad_weight_kernel(const float* __restrict__ w, uint16_t* 
     }
 }
 
+// rows of an fp32 matrix [O][I] -> 16-bit [O][I_pad], zero padded (the stem filter as a 1x1 bank over im2col patches)
+__global__ void pack_rows_padded_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int O, int I, int I_pad, int dtype) {
+    const size_t total = (size_t)O * I_pad;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int i = idx % I_pad, o = idx / I_pad;
+        out[idx] = f2h(i < I ? w[(size_t)o * I + i] : 0.f, dtype);
+    }
+}
+
+// im2col of a K x K stride-S pad-P convolution over an NCHW fp32 image with few channels (the ResNet stem, Cin = 3):
+// out[n,ho,wo, ci*K*K + r*K + s] = x[n,ci,ho*S-P+r,wo*S-P+s] (0 outside the image and for the padding columns up to Kp).
+// The patch matrix turns the stem conv and its weight gradient into 1x1 tensor-core GEMMs (training path).
+__global__ void __launch_bounds__(256)
+im2col_small_cin_kernel(const float* __restrict__ x, uint16_t* __restrict__ out, int N, int Cin, int H, int W, int K, int S,
+                        int P, int Ho, int Wo, int Kp8, int dtype) {
+    const size_t total = (size_t)N * Ho * Wo * Kp8;
+    const int KK = K * K, Ktot = Cin * KK;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int k8 = idx % Kp8;
+        const int wo = (idx / Kp8) % Wo;
+        const int ho = (idx / ((size_t)Kp8 * Wo)) % Ho;
+        const int n = idx / ((size_t)Kp8 * Wo * Ho);
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int kk = k8 * 8 + j;
+            float v = 0.f;
+            if (kk < Ktot) {
+                const int ci = kk / KK, r = (kk % KK) / K, q = kk % K;
+                const int ih = ho * S - P + r, iw = wo * S - P + q;
+                if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * Cin + ci) * H + ih) * W + iw);
+            }
+            f[j] = v;
+        }
+        *(reinterpret_cast<uint4*>(out) + idx) = pack8(f, dtype);
+    }
+}
+
 // ConvTranspose2d k2 s2: w [I][O][2][2] -> [4 (a*2+b)][O][I]
 __global__ void pack_convT_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int I, int O, int dtype) {
     const size_t total = (size_t)4 * O * I;
@@ -279,6 +317,25 @@ extern "C" int vu_pack_conv_weight(const float* w, void* out, int O, int I, int 
     pack_conv_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, KH * KW,
                                                                                transpose_io, dtype);
     VU_CHECK_LAUNCH("pack_conv_weight");
+    return 0;
+}
+
+extern "C" int vu_pack_rows_padded(const float* w, void* out, int O, int I, int I_pad, int dtype, vu_stream_t st) {
+    if (!w || !out || O < 1 || I < 1 || I_pad < I) return set_error(VU_ERR_INVALID, "pack_rows_padded: bad args");
+    pack_rows_padded_kernel<<<grid_for((size_t)O * I_pad, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, I_pad, dtype);
+    VU_CHECK_LAUNCH("pack_rows_padded");
+    return 0;
+}
+
+extern "C" int vu_im2col_small_cin(const float* x_nchw, void* out, int N, int Cin, int H, int W, int K, int S, int P, int Kp,
+                                   int dtype, vu_stream_t st) {
+    if (!x_nchw || !out || Cin < 1 || K < 1 || S < 1 || Kp % 8 || Kp < Cin * K * K)
+        return set_error(VU_ERR_INVALID, "im2col_small_cin: bad args (Kp multiple of 8, >= Cin*K*K)");
+    const int Ho = (H + 2 * P - K) / S + 1, Wo = (W + 2 * P - K) / S + 1;
+    const size_t total = (size_t)N * Ho * Wo * (Kp / 8);
+    im2col_small_cin_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(x_nchw, (uint16_t*)out, N, Cin, H, W, K, S, P,
+                                                                               Ho, Wo, Kp / 8, dtype);
+    VU_CHECK_LAUNCH("im2col_small_cin");
     return 0;
 }
 

@@ -40,23 +40,59 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
         for (int j = 0; j < 8; ++j) { mu[j] = mean[c8 * 8 + j]; is[j] = invstd[c8 * 8 + j]; }
     }
     if (pl < lanes) {
-        for (size_t p = (size_t)blockIdx.x * lanes + pl; p < npix; p += (size_t)gridDim.x * lanes) {
-            float f[8];
-            unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
-            if (MODE == 0) {
+        const size_t step = (size_t)gridDim.x * lanes;
+        size_t p = (size_t)blockIdx.x * lanes + pl;
+        if (MODE == 0) {
+            // four independent 16-byte loads in flight per thread
+            for (; p + 3 * step < npix; p += 4 * step) {
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(x + (p + u * step) * x_ctot + x_coff) + c8);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    float f[8];
+                    unpack8(v[u], f, dtype);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { a0[j] += f[j]; a1[j] = fmaf(f[j], f[j], a1[j]); }
+                }
+            }
+            for (; p < npix; p += step) {
+                float f[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) { a0[j] += f[j]; a1[j] = fmaf(f[j], f[j], a1[j]); }
-            } else {
-                float g[8];
-                unpack8(__ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8), g, dtype);
+            }
+        } else {
+            auto body = [&](const uint4& vx, const uint4& vg, const uint4& vy) {
+                float f[8], g[8];
+                unpack8(vx, f, dtype);
+                unpack8(vg, g, dtype);
                 if (y != nullptr) {
                     float o[8];
-                    unpack8(__ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8), o, dtype);
+                    unpack8(vy, o, dtype);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
                 }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) { a0[j] += g[j]; a1[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], a1[j]); }
+            };
+            for (; p + step < npix; p += 2 * step) {
+                uint4 vx[2], vg[2], vy[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const size_t q = p + u * step;
+                    vx[u] = __ldg(reinterpret_cast<const uint4*>(x + q * x_ctot + x_coff) + c8);
+                    vg[u] = __ldg(reinterpret_cast<const uint4*>(dy + q * dy_ctot + dy_coff) + c8);
+                    vy[u] = y ? __ldg(reinterpret_cast<const uint4*>(y + q * y_ctot + y_coff) + c8) : make_uint4(0, 0, 0, 0);
+                }
+                body(vx[0], vg[0], vy[0]);
+                body(vx[1], vg[1], vy[1]);
+            }
+            for (; p < npix; p += step) {
+                const uint4 vx = __ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8);
+                const uint4 vg = __ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8);
+                const uint4 vy = y ? __ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8) : make_uint4(0, 0, 0, 0);
+                body(vx, vg, vy);
             }
         }
     }
@@ -93,32 +129,59 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
     }
 }
 
-// y = act(gamma * (x - mean) * invstd + beta + residual)
+// y = act(gamma * (x - mean) * invstd + beta + residual) = act(x * sc + sh + residual).
+// The launch uses gridDim * 256 threads with 256 % C8 == 0 whenever C8 is a power of two (every BatchNorm of the model),
+// so a thread keeps the same 8 channels for its whole grid-stride loop and loads the coefficients once (FIXED = true).
+template <bool FIXED>
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const float* __restrict__ mean,
                 const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                 const uint16_t* __restrict__ res, int res_ctot, int res_coff, int relu, uint16_t* __restrict__ y,
                 int y_ctot, int y_coff, size_t npix, int C8, int dtype) {
     const size_t total = npix * C8;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const int c8 = idx % C8;
-        const size_t p = idx / C8;
-        float f[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
-        float r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (res != nullptr) unpack8(__ldg(reinterpret_cast<const uint4*>(res + p * res_ctot + res_coff) + c8), r, dtype);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    float sc[8], sh[8];
+    auto coeff = [&](int c8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = c8 * 8 + j;
-            float v = (f[j] - mean[c]) * invstd[c] * gamma[c] + beta[c] + r[j];
+            sc[j] = invstd[c] * gamma[c];
+            sh[j] = beta[c] - mean[c] * sc[j];
+        }
+    };
+    size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (FIXED) coeff((int)(idx % C8));
+    auto one = [&](size_t i, const uint4& vx, const uint4& vr) {
+        const int c8 = (int)(i % C8);
+        const size_t p = i / C8;
+        if (!FIXED) coeff(c8);
+        float f[8], r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        unpack8(vx, f, dtype);
+        if (res != nullptr) unpack8(vr, r, dtype);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float v = fmaf(f[j], sc[j], sh[j]) + r[j];
             f[j] = relu ? fmaxf(v, 0.f) : v;
         }
         *(reinterpret_cast<uint4*>(y + p * y_ctot + y_coff) + c8) = pack8(f, dtype);
+    };
+    auto ldx = [&](size_t i) { return __ldg(reinterpret_cast<const uint4*>(x + (i / C8) * x_ctot + x_coff) + (i % C8)); };
+    auto ldr = [&](size_t i) {
+        return res ? __ldg(reinterpret_cast<const uint4*>(res + (i / C8) * res_ctot + res_coff) + (i % C8)) : make_uint4(0, 0, 0, 0);
+    };
+    for (; idx + 3 * stride < total; idx += 4 * stride) {
+        uint4 vx[4], vr[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { vx[u] = ldx(idx + u * stride); vr[u] = ldr(idx + u * stride); }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) one(idx + u * stride, vx[u], vr[u]);
     }
+    for (; idx < total; idx += stride) one(idx, ldx(idx), ldr(idx));
 }
 
-// dx = gamma * invstd * (dz - mean(dz) - xh * mean(dz * xh)),  dz = dy * (y > 0 if y). dz_out (optional) = dz
-// (the gradient of a residual branch added before the ReLU).
+// dx = gamma * invstd * (dz - mean(dz) - xh * mean(dz * xh)) = ka * dz + kb * x + kc,  dz = dy * (y > 0 if y).
+// dz_out (optional) = dz (the gradient of a residual branch added before the ReLU). Coefficients per thread as above.
+template <bool FIXED>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy,
                     int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
@@ -130,29 +193,57 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
     const int C = C8 * 8;
     if (blockIdx.x == 0 && dgamma != nullptr)      // parameter gradients, accumulated (gradient accumulation steps)
         for (int c = threadIdx.x; c < C; c += blockDim.x) { dgamma[c] += (float)sums[C + c]; dbeta[c] += (float)sums[c]; }
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const int c8 = idx % C8;
-        const size_t p = idx / C8;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    float ka[8], kb[8], kc[8];
+    auto coeff = [&](int c8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = c8 * 8 + j;
+            const float m_dz = (float)(sums[c] / count), m_dzx = (float)(sums[C + c] / count);
+            const float is = invstd[c], a = gamma[c] * is;
+            ka[j] = a;
+            kb[j] = -a * m_dzx * is;
+            kc[j] = -a * m_dz - kb[j] * mean[c];
+        }
+    };
+    size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (FIXED) coeff((int)(idx % C8));
+    auto one = [&](size_t i, const uint4& vx, const uint4& vg, const uint4& vy) {
+        const int c8 = (int)(i % C8);
+        const size_t p = i / C8;
+        if (!FIXED) coeff(c8);
         float f[8], g[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8), f, dtype);
-        unpack8(__ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8), g, dtype);
+        unpack8(vx, f, dtype);
+        unpack8(vg, g, dtype);
         if (y != nullptr) {
             float o[8];
-            unpack8(__ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8), o, dtype);
+            unpack8(vy, o, dtype);
 #pragma unroll
             for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
         }
         if (dz_out != nullptr) *(reinterpret_cast<uint4*>(dz_out + p * dz_ctot + dz_coff) + c8) = pack8(g, dtype);
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = c8 * 8 + j;
-            const float m_dz = (float)(sums[c] / count), m_dzx = (float)(sums[C + c] / count);
-            const float xh = (f[j] - mean[c]) * invstd[c];
-            o[j] = gamma[c] * invstd[c] * (g[j] - m_dz - xh * m_dzx);
-        }
+        for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], g[j], fmaf(kb[j], f[j], kc[j]));
         *(reinterpret_cast<uint4*>(dx + p * dx_ctot + dx_coff) + c8) = pack8(o, dtype);
+    };
+    auto ld = [&](const uint16_t* t, int ctot, int coff, size_t i) {
+        return __ldg(reinterpret_cast<const uint4*>(t + (i / C8) * ctot + coff) + (i % C8));
+    };
+    for (; idx + stride < total; idx += 2 * stride) {
+        uint4 vx[2], vg[2], vy[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const size_t i = idx + u * stride;
+            vx[u] = ld(x, x_ctot, x_coff, i);
+            vg[u] = ld(dy, dy_ctot, dy_coff, i);
+            vy[u] = y ? ld(y, y_ctot, y_coff, i) : make_uint4(0, 0, 0, 0);
+        }
+        one(idx, vx[0], vg[0], vy[0]);
+        one(idx + stride, vx[1], vg[1], vy[1]);
     }
+    for (; idx < total; idx += stride)
+        one(idx, ld(x, x_ctot, x_coff, idx), ld(dy, dy_ctot, dy_coff, idx), y ? ld(y, y_ctot, y_coff, idx) : make_uint4(0, 0, 0, 0));
 }
 
 // dst += src (gradient accumulation over the consumers of an activation)
@@ -184,7 +275,7 @@ extern "C" int vu_bn_stats(const void* x, size_t npix, int C, int x_ctot, int x_
     VU_TR_ALIGN((C | x_ctot | x_coff) % 8, "bn_stats");
     const int C8 = C / 8, lanes = 256 / C8;
     cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), (cudaStream_t)st);
-    channel_sums_kernel<0><<<tr_grid(npix, lanes * 16, 4), 256, 2 * lanes * C * sizeof(float), (cudaStream_t)st>>>(
+    channel_sums_kernel<0><<<tr_grid(npix, lanes * 16, 8), 256, 2 * lanes * C * sizeof(float), (cudaStream_t)st>>>(
         (const uint16_t*)x, x_ctot, x_coff, nullptr, 0, 0, nullptr, 0, 0, nullptr, nullptr, npix, C8, sums, dtype);
     VU_CHECK_LAUNCH("bn_stats");
     return 0;
@@ -205,9 +296,16 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
                            vu_stream_t st) {
     if (!x || !y || !mean || !invstd || !gamma || !beta) return set_error(VU_ERR_INVALID, "bn_apply: null");
     VU_TR_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff | res_ctot | res_coff) % 8, "bn_apply");
-    bn_apply_kernel<<<tr_grid(npix * (C / 8), 256), 256, 0, (cudaStream_t)st>>>(
-        (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
-        (uint16_t*)y, y_ctot, y_coff, npix, C / 8, dtype);
+    const int C8 = C / 8;
+    const int grid = tr_grid(npix * C8, 256 * 4, 16);
+    if (256 % C8 == 0)
+        bn_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
+            (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype);
+    else
+        bn_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
+            (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype);
     VU_CHECK_LAUNCH("bn_apply");
     return 0;
 }
@@ -222,14 +320,21 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
     const int C8 = C / 8, lanes = 256 / C8;
     cudaStream_t s = (cudaStream_t)st;
     cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), s);
-    channel_sums_kernel<1><<<tr_grid(npix, lanes * 16, 4), 256, 2 * lanes * C * sizeof(float), s>>>(
+    channel_sums_kernel<1><<<tr_grid(npix, lanes * 8, 8), 256, 2 * lanes * C * sizeof(float), s>>>(
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
         mean, invstd, npix, C8, sums, dtype);
     VU_CHECK_LAUNCH("bn_bwd_reduce");
-    bn_bwd_apply_kernel<<<tr_grid(npix * C8, 256), 256, 0, s>>>(
-        (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
-        mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
-        C8, dtype, dgamma, dbeta);
+    const int grid = tr_grid(npix * C8, 256 * 2, 16);
+    if (256 % C8 == 0)
+        bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(
+            (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
+            mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
+            C8, dtype, dgamma, dbeta);
+    else
+        bn_bwd_apply_kernel<false><<<grid, 256, 0, s>>>(
+            (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
+            mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
+            C8, dtype, dgamma, dbeta);
     VU_CHECK_LAUNCH("bn_bwd_apply");
     return 0;
 }

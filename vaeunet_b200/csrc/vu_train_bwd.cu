@@ -58,6 +58,75 @@ maxpool_bwd_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const
     }
 }
 
+// ---------------------------------------------------------------- max-pool with saved argmax (training fast path)
+// Forward also writes, per output element, the position r*k+q of the FIRST maximum of its window (row-major scan, as
+// ATen); backward is then a pure gather: input pixel (ih,iw) sums dy over the <= 4 windows whose code points at it.
+__global__ void __launch_bounds__(256)
+maxpool_idx_fwd_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, uint16_t* __restrict__ y, int y_ctot,
+                       int y_coff, uint8_t* __restrict__ code, int N, int H, int W, int C8, int k, int s, int p, int Ho,
+                       int Wo, int dtype) {
+    const size_t total = (size_t)N * Ho * Wo * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int wo = (idx / C8) % Wo;
+        const int ho = (idx / ((size_t)C8 * Wo)) % Ho;
+        const int n = idx / ((size_t)C8 * Wo * Ho);
+        float m[8];
+        uint32_t cd[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; cd[j] = 0xFFu; }
+        for (int r = 0; r < k; ++r) {
+            const int ih = ho * s - p + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int q = 0; q < k; ++q) {
+                const int iw = wo * s - p + q;
+                if (iw < 0 || iw >= W) continue;
+                float f[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(x + (((size_t)n * H + ih) * W + iw) * x_ctot + x_coff) + c8), f, dtype);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (f[j] > m[j] || cd[j] == 0xFFu) { m[j] = f[j]; cd[j] = (uint32_t)(r * k + q); }
+            }
+        }
+        const size_t o = ((size_t)n * Ho + ho) * Wo + wo;
+        *(reinterpret_cast<uint4*>(y + o * y_ctot + y_coff) + c8) = pack8(m, dtype);
+        uint2 pk;
+        pk.x = cd[0] | (cd[1] << 8) | (cd[2] << 16) | (cd[3] << 24);
+        pk.y = cd[4] | (cd[5] << 8) | (cd[6] << 16) | (cd[7] << 24);
+        *(reinterpret_cast<uint2*>(code + o * (size_t)(C8 * 8)) + c8) = pk;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+maxpool_idx_bwd_kernel(const uint8_t* __restrict__ code, const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff,
+                       uint16_t* __restrict__ dx, int dx_ctot, int dx_coff, int N, int H, int W, int C8, int k, int s, int p,
+                       int Ho, int Wo, int dtype) {
+    const size_t total = (size_t)N * H * W * C8;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int iw = (idx / C8) % W;
+        const int ih = (idx / ((size_t)C8 * W)) % H;
+        const int n = idx / ((size_t)C8 * W * H);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const int ho_lo = max(0, (ih + p - k + s) / s), ho_hi = min(Ho - 1, (ih + p) / s);
+        const int wo_lo = max(0, (iw + p - k + s) / s), wo_hi = min(Wo - 1, (iw + p) / s);
+        for (int ho = ho_lo; ho <= ho_hi; ++ho)
+            for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+                const uint32_t me = (uint32_t)((ih - (ho * s - p)) * k + (iw - (wo * s - p)));
+                const size_t o = ((size_t)n * Ho + ho) * Wo + wo;
+                const uint2 pk = __ldg(reinterpret_cast<const uint2*>(code + o * (size_t)(C8 * 8)) + c8);
+                float g[8];
+                unpack8(__ldg(reinterpret_cast<const uint4*>(dy + o * dy_ctot + dy_coff) + c8), g, dtype);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t cj = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xFFu;
+                    acc[j] += (cj == me) ? g[j] : 0.f;
+                }
+            }
+        *(reinterpret_cast<uint4*>(dx + (((size_t)n * H + ih) * W + iw) * dx_ctot + dx_coff) + c8) = pack8(acc, dtype);
+    }
+}
+
 // ---------------------------------------------------------------- bilinear (align_corners=True) backward
 // Adjoint of vu_bilinear_ac_nhwc as a gather: source pixel (hs,ws) collects w(ho;hs) * w(wo;ws) * dy[ho,wo] over the
 // few destination rows / columns whose interpolation footprint contains it (same fp32 index arithmetic as forward).
@@ -252,6 +321,29 @@ extern "C" int vu_maxpool_bwd(const void* x, const void* dy, void* dx, int N, in
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W,
         C / 8, k, s, p, Ho, Wo, dtype);
     VU_CHECK_LAUNCH("maxpool_bwd");
+    return 0;
+}
+
+extern "C" int vu_maxpool_idx_fwd(const void* x, void* y, void* code, int N, int H, int W, int C, int x_ctot, int x_coff,
+                                  int y_ctot, int y_coff, int k, int s, int p, int dtype, vu_stream_t st) {
+    if (!x || !y || !code || k < 1 || k > 3) return set_error(VU_ERR_INVALID, "maxpool_idx_fwd: bad args (k <= 3)");
+    VU_TB_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff) % 8, "maxpool_idx_fwd");
+    const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+    maxpool_idx_fwd_kernel<<<tb_grid((size_t)N * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+        (const uint16_t*)x, x_ctot, x_coff, (uint16_t*)y, y_ctot, y_coff, (uint8_t*)code, N, H, W, C / 8, k, s, p, Ho, Wo, dtype);
+    VU_CHECK_LAUNCH("maxpool_idx_fwd");
+    return 0;
+}
+
+extern "C" int vu_maxpool_idx_bwd(const void* code, const void* dy, void* dx, int N, int H, int W, int C, int dy_ctot,
+                                  int dy_coff, int dx_ctot, int dx_coff, int k, int s, int p, int dtype, vu_stream_t st) {
+    if (!code || !dy || !dx || k < 1 || k > 3) return set_error(VU_ERR_INVALID, "maxpool_idx_bwd: bad args (k <= 3)");
+    VU_TB_ALIGN((C | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "maxpool_idx_bwd");
+    const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+    maxpool_idx_bwd_kernel<<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+        (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W, C / 8, k, s, p,
+        Ho, Wo, dtype);
+    VU_CHECK_LAUNCH("maxpool_idx_bwd");
     return 0;
 }
 

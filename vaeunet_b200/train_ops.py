@@ -85,6 +85,27 @@ def maxpool_bwd(x: Act, dy: Act, k: int, s: int, p: int) -> Act:
     return dx
 
 
+def maxpool_idx_fwd(x: Act, k: int, s: int, p: int):
+    """-> (y, code): max-pool + the uint8 position of each window's first maximum (for maxpool_idx_bwd)."""
+    require_device()
+    Ho, Wo = (x.H + 2 * p - k) // s + 1, (x.W + 2 * p - k) // s + 1
+    y = ops.new_act(x.N, Ho, Wo, x.C, x.dt, x.t.device)
+    code = torch.empty((x.N, Ho, Wo, x.C), dtype=torch.uint8, device=x.t.device)
+    check(load().vu_maxpool_idx_fwd(x.t.data_ptr(), y.t.data_ptr(), code.data_ptr(), x.N, x.H, x.W, x.C, x.ctot, x.coff,
+                                    y.ctot, y.coff, k, s, p, x.dt, _stream()), "vu_maxpool_idx_fwd")
+    _count()
+    return y, code
+
+
+def maxpool_idx_bwd(code: torch.Tensor, dy: Act, H: int, W: int, k: int, s: int, p: int) -> Act:
+    require_device()
+    dx = ops.new_act(dy.N, H, W, dy.C, dy.dt, dy.t.device)
+    check(load().vu_maxpool_idx_bwd(code.data_ptr(), dy.t.data_ptr(), dx.t.data_ptr(), dy.N, H, W, dy.C, dy.ctot, dy.coff,
+                                    dx.ctot, dx.coff, k, s, p, dy.dt, _stream()), "vu_maxpool_idx_bwd")
+    _count()
+    return dx
+
+
 def bilinear_ac_bwd(dy: Act, Hs: int, Ws: int, dx: Optional[Act] = None, accumulate: bool = False) -> Act:
     require_device()
     if dx is None:
@@ -242,6 +263,33 @@ def stem_conv_raw(x: torch.Tensor, w: torch.Tensor, dtype) -> Act:
     one = torch.ones(Cout, device=x.device); zero = torch.zeros(Cout, device=x.device)
     check(load().vu_stem_conv7x7s2_act(x.data_ptr(), _f32(w).data_ptr(), one.data_ptr(), zero.data_ptr(), out.t.data_ptr(), N,
                                        Cin, H, W, Cout, out.ctot, out.coff, 0, out.dt, _stream()), "vu_stem_conv7x7s2_act")
+    _count()
+    return out
+
+
+def im2col_small_cin(x: torch.Tensor, k: int, stride: int, pad: int, dtype) -> Act:
+    """NCHW fp32 image -> NHWC 16-bit patch matrix [N,Ho,Wo,Kp] (Kp = Cin*k*k rounded up to 8, zero padded)."""
+    require_device()
+    x = _f32(x.float().contiguous())
+    N, Cin, H, W = x.shape
+    Kp = (Cin * k * k + 7) // 8 * 8
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    out = ops.new_act(N, Ho, Wo, Kp, dtype, x.device)
+    check(load().vu_im2col_small_cin(x.data_ptr(), out.t.data_ptr(), N, Cin, H, W, k, stride, pad, Kp, dtype, _stream()),
+          "vu_im2col_small_cin")
+    _count()
+    return out
+
+
+def pack_rows_padded(w: torch.Tensor, I_pad: int, dtype, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 [O, ...] -> 16-bit [O, 1, I_pad] (a 1x1 filter bank over im2col patches)."""
+    require_device()
+    w = _f32(w)
+    O = w.shape[0]
+    I = w.numel() // O
+    if out is None:
+        out = torch.empty((O, 1, I_pad), dtype=ops._TORCH_DT[dtype], device=w.device)
+    check(load().vu_pack_rows_padded(w.data_ptr(), out.data_ptr(), O, I, I_pad, dtype, _stream()), "vu_pack_rows_padded")
     _count()
     return out
 

@@ -139,6 +139,9 @@ class TrainStep:
                 if li > 1 and b == 0 and (".conv1." in n or ".downsample." in n):
                     stride = 2
             self.convs[n[:-len(".weight")]] = _Conv(n, w, k, stride, self.dt, self.dev)
+        ws = self.P["encoder.conv1.weight"]
+        kp = (ws[0].numel() + 7) // 8 * 8
+        self.stem_w16 = torch.empty((ws.shape[0], 1, kp), dtype=ops._TORCH_DT[self.dt], device=self.dev)
 
     def repack(self):
         """fp32 master filters -> 16-bit tensor-core banks (forward + data-gradient), once per step."""
@@ -150,6 +153,8 @@ class TrainStep:
             ops.check(lib.vu_pack_conv_weight(w.data_ptr(), c.w16.data_ptr(), O, I, c.k, c.k, 0, self.dt, st), "vu_pack_conv_weight")
             ops.check(lib.vu_pack_dgrad_weight(w.data_ptr(), c.banks_t.data_ptr(), O, I, c.k, c.stride, self.dt, st),
                       "vu_pack_dgrad_weight")
+        ws = self.P["encoder.conv1.weight"]
+        T.pack_rows_padded(ws, self.stem_w16.shape[2], self.dt, out=self.stem_w16)
         ops._count(2 * len(self.convs))
 
     # ------------------------------------------------------------------ small helpers
@@ -194,10 +199,13 @@ class TrainStep:
         images = images.float().contiguous()
         B, _, H, W = images.shape
         S: dict = {"images": images, "B": B, "H": H, "W": W}
-        x0raw = T.stem_conv_raw(images, P["encoder.conv1.weight"], dt)
+        # stem 7x7 s2 on the tensor cores: im2col patches (147 -> 152 columns) x 1x1 filter bank
+        xcol = T.im2col_small_cin(images, 7, 2, 3, dt)
+        x0raw = ops.conv2d(xcol, self.stem_w16, 1, 1, 0, None, None, False)
+        S["xcol"] = xcol
         f0, st0 = self._bn(x0raw, "encoder.bn1.", True)
-        pool = ops.maxpool(f0, 3, 2, 1)
-        S.update(x0raw=x0raw, f0=f0, st0=st0)
+        pool, pool_code = T.maxpool_idx_fwd(f0, 3, 2, 1)
+        S.update(x0raw=x0raw, f0=f0, st0=st0, pool_code=pool_code)
         x = pool
         feats: List[Act] = [f0]
         blocks = []
@@ -386,10 +394,13 @@ class TrainStep:
                 self._all_reduce_bucket("layer3")
         # stem: max-pool, BN + ReLU, 7x7 conv
         f0 = S["f0"]
-        df0 = T.maxpool_bwd(f0, dout, 3, 2, 1)
+        df0 = T.maxpool_idx_bwd(S["pool_code"], dout, f0.H, f0.W, 3, 2, 1)
         T.add_(df0, dfeat[0])
         dx0raw, _ = self._bn_bwd(S["x0raw"], df0, f0, S["st0"], "encoder.bn1.")
-        T.stem_wgrad(S["images"], dx0raw, G["encoder.conv1.weight"])
+        xcol = S["xcol"]
+        dw = ops.conv2d_wgrad(xcol, dx0raw, 1, 1, 0)                                   # [64, 1, 152] packed
+        gw = G["encoder.conv1.weight"]
+        gw.view(gw.shape[0], -1).add_(dw.view(gw.shape[0], -1)[:, :gw[0].numel()])
         self._all_reduce_bucket("rest")
 
     # ------------------------------------------------------------------ data parallel (NCCL all-reduce of gradients)
