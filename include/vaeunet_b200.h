@@ -78,6 +78,11 @@ int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
 /* Same, accumulated straight into the parameter's own OIHW layout dw[co][ci][r][s] (the .grad of nn.Conv2d.weight). */
 int vu_conv2d_wgrad_oihw(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
+/* Packed weight gradients (vu_conv2d_wgrad) of a list of convolutions -> the parameters' OIHW gradient buffers, accumulated,
+ * in one launch. table: device array of n_entries records {int64 src_off, int64 dst_off (floats from the two bases),
+ * int32 O, T, I, pad}; max_row_floats = max over entries of T*I. */
+int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_base, const void* table, int n_entries,
+                            int max_row_floats, vu_stream_t stream);
 /* Filter banks for the DATA gradient of conv2d(x, w) (w OIHW fp32; 3x3 p1 or 1x1 p0; stride 1|2), to be run by
  * vu_conv2d_fwd on dY: stride 1 -> one bank [I][K*K][O] (taps rotated 180 degrees); stride 2, 1x1 -> one bank [I][1][O]
  * (written to dX parity (0,0) with out_up = 2); stride 2, 3x3 -> four 3x3 p1 banks [ph*2+pc][I][9][O], one per parity of

@@ -152,9 +152,18 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
             const int ci0 = n_tile * BN + c * 32;
             if (co < p.cout) {
                 float* dst = p.dw + static_cast<size_t>(co) * p.co_stride + tap * p.tap_stride + static_cast<size_t>(ci0) * p.ci_stride;
+                if (p.ci_stride == 1) {
+                    // packed layout: this thread's 32 input channels are 128 contiguous bytes -> eight 16-byte vector reductions
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (ci0 + j < p.cin) atomicAdd(dst + j * p.ci_stride, __uint_as_float(r[j]));
+                    for (int j = 0; j < 32; j += 4)
+                        if (ci0 + j < p.cin)
+                            red_add_v4_f32(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                           __uint_as_float(r[j + 3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (ci0 + j < p.cin) atomicAdd(dst + j * p.ci_stride, __uint_as_float(r[j]));
+                }
             }
         }
     }

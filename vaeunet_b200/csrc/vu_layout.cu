@@ -82,6 +82,29 @@ im2col_small_cin_kernel(const float* __restrict__ x, uint16_t* __restrict__ out,
     }
 }
 
+// Packed weight gradients [O][T][I] fp32 -> the parameters' own OIHW layout [O][I][T], ACCUMULATED, for a whole list of
+// convolutions in one launch. table[e] = {src offset, dst offset (floats), O, T, I}; blockIdx.y = entry, blockIdx.x
+// strides over the O rows; a row is a T x I matrix transposed through shared memory.
+struct UnpackEntry { long long src, dst; int O, T, I, pad; };
+__global__ void __launch_bounds__(256)
+unpack_wgrad_batched_kernel(const float* __restrict__ src_base, float* __restrict__ dst_base,
+                            const UnpackEntry* __restrict__ table) {
+    extern __shared__ float row[];     // T * I floats
+    const UnpackEntry e = table[blockIdx.y];
+    const int n = e.T * e.I;
+    for (int o = blockIdx.x; o < e.O; o += gridDim.x) {
+        const float* sp = src_base + e.src + (size_t)o * n;
+        float* dp = dst_base + e.dst + (size_t)o * n;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) row[i] = sp[i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {      // i = ci * T + t (OIHW order)
+            const int ci = i / e.T, t = i % e.T;
+            dp[i] += row[t * e.I + ci];
+        }
+        __syncthreads();
+    }
+}
+
 // ConvTranspose2d k2 s2: w [I][O][2][2] -> [4 (a*2+b)][O][I]
 __global__ void pack_convT_kernel(const float* __restrict__ w, uint16_t* __restrict__ out, int I, int O, int dtype) {
     const size_t total = (size_t)4 * O * I;
@@ -317,6 +340,23 @@ extern "C" int vu_pack_conv_weight(const float* w, void* out, int O, int I, int 
     pack_conv_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, KH * KW,
                                                                                transpose_io, dtype);
     VU_CHECK_LAUNCH("pack_conv_weight");
+    return 0;
+}
+
+extern "C" int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_base, const void* table, int n_entries,
+                                       int max_row_floats, vu_stream_t st) {
+    if (!packed_base || !oihw_base || !table || n_entries < 1 || max_row_floats < 1)
+        return set_error(VU_ERR_INVALID, "unpack_wgrad_batched: bad args");
+    const size_t smem = (size_t)max_row_floats * sizeof(float);
+    if (smem > 160 * 1024) return set_error(VU_ERR_UNSUPPORTED, "unpack_wgrad_batched: row of %d floats exceeds shared memory", max_row_floats);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(unpack_wgrad_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        attr_set = true;
+    }
+    dim3 grid(32, n_entries);
+    unpack_wgrad_batched_kernel<<<grid, 256, smem, (cudaStream_t)st>>>(packed_base, oihw_base, (const UnpackEntry*)table);
+    VU_CHECK_LAUNCH("unpack_wgrad_batched");
     return 0;
 }
 

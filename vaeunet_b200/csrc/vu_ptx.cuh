@@ -177,4 +177,9 @@ __host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t m, uint32_t n, ui
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
+// 16-byte vector reduction into global memory (fire-and-forget fp32 x4 add; REDG.E.ADD.F32x4)
+__device__ __forceinline__ void red_add_v4_f32(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 }  // namespace vu

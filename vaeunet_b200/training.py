@@ -142,6 +142,31 @@ class TrainStep:
         ws = self.P["encoder.conv1.weight"]
         kp = (ws[0].numel() + 7) // 8 * 8
         self.stem_w16 = torch.empty((ws.shape[0], 1, kp), dtype=ops._TORCH_DT[self.dt], device=self.dev)
+        # The wgrad kernel accumulates in its packed layout [O][k*k][I] (contiguous 16-byte vector reductions); one batched
+        # launch per all-reduce bucket transposes those into the parameters' OIHW .grad views.
+        total = 0
+        goff = {}
+        for name, c in self.convs.items():
+            goff[name] = total
+            total += (self.P[c.name].numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.flat_gp = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        self.GP = {}
+        for name, c in self.convs.items():
+            O, I = self.P[c.name].shape[:2]
+            self.GP[name] = self.flat_gp[goff[name]:goff[name] + O * I * c.k * c.k].view(O, c.k * c.k, I)
+        import struct
+        self.unpack_tables = {}
+        for bname, (lo, hi) in self.buckets.items():
+            recs, max_row = [], 1
+            for name, c in self.convs.items():
+                o = self.offs[c.name]
+                if lo <= o < hi:
+                    O, I = self.P[c.name].shape[:2]
+                    recs.append(struct.pack("<qqiiii", goff[name], o, O, c.k * c.k, I, 0))
+                    max_row = max(max_row, c.k * c.k * I)
+            if recs:
+                tab = torch.frombuffer(bytearray(b"".join(recs)), dtype=torch.uint8).to(self.dev)
+                self.unpack_tables[bname] = (tab, len(recs), max_row)
 
     def repack(self):
         """fp32 master filters -> 16-bit tensor-core banks (forward + data-gradient), once per step."""
@@ -175,7 +200,7 @@ class TrainStep:
 
     def _wgrad(self, x: Act, dy: Act, name: str):
         c = self.convs[name]
-        ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.G[c.name], oihw=True)
+        ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.GP[name])
 
     def _dgrad(self, dy: Act, name: str, H: int, W: int, out: Optional[Act] = None, accumulate=False) -> Act:
         c = self.convs[name]
@@ -300,6 +325,7 @@ class TrainStep:
         P, G, dt, dev, L = self.P, self.G, self.dt, self.dev, self.L
         B = S["B"]
         feats, dec = S["feats"], S["dec"]
+        self.flat_gp.zero_()
         y2 = dec[3]["y2"]
         dlow = T.resize_map_bwd(dlogits, y2.H, y2.W)
         G["final_conv.weight"].view(-1).add_(T.weighted_channel_sum(y2, dlow, per_image=False))
@@ -405,6 +431,12 @@ class TrainStep:
 
     # ------------------------------------------------------------------ data parallel (NCCL all-reduce of gradients)
     def _all_reduce_bucket(self, name: str):
+        """A bucket of parameters has its final gradients: unpack its conv weight gradients, then start its all-reduce."""
+        if name in self.unpack_tables:
+            tab, n, max_row = self.unpack_tables[name]
+            ops.check(ops.load().vu_unpack_wgrad_batched(self.flat_gp.data_ptr(), self.flat_g.data_ptr(), tab.data_ptr(), n,
+                                                         max_row, ops._stream()), "vu_unpack_wgrad_batched")
+            ops._count()
         if self.pg is None or self.world == 1:
             return
         import torch.distributed as dist
