@@ -1,4 +1,5 @@
-"""Headline benchmark (BASELINE.json): MC-uncertainty patches/s, 512x512 patches, T=1.0, N=10
+"""Headline benchmark (BASELINE.json): MC-uncertainty patches/s (the JSON line's metric) and, in its "train" object,
+training images/s (configs[2]). MC: 512x512 patches, T=1.0, N=10
 latent samples, mean/std/entropy maps, 16-bit tensor-core operands (f16 default, --dtype bf16), fp32
 accumulation, synthetic fundus patches, fixture weights.
 
@@ -28,6 +29,8 @@ import torch  # noqa: E402
 
 PATCH, NS, TEMP = 512, 10, 1.0
 F_ALG_PATCH_GF = 761.40      # F_enc + F_head + 10 * F_dec at 512^2
+TRAIN_B = 16                 # configs[2]: batch 16 of 512x512 per GPU (weak scaling)
+F_ALG_TRAIN_STEP_GF = 5289.0 # fwd + dgrad + wgrad of every conv at B=16 (no dgrad for the stem)
 
 
 def _peaks():
@@ -91,6 +94,125 @@ def cpu_baseline(threads: int, reps: int = 3):
     return 1.0 / statistics.median(ts), ts
 
 
+def cpu_train_baseline(threads: int, batch: int = 2):
+    """The reference training step (train.py:385-411: forward in train mode, loss + beta*KL, backward, clip, AdamW) through
+    the oracle port on the host cores, ONE step at a reduced batch (per-image cost is batch-independent on the CPU)."""
+    from oracle import vaeunet_oracle as O
+    from vaeunet_b200 import testing
+    from vaeunet_b200.synthetic import synthetic_fundus
+    torch.set_num_threads(threads)
+    sd, _ = testing.resnet_fixture()
+    x, m = synthetic_fundus(batch, PATCH, seed=77)
+    eps = torch.randn(batch, 32, generator=torch.Generator().manual_seed(2))
+    t0 = time.perf_counter()
+    _, _, _, grads, _ = O.training_grads(sd, O.ResNetCfg(), x, m, eps, 0.001, 1e-3, "EX")
+    params = {k: sd[k].clone() for k in grads}
+    O.clip_grad_norm_(grads, 1.0)
+    O.adamw_step(params, grads, {}, lr=1e-4, wd=1e-5)
+    dt = time.perf_counter() - t0
+    return batch / dt, dt
+
+
+def bench_train(args, dev, rank, world, dist):
+    """configs[2]: VAE-UNet training step (CombinedLoss + beta*KL, clip 1.0, AdamW), batch 16 of 512x512 per GPU, bf16
+    activations / fp32 master weights, data parallel with an NCCL all-reduce of the gradients (weak scaling)."""
+    from vaeunet_b200 import ops, testing
+    from vaeunet_b200.synthetic import synthetic_fundus
+    from vaeunet_b200.training import TrainStep
+    from vaeunet_b200.unet import UNetResNet
+    sd, kw = testing.resnet_fixture()
+    model = UNetResNet(**kw)
+    model.load_state_dict(sd)
+    model = model.to(dev).train()
+    pg = dist.group.WORLD if dist is not None else None
+    ts = TrainStep(model, lesion="EX", dtype=ops.BF16, process_group=pg)
+    B, POOL = TRAIN_B, 4                       # 4 x (50 MB images + 17 MB masks) > L2; activations are GBs per step
+    base, mask = synthetic_fundus(4, PATCH, seed=4321 + rank)
+    base, mask = base.repeat(B // 4, 1, 1, 1), mask.repeat(B // 4, 1, 1, 1)
+    host = [(base.roll(13 * i, dims=3).contiguous().pin_memory(), mask.roll(13 * i, dims=3).contiguous().pin_memory())
+            for i in range(POOL)]
+    devp = [(a.to(dev), b.to(dev)) for a, b in host]
+    g = torch.Generator().manual_seed(7 + rank)
+    eps = [torch.randn(B, 32, generator=g).to(dev) for _ in range(POOL)]
+    loss_host = torch.zeros(1).pin_memory()
+
+    def step(i, e2e=False):
+        j = i % POOL
+        if e2e:
+            x, m = host[j][0].to(dev, non_blocking=True), host[j][1].to(dev, non_blocking=True)
+        else:
+            x, m = devp[j]
+        out = ts.step(x, m, 0.001, eps[j])
+        if e2e:
+            loss_host.copy_(out["loss"].reshape(1), non_blocking=True)
+        return out
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e):
+        for i in range(args.warmup):
+            step(i, e2e)
+        barrier()
+        l0 = ops.LAUNCHES
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            step(args.warmup + i, e2e)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms, ops.LAUNCHES - l0
+
+    ms, launches = timed(False)
+    ms_e2e, _ = timed(True)
+    ops.CONV_TIMING = []
+    barrier()
+    step(0)
+    barrier()
+    ev = ops.CONV_TIMING
+    ops.CONV_TIMING = None
+    conv_ms = sum(a.elapsed_time(b) for a, b, *_ in ev)
+    conv_flop = sum(f for _, _, f, _ in ev)
+    sustained, burst, hbm, src = _peaks()
+    imgs = B * world * args.steps
+    value = imgs / (ms / 1e3)
+    step_tf = F_ALG_TRAIN_STEP_GF * args.steps / (ms / 1e3) / 1e3
+    res = {
+        "metric": "train_images_per_sec", "value": value, "unit": "img/s", "ms_per_step": ms / args.steps, "dtype": "bf16",
+        "scaling": "weak", "higher_is_better": True,
+        "config": {"workload": "configs[2]: VAE-UNet (ResNet-34 encoder) training step, CombinedLoss + beta*KL (free bits 1e-3), "
+                               "clip 1.0, AdamW(1e-4, wd 1e-5); bf16 activations / gradients, fp32 master weights",
+                   "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}: bucketed NCCL all-reduce of 121.8 MB fp32 gradients"
+                   if world > 1 else "dp1", "l2": "rotating pool of 4 input batches (268 MB) + multi-GB activations per step > 126 MB L2"},
+        "e2e": {"value": imgs / (ms_e2e / 1e3), "unit": "img/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": B * 4 * PATCH * PATCH * 4, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches,
+        "roofline": {"bound": "tensor", "kernel": "tcgen05 conv kernels (forward + data gradient: conv_igemm / conv3x3_halo; weight gradient: conv_wgrad)",
+                     "achieved": conv_flop / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0, "peak": sustained, "unit": "TFLOP/s",
+                     "frac": (conv_flop / (conv_ms / 1e3) / 1e12 / sustained) if conv_ms > 0 else 0.0,
+                     "conv_launches_per_step": len(ev), "conv_ms_per_step": conv_ms, "alg_gflop_per_step_convs": conv_flop / 1e9,
+                     "peak_source": f"{src} bf16_tflops_sustained", "traffic": None,
+                     "whole_step": {"alg_gflop_per_step": F_ALG_TRAIN_STEP_GF, "achieved_tflops": step_tf / world,
+                                    "frac_of_sustained": step_tf / world / sustained}},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, dt = cpu_train_baseline(threads)
+        res["cpu_baseline"] = {"value": v, "unit": "img/s", "cores": threads, "kind": "port",
+                               "sample": f"ONE training step (forward, loss, backward, clip, AdamW) at batch 2 of 512x512 through the "
+                                         f"oracle port (fp32 PyTorch CPU autograd, {threads} threads): {dt:.1f} s"}
+    del ts, model
+    torch.cuda.empty_cache()
+    return res
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -129,11 +251,13 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=8, help="patches per step per GPU")
+    ap.add_argument("--batch", type=int, default=16, help="patches per step per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", default=None, help="write a per-conv-shape timing table (csv) to this path")
     ap.add_argument("--dtype", default="f16", choices=["bf16", "f16"])
+    ap.add_argument("--workload", default="both", choices=["both", "mc", "train"],
+                    help="mc: configs[1] only; train: configs[2] only (printed as the line's metric); both: MC line + 'train' object")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -154,6 +278,19 @@ def main():
     from vaeunet_b200 import ops, testing
     from vaeunet_b200.synthetic import synthetic_fundus
     from vaeunet_b200.unet import UNetResNet
+
+    if args.workload == "train":
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        res = bench_train(args, dev, rank, world, dist)
+        res.update({"n_gpus": world, "steps": args.steps, "warmup": args.warmup, "vs_baseline": None, "data": "synthetic",
+                    "clocks": sampler.stop() if rank == 0 else None})
+        if rank == 0:
+            print(json.dumps(res))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
 
     sd, kw = testing.resnet_fixture()
     model = UNetResNet(**kw)
@@ -268,6 +405,10 @@ def main():
         out["cpu_baseline"] = {"value": v, "unit": "patches/s", "cores": threads, "kind": "port",
                                "sample": f"median of {len(ts)} runs of ONE 512x512 patch, N=10 (oracle port of the reference, "
                                          f"fp32 PyTorch CPU, {threads} threads); run times {['%.2f' % t for t in ts]} s"}
+    if args.workload == "both":
+        del eng, model, dev_pool, eps_pool
+        torch.cuda.empty_cache()
+        out["train"] = bench_train(args, dev, rank, world, dist)
     if rank == 0:
         print(json.dumps(out))
     if dist is not None:

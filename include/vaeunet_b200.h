@@ -78,6 +78,11 @@ int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 int vu_conv2d_wgrad(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
 /* Same, accumulated straight into the parameter's own OIHW layout dw[co][ci][r][s] (the .grad of nn.Conv2d.weight). */
 int vu_conv2d_wgrad_oihw(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, vu_stream_t stream);
+/* vu_pack_conv_weight + vu_pack_dgrad_weight for a whole list of convolutions in one launch (the training step repacks
+ * every bank after each optimizer step). table: device array of records {int64 src_off (floats from src_base),
+ * int64 dst_fwd_off, int64 dst_bank_off (16-bit elements from dst_base), int32 O, I, K, stride}. */
+int vu_pack_weights_batched(const float* src_base, void* dst_base, const void* table, int n_entries, int dtype,
+                            vu_stream_t stream);
 /* Packed weight gradients (vu_conv2d_wgrad) of a list of convolutions -> the parameters' OIHW gradient buffers, accumulated,
  * in one launch. table: device array of n_entries records {int64 src_off, int64 dst_off (floats from the two bases),
  * int32 O, T, I, pad}; max_row_floats = max over entries of T*I. */

@@ -41,6 +41,7 @@ SIGNATURES = {
     "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
     "vu_conv2d_wgrad": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_conv2d_wgrad_oihw": [C.POINTER(ConvArgs), p, i, i, p, p],
+    "vu_pack_weights_batched": [p, p, p, i, i, p],
     "vu_unpack_wgrad_batched": [p, p, p, i, i, p],
     "vu_pack_dgrad_weight": [p, p, i, i, i, i, i, p],
     "vu_pack_conv_weight": [p, p, i, i, i, i, i, i, p],

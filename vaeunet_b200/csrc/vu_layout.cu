@@ -56,29 +56,41 @@ __global__ void pack_rows_padded_kernel(const float* __restrict__ w, uint16_t* _
 // im2col of a K x K stride-S pad-P convolution over an NCHW fp32 image with few channels (the ResNet stem, Cin = 3):
 // out[n,ho,wo, ci*K*K + r*K + s] = x[n,ci,ho*S-P+r,wo*S-P+s] (0 outside the image and for the padding columns up to Kp).
 // The patch matrix turns the stem conv and its weight gradient into 1x1 tensor-core GEMMs (training path).
+// Block = 32 consecutive output pixels of one output row: the Cin x K x ((32-1)*S+K) input patch is staged in shared memory
+// with coalesced loads, then every (pixel, 8-column chunk) is assembled from it and written as one 16-byte store (the
+// 32 pixels are one contiguous run of the patch matrix).
+constexpr int kI2cPix = 32;
 __global__ void __launch_bounds__(256)
 im2col_small_cin_kernel(const float* __restrict__ x, uint16_t* __restrict__ out, int N, int Cin, int H, int W, int K, int S,
                         int P, int Ho, int Wo, int Kp8, int dtype) {
-    const size_t total = (size_t)N * Ho * Wo * Kp8;
+    extern __shared__ float sm[];
+    const int cols = (kI2cPix - 1) * S + K;
+    float* tile = sm;                                        // [Cin][K][cols]
+    int* tab = reinterpret_cast<int*>(sm + Cin * K * cols);  // [Kp8 * 8] smem offset of column kk (or -1)
+    const int n = blockIdx.z, ho = blockIdx.y, wo0 = blockIdx.x * kI2cPix;
     const int KK = K * K, Ktot = Cin * KK;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const int k8 = idx % Kp8;
-        const int wo = (idx / Kp8) % Wo;
-        const int ho = (idx / ((size_t)Kp8 * Wo)) % Ho;
-        const int n = idx / ((size_t)Kp8 * Wo * Ho);
+    for (int i = threadIdx.x; i < Kp8 * 8; i += blockDim.x) {
+        int off = -1;
+        if (i < Ktot) { const int ci = i / KK, r = (i % KK) / K, q = i % K; off = (ci * K + r) * cols + q; }
+        tab[i] = off;
+    }
+    for (int i = threadIdx.x; i < Cin * K * cols; i += blockDim.x) {
+        const int c = i % cols, r = (i / cols) % K, ci = i / (cols * K);
+        const int ih = ho * S - P + r, iw = wo0 * S - P + c;
+        tile[i] = (ih >= 0 && ih < H && iw >= 0 && iw < W) ? __ldg(x + (((size_t)n * Cin + ci) * H + ih) * W + iw) : 0.f;
+    }
+    __syncthreads();
+    const int npx = min(kI2cPix, Wo - wo0);
+    uint4* dst = reinterpret_cast<uint4*>(out) + (((size_t)n * Ho + ho) * Wo + wo0) * Kp8;
+    for (int i = threadIdx.x; i < npx * Kp8; i += blockDim.x) {
+        const int px = i / Kp8, k8 = i % Kp8;
         float f[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const int kk = k8 * 8 + j;
-            float v = 0.f;
-            if (kk < Ktot) {
-                const int ci = kk / KK, r = (kk % KK) / K, q = kk % K;
-                const int ih = ho * S - P + r, iw = wo * S - P + q;
-                if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * Cin + ci) * H + ih) * W + iw);
-            }
-            f[j] = v;
+            const int off = tab[k8 * 8 + j];
+            f[j] = off >= 0 ? tile[off + px * S] : 0.f;
         }
-        *(reinterpret_cast<uint4*>(out) + idx) = pack8(f, dtype);
+        dst[i] = pack8(f, dtype);
     }
 }
 
@@ -102,6 +114,34 @@ unpack_wgrad_batched_kernel(const float* __restrict__ src_base, float* __restric
             dp[i] += row[t * e.I + ci];
         }
         __syncthreads();
+    }
+}
+
+// Every tensor-core filter bank of a model in ONE launch (training repacks after each optimizer step): for table entry e
+// the fp32 OIHW master at src -> the forward bank [O][K*K][I] at dst_fwd and the data-gradient bank(s) at dst_bank
+// (same layouts as pack_conv_weight_kernel / pack_dgrad_weight_kernel). blockIdx.y = entry.
+struct PackEntry { long long src, dst_fwd, dst_bank; int O, I, K, stride; };
+__global__ void __launch_bounds__(256)
+pack_weights_batched_kernel(const float* __restrict__ src_base, uint16_t* __restrict__ dst_base,
+                            const PackEntry* __restrict__ table, int dtype) {
+    const PackEntry e = table[blockIdx.y];
+    const float* w = src_base + e.src;
+    const int T = e.K * e.K;
+    const size_t n = (size_t)e.O * T * e.I;
+    uint16_t* fwd = dst_base + e.dst_fwd;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        const int i = idx % e.I, t = (idx / e.I) % T, o = idx / ((size_t)e.I * T);
+        fwd[idx] = f2h(w[((size_t)o * e.I + i) * T + t], dtype);
+    }
+    const int nbanks = (e.stride == 2 && e.K == 3) ? 4 : 1;
+    uint16_t* bank = dst_base + e.dst_bank;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < n * nbanks; idx += (size_t)gridDim.x * blockDim.x) {
+        const int o = idx % e.O, t = (idx / e.O) % T, i = (idx / ((size_t)e.O * T)) % e.I, b = idx / n;
+        int r, s2;
+        if (e.stride == 1) { r = e.K - 1 - t / e.K; s2 = e.K - 1 - t % e.K; }
+        else if (e.K == 1) { r = 0; s2 = 0; }
+        else { r = dgrad_s2_src(b >> 1, t / 3); s2 = dgrad_s2_src(b & 1, t % 3); }
+        bank[idx] = f2h((r < 0 || s2 < 0) ? 0.f : w[(((size_t)o * e.I + i) * e.K + r) * e.K + s2], dtype);
     }
 }
 
@@ -360,6 +400,15 @@ extern "C" int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_bas
     return 0;
 }
 
+extern "C" int vu_pack_weights_batched(const float* src_base, void* dst_base, const void* table, int n_entries, int dtype,
+                                       vu_stream_t st) {
+    if (!src_base || !dst_base || !table || n_entries < 1) return set_error(VU_ERR_INVALID, "pack_weights_batched: bad args");
+    dim3 grid(48, n_entries);
+    pack_weights_batched_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(src_base, (uint16_t*)dst_base, (const PackEntry*)table, dtype);
+    VU_CHECK_LAUNCH("pack_weights_batched");
+    return 0;
+}
+
 extern "C" int vu_pack_rows_padded(const float* w, void* out, int O, int I, int I_pad, int dtype, vu_stream_t st) {
     if (!w || !out || O < 1 || I < 1 || I_pad < I) return set_error(VU_ERR_INVALID, "pack_rows_padded: bad args");
     pack_rows_padded_kernel<<<grid_for((size_t)O * I_pad, 256), 256, 0, (cudaStream_t)st>>>(w, (uint16_t*)out, O, I, I_pad, dtype);
@@ -372,9 +421,12 @@ extern "C" int vu_im2col_small_cin(const float* x_nchw, void* out, int N, int Ci
     if (!x_nchw || !out || Cin < 1 || K < 1 || S < 1 || Kp % 8 || Kp < Cin * K * K)
         return set_error(VU_ERR_INVALID, "im2col_small_cin: bad args (Kp multiple of 8, >= Cin*K*K)");
     const int Ho = (H + 2 * P - K) / S + 1, Wo = (W + 2 * P - K) / S + 1;
-    const size_t total = (size_t)N * Ho * Wo * (Kp / 8);
-    im2col_small_cin_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(x_nchw, (uint16_t*)out, N, Cin, H, W, K, S, P,
-                                                                               Ho, Wo, Kp / 8, dtype);
+    if (Cin > 4 || K > 7 || S > 2) return set_error(VU_ERR_UNSUPPORTED, "im2col_small_cin: Cin <= 4, K <= 7, S <= 2");
+    const int cols = (kI2cPix - 1) * S + K;
+    const size_t smem = (size_t)Cin * K * cols * sizeof(float) + (size_t)Kp * sizeof(int);
+    dim3 grid((Wo + kI2cPix - 1) / kI2cPix, Ho, N);
+    im2col_small_cin_kernel<<<grid, 256, smem, (cudaStream_t)st>>>(x_nchw, (uint16_t*)out, N, Cin, H, W, K, S, P, Ho, Wo,
+                                                                  Kp / 8, dtype);
     VU_CHECK_LAUNCH("im2col_small_cin");
     return 0;
 }

@@ -36,16 +36,55 @@ from .ops import Act
 _ALIGN = 64   # floats: every parameter starts on a 256-byte boundary of the flat buffers
 
 
-class _Conv:
-    """A tensor-core convolution of the model: live 16-bit filter bank + data-gradient banks, repacked every step."""
-    __slots__ = ("name", "k", "stride", "w16", "banks_t", "banks")
+BUCKET_ORDER = ("decoder", "latent", "layer4", "layer3", "rest")     # the order the backward finishes them
+_BUCKET_PREFIXES = {
+    "decoder": ("decoder_blocks.", "final_conv."),
+    "latent": ("mu_head.", "logvar_head.", "z_initial."),
+    "layer4": ("encoder.layer4.",),
+    "layer3": ("encoder.layer3.",),
+    "rest": ("encoder.conv1.", "encoder.bn1.", "encoder.layer1.", "encoder.layer2."),
+}
 
-    def __init__(self, name, w, k, stride, dt, dev):
+
+def param_layout(named_shapes):
+    """Flat-buffer layout of the parameters (host logic, no device): every parameter starts on a 256-byte boundary, in
+    `named_parameters()` order. -> (offsets {name: float offset}, total floats, buckets {name: (lo, hi)}): the buckets are
+    contiguous, disjoint ranges that cover the whole buffer; each is all-reduced as soon as the backward has finished it."""
+    offs, total = {}, 0
+    for n, shape in named_shapes:
+        k = 1
+        for d in shape:
+            k *= int(d)
+        offs[n] = total
+        total += (k + _ALIGN - 1) // _ALIGN * _ALIGN
+    names = [n for n, _ in named_shapes]
+    ends = {n: (offs[names[i + 1]] if i + 1 < len(names) else total) for i, n in enumerate(names)}
+    buckets = {}
+    for b, prefixes in _BUCKET_PREFIXES.items():
+        ks = [n for n in names if n.startswith(prefixes)]
+        if ks:
+            buckets[b] = (min(offs[n] for n in ks), max(ends[n] for n in ks))
+    return offs, total, buckets
+
+
+class _Conv:
+    """A tensor-core convolution of the model: live 16-bit filter bank + data-gradient banks (views of one flat 16-bit
+    buffer, repacked from the fp32 masters by one batched launch per step)."""
+    __slots__ = ("name", "k", "stride", "w16", "banks_t", "banks", "n_fwd", "n_bank")
+
+    def __init__(self, name, w, k, stride):
         O, I = w.shape[:2]
         self.name, self.k, self.stride = name, k, stride
-        self.w16 = torch.empty((O, k * k, I), dtype=ops._TORCH_DT[dt], device=dev)
         nb = 4 if (stride == 2 and k == 3) else 1
-        self.banks_t = torch.empty((nb, I, k * k, O), dtype=ops._TORCH_DT[dt], device=dev)
+        self.n_fwd = O * I * k * k
+        self.n_bank = nb * self.n_fwd
+
+    def bind(self, flat16, off_fwd, off_bank, w):
+        O, I = w.shape[:2]
+        k = self.k
+        nb = self.n_bank // self.n_fwd
+        self.w16 = flat16[off_fwd:off_fwd + self.n_fwd].view(O, k * k, I)
+        self.banks_t = flat16[off_bank:off_bank + self.n_bank].view(nb, I, k * k, O)
         self.banks = [self.banks_t[b] for b in range(nb)]
 
 
@@ -87,10 +126,7 @@ class TrainStep:
     # ------------------------------------------------------------------ parameter storage
     def _flatten(self):
         named = [(n, p) for n, p in self.model.named_parameters()]
-        offs, total = {}, 0
-        for n, p in named:
-            offs[n] = total
-            total += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        offs, total, self.buckets = param_layout([(n, tuple(p.shape)) for n, p in named])
         dev = self.dev
         self.flat_p = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
@@ -109,19 +145,6 @@ class TrainStep:
             self.P[n], self.G[n] = view, g
         self.Bf = dict(self.model.named_buffers())
         self.nbt = [b for n, b in self.Bf.items() if n.endswith("num_batches_tracked")]
-        # contiguous ranges of the flat gradient, in the order the backward finishes them (for bucketed all-reduce)
-        def rng(prefix_list):
-            ks = [n for n, _ in named if any(n.startswith(pf) for pf in prefix_list)]
-            lo = min(offs[n] for n in ks)
-            hi = max(offs[n] + (self.P[n].numel() + _ALIGN - 1) // _ALIGN * _ALIGN for n in ks)
-            return lo, hi
-        self.buckets = {
-            "decoder": rng(["decoder_blocks.", "final_conv."]),
-            "latent": rng(["mu_head.", "logvar_head.", "z_initial."]),
-            "layer4": rng(["encoder.layer4."]),
-            "layer3": rng(["encoder.layer3."]),
-            "rest": rng(["encoder.conv1.", "encoder.bn1.", "encoder.layer1.", "encoder.layer2."]),
-        }
 
     def _register_convs(self):
         self.convs: Dict[str, _Conv] = {}
@@ -138,10 +161,23 @@ class TrainStep:
                 li, b = int(n.split(".")[1][5:]), int(n.split(".")[2])
                 if li > 1 and b == 0 and (".conv1." in n or ".downsample." in n):
                     stride = 2
-            self.convs[n[:-len(".weight")]] = _Conv(n, w, k, stride, self.dt, self.dev)
+            self.convs[n[:-len(".weight")]] = _Conv(n, w, k, stride)
         ws = self.P["encoder.conv1.weight"]
         kp = (ws[0].numel() + 7) // 8 * 8
         self.stem_w16 = torch.empty((ws.shape[0], 1, kp), dtype=ops._TORCH_DT[self.dt], device=self.dev)
+        import struct
+        a16 = lambda v: (v + 127) // 128 * 128                  # 256-byte aligned 16-bit offsets (TMA base alignment)
+        tot16, recs = 0, []
+        for name, c in self.convs.items():
+            off_fwd = tot16; tot16 += a16(c.n_fwd)
+            off_bank = tot16; tot16 += a16(c.n_bank)
+            w = self.P[c.name]
+            recs.append((c, off_fwd, off_bank, struct.pack("<qqqiiii", self.offs[c.name], off_fwd, off_bank, w.shape[0],
+                                                           w.shape[1], c.k, c.stride)))
+        self.flat16 = torch.zeros(tot16, dtype=ops._TORCH_DT[self.dt], device=self.dev)
+        for c, off_fwd, off_bank, _ in recs:
+            c.bind(self.flat16, off_fwd, off_bank, self.P[c.name])
+        self.pack_table = torch.frombuffer(bytearray(b"".join(r[3] for r in recs)), dtype=torch.uint8).to(self.dev)
         # The wgrad kernel accumulates in its packed layout [O][k*k][I] (contiguous 16-byte vector reductions); one batched
         # launch per all-reduce bucket transposes those into the parameters' OIHW .grad views.
         total = 0
@@ -169,18 +205,12 @@ class TrainStep:
                 self.unpack_tables[bname] = (tab, len(recs), max_row)
 
     def repack(self):
-        """fp32 master filters -> 16-bit tensor-core banks (forward + data-gradient), once per step."""
-        lib = ops.load()
-        st = ops._stream()
-        for c in self.convs.values():
-            w = self.P[c.name]
-            O, I = w.shape[:2]
-            ops.check(lib.vu_pack_conv_weight(w.data_ptr(), c.w16.data_ptr(), O, I, c.k, c.k, 0, self.dt, st), "vu_pack_conv_weight")
-            ops.check(lib.vu_pack_dgrad_weight(w.data_ptr(), c.banks_t.data_ptr(), O, I, c.k, c.stride, self.dt, st),
-                      "vu_pack_dgrad_weight")
+        """fp32 master filters -> 16-bit tensor-core banks (forward + data-gradient): one batched launch per step."""
+        ops.check(ops.load().vu_pack_weights_batched(self.flat_p.data_ptr(), self.flat16.data_ptr(), self.pack_table.data_ptr(),
+                                                     len(self.convs), self.dt, ops._stream()), "vu_pack_weights_batched")
         ws = self.P["encoder.conv1.weight"]
         T.pack_rows_padded(ws, self.stem_w16.shape[2], self.dt, out=self.stem_w16)
-        ops._count(2 * len(self.convs))
+        ops._count(2)
 
     # ------------------------------------------------------------------ small helpers
     def _conv(self, x: Act, name: str, bias: Optional[torch.Tensor] = None, out: Optional[Act] = None) -> Act:
