@@ -467,6 +467,11 @@ class TrainStep:
             ops.check(ops.load().vu_unpack_wgrad_batched(self.flat_gp.data_ptr(), self.flat_g.data_ptr(), tab.data_ptr(), n,
                                                          max_row, ops._stream()), "vu_unpack_wgrad_batched")
             ops._count()
+        self._start_all_reduce(name)
+
+    def _start_all_reduce(self, name: str):
+        """Asynchronous NCCL all-reduce (sum) of one contiguous range of the flat gradient; the 1/world average is folded
+        into the AdamW kernel's gradient scale."""
         if self.pg is None or self.world == 1:
             return
         import torch.distributed as dist
