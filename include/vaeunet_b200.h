@@ -236,7 +236,9 @@ int vu_confusion_counts(const float* x, const float* t, size_t n, float thr, dou
  * vu_bn_stats -> sums[0..C) = sum x, sums[C..2C) = sum x^2 (fp64); vu_bn_finalize -> mean / invstd (biased var, eps)
  * and the running statistics update (momentum, unbiased var); vu_bn_apply -> y = act(gamma*(x-mean)*invstd + beta
  * + residual). vu_bn_bwd: dz = dy * (y_relu > 0 if y_relu), sums <- (sum dz, sum dz*xhat) = (dbeta, dgamma) in fp64,
- * dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dz_out (optional) receives dz (residual-branch gradient). */
+ * dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dz_out (optional) receives dz (residual-branch gradient).
+ * relu_beta (optional, with y_relu NULL): the layer was BN + ReLU without a residual - the mask is recomputed from x with
+ * the forward's own expressions (gamma*invstd*x + beta - mean*gamma*invstd > 0), saving the read of y in both passes. */
 int vu_bn_stats(const void* x, size_t npix, int C, int x_ctot, int x_coff, double* sums, int dtype, vu_stream_t stream);
 int vu_bn_finalize(const double* sums, double count, int C, float eps, float momentum, float* mean, float* invstd,
                    float* running_mean, float* running_var, vu_stream_t stream);
@@ -246,7 +248,7 @@ int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const
 int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot, int dy_coff,
               const void* y_relu, int y_ctot, int y_coff, const float* mean, const float* invstd, const float* gamma,
               double* sums, void* dx, int dx_ctot, int dx_coff, void* dz_out, int dz_ctot, int dz_coff,
-              float* dgamma /* += , optional */, float* dbeta /* += */, int dtype, vu_stream_t stream);
+              float* dgamma /* += , optional */, float* dbeta /* += */, const float* relu_beta, int dtype, vu_stream_t stream);
 /* dst += src (gradient accumulation over the consumers of an activation). */
 int vu_add_nhwc(void* dst, int d_ctot, int d_coff, const void* src, int s_ctot, int s_coff, size_t npix, int C,
                 int dtype, vu_stream_t stream);

@@ -46,6 +46,22 @@ def test_conv_wgrad(case, cuda_dev):
     assert (got - ref).abs().max().item() <= 1e-3 * ref.abs().max().item() + 1e-4
 
 
+def test_conv_wgrad_row_kernel(cuda_dev, monkeypatch):
+    """The filter-row kernel (3 taps per work item from one halo'd X tile) forced on for small shapes, incl. ragged tiles."""
+    from vaeunet_b200 import ops
+    monkeypatch.setenv("VU_WGRAD_ROW3", "1")
+    for case in [("r3_64_64", 2, 32, 32, 64, 64, 3, 1), ("r3_224_64", 1, 24, 130, 224, 64, 3, 1), ("r3_128_256", 3, 16, 16, 128, 256, 3, 1),
+                 ("r3_ksplit", 4, 128, 128, 64, 64, 3, 1), ("r3_ragged", 2, 20, 48, 32, 96, 3, 1)]:
+        name, N, H, W, Cin, Cout, k, stride = case
+        x, w, dy, pad = _setup(case, cuda_dev)
+        wr = w.clone().requires_grad_(True)
+        F.conv2d(x, wr, None, stride, pad).backward(dy)
+        xa = ops.Act(x.permute(0, 2, 3, 1).contiguous().bfloat16().to(cuda_dev))
+        dya = ops.Act(dy.permute(0, 2, 3, 1).contiguous().bfloat16().to(cuda_dev))
+        got = ops.unpack_wgrad(ops.conv2d_wgrad(xa, dya, k, stride, pad), k).cpu()
+        assert ((got - wr.grad).norm() / wr.grad.norm()).item() < 2e-4, name
+
+
 @pytest.mark.parametrize("case", [c for c in CASES if c[2] % 2 == 0 or c[7] == 1], ids=lambda c: c[0].replace("wg", "dg"))
 def test_conv_dgrad(case, cuda_dev):
     from vaeunet_b200 import ops
@@ -111,6 +127,10 @@ def test_bn_train_fwd_bwd(cuda_dev, C, relu, res):
     assert ((_nchw(dx) - xr.grad).norm() / xr.grad.norm()).item() < 1.5e-2
     assert ((dgam.cpu() - gr.grad).norm() / gr.grad.norm()).item() < 5e-3
     assert ((dbet.cpu() - br.grad).norm() / br.grad.norm()).item() < 5e-3
+    if relu and not res:     # ReLU mask recomputed from x (no read of y): identical result
+        dx2, dgam2, dbet2, _ = T.bn_train_bwd(xa, _act(ops, dy, d), None, mean, invstd, gamma.to(d), relu_beta=beta.to(d))
+        assert (dx2.t.float() - dx.t.float()).abs().max() <= 1e-2 * dx.t.float().abs().max()      # fp64 atomics order
+        assert torch.allclose(dgam2, dgam, rtol=1e-5, atol=1e-6) and torch.allclose(dbet2, dbet, rtol=1e-5, atol=1e-6)
     if res:
         mask = (y.detach() > 0).float() if relu else torch.ones_like(dy)
         assert ((_nchw(dz) - dy * mask).norm() / (dy * mask).norm()).item() < 5e-3

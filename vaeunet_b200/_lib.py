@@ -75,7 +75,7 @@ SIGNATURES = {
     "vu_bn_stats": [p, sz, i, i, i, p, i, p],
     "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
     "vu_bn_apply": [p, sz, i, i, i, p, p, p, p, p, i, i, i, p, i, i, i, p],
-    "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, i, p],
+    "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, p, i, p],
     "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],
     "vu_maxpool_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],
     "vu_maxpool_idx_fwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, p],

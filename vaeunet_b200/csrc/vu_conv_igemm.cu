@@ -330,8 +330,9 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         if (best < 0 || cost < best) { best = cost; bn = cand; }
     }
     const int sms = num_sms();
-    // only drop from 256 to 128 columns when that is needed to reach one wave of tiles
-    while (bn > 128 && (long)kp.num_m_tiles * ((a->Cout + bn - 1) / bn) < sms) bn >>= 1;
+    // only drop from 256 to 128 columns when the wide tiles would leave more than ~40 % of the SMs idle: a single
+    // 86 %-full wave of 256-column tiles moves fewer bytes through L2 than two rounds of 128-column tiles
+    while (bn > 128 && (long)kp.num_m_tiles * ((a->Cout + bn - 1) / bn) * 5 < (long)sms * 3) bn >>= 1;
     kp.num_n_tiles = (a->Cout + bn - 1) / bn;
 
     // activation tensor maps

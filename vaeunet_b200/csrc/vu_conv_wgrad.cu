@@ -176,6 +176,151 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// 3x3 stride-1 weight gradient, one filter ROW (3 taps) per work item. The per-tap kernel above re-reads the dY tile and the
+// X tile for every tap and is bound by L2->SM traffic (ncu: 9.5 TB/s, tensor pipe < 25 %). Here a k-iteration loads the dY
+// tile once and the X tile once with a one-pixel halo on both sides of every tile row (box (64 ch, wt+2, ht, nt) at
+// w0-1, h0+r-1), and issues the MMAs of the three taps s = 0,1,2 from it: tap s reads the same shared-memory tile with
+// the operand descriptor advanced by s pixel rows (128 B each; the 128-byte swizzle is a function of the absolute
+// shared-memory address, the property vu_conv_halo.cu relies on). Three fp32 accumulators of BN columns live in TMEM.
+// Traffic per 3 taps: 32 KB (dY) + ~36 KB (X) instead of 3 x 64 KB.
+struct WgradRow3Params {
+    int wt, ht, nt, tiles_w, tiles_h, tiles_n, num_pix_tiles;
+    int num_m_tiles, num_n_tiles, ksplit, tiles_per_split;
+    int cout, cin;
+    int b_atom_bytes;        // (wt+2)*ht*nt*128 rounded up to 1024
+    int b_box_bytes;         // (wt+2)*ht*nt*128
+    int stage_bytes, stages;
+    float* dw;               // packed [Cout][9][Cin]
+    int dtype;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv_wgrad_row3_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_xh,
+                       const WgradRow3Params p) {
+    constexpr int kTmemCols = 512;                 // 3 accumulators x BN (<= 128) columns
+    constexpr int kMaxStages = 4;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const int stages = p.stages;
+    const uint32_t bar_base = smem_base + stages * p.stage_bytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
+    const uint32_t done_bar = bar_base + 8u * (2 * kMaxStages);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 1);
+    volatile uint32_t* tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t*>(smem_al + stages * p.stage_bytes + 8 * (2 * kMaxStages + 1));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_dy);
+        tma_prefetch_desc(&map_xh);
+        for (int s = 0; s < stages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(done_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<kTmemCols>(tmem_slot);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    // work item = blockIdx.x -> (ksplit, n_tile, m_tile, r), r fastest (neighbouring CTAs share pixel tiles in L2)
+    int item = blockIdx.x;
+    const int r = item % 3; item /= 3;
+    const int m_tile = item % p.num_m_tiles; item /= p.num_m_tiles;
+    const int n_tile = item % p.num_n_tiles; item /= p.num_n_tiles;
+    const int ks = item;
+    const int t_begin = ks * p.tiles_per_split;
+    const int t_end = min(p.num_pix_tiles, t_begin + p.tiles_per_split);
+    const int n_iters = max(0, t_end - t_begin);
+    const int pitch = p.wt + 2;                    // pixels per tile row of the halo'd X tile
+
+    if (warp == 0) {
+        if (elect_one()) {
+            for (int i = 0; i < n_iters; ++i) {
+                const int t = t_begin + i;
+                const int wb = t % p.tiles_w;
+                const int hb = (t / p.tiles_w) % p.tiles_h;
+                const int nb = t / (p.tiles_w * p.tiles_h);
+                const int w0 = wb * p.wt, h0 = hb * p.ht, n0 = nb * p.nt;
+                const int s = i % stages;
+                mbar_wait(empty_bar(s), ((i / stages) & 1) ^ 1);
+                const uint32_t sa = smem_base + s * p.stage_bytes;
+                mbar_arrive_expect_tx(full_bar(s), kWgABytes + (BN / 64) * p.b_box_bytes);
+                tma_load_4d(sa, &map_dy, full_bar(s), m_tile * 128, w0, h0, n0);
+                tma_load_4d(sa + kWgAtomBytes, &map_dy, full_bar(s), m_tile * 128 + 64, w0, h0, n0);
+#pragma unroll
+                for (int a = 0; a < BN / 64; ++a)
+                    tma_load_4d(sa + kWgABytes + a * p.b_atom_bytes, &map_xh, full_bar(s), n_tile * BN + a * 64, w0 - 1,
+                                h0 + r - 1, n0);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        const uint32_t idesc = umma_idesc_f16(128, BN, p.dtype == 0 ? 1u : 0u) | (1u << 15) | (1u << 16);
+        for (int i = 0; i < n_iters; ++i) {
+            const int s = i % stages;
+            mbar_wait(full_bar(s), (i / stages) & 1);
+            tc_fence_after();
+            const uint32_t sa = smem_base + s * p.stage_bytes;
+            const uint64_t adesc = umma_desc_mn_sw128(sa, kWgAtomBytes);
+            const uint64_t bdesc = umma_desc_mn_sw128(sa + kWgABytes, p.b_atom_bytes);
+            if (elect_one()) {
+#pragma unroll 1
+                for (int k = 0; k < kWgPix / 16; ++k) {     // 16 tile pixels (inside one tile row: wt % 16 == 0)
+                    const int lin = k * 16;
+                    const uint32_t brow = (lin / p.wt) * pitch + (lin % p.wt);     // halo'd row index of tap s = 0
+#pragma unroll
+                    for (int sx = 0; sx < 3; ++sx)
+                        umma_f16_ss(tmem_base + sx * BN, adesc + 128u * k, bdesc + 8u * (brow + sx), idesc, (i | k) != 0);
+                }
+                umma_commit(empty_bar(s));
+                if (i == n_iters - 1) umma_commit(done_bar);
+            }
+            __syncwarp();
+        }
+    } else if (n_iters > 0) {
+        const int q = warp & 3;
+        const int co = m_tile * 128 + q * 32 + lane;
+        mbar_wait(done_bar, 0);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int sx = 0; sx < 3; ++sx) {
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(taddr + sx * BN + c * 32, v);
+                tmem_ld_wait();
+                const int ci0 = n_tile * BN + c * 32;
+                if (co < p.cout) {
+                    float* dst = p.dw + (static_cast<size_t>(co) * 9 + r * 3 + sx) * p.cin + ci0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        if (ci0 + j < p.cin)
+                            red_add_v4_f32(dst + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                           __uint_as_float(v[j + 3]));
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
 }  // namespace vu
 
 using namespace vu;
@@ -206,6 +351,90 @@ static int launch_wgrad(const CUtensorMap& dym, const CUtensorMap* xm, const Wgr
     return 0;
 }
 
+// tile (wt, ht, nt) with wt a multiple of 16 (a 16-pixel MMA K step must stay inside one tile row), product 128
+static bool wg_choose_tile_row3(int n, int h, int w, int* wt_o, int* ht_o, int* nt_o) {
+    double best = -1.0;
+    for (int wt = 128; wt >= 16; wt >>= 1)
+        for (int ht = 128 / wt; ht >= 1; ht >>= 1) {
+            const int nt = 128 / (wt * ht);
+            const double cover = (double)((w + wt - 1) / wt * wt) * ((h + ht - 1) / ht * ht) * ((n + nt - 1) / nt * nt);
+            const double eff = (double)w * h * n / cover;
+            if (eff > best + 1e-9) { best = eff; *wt_o = wt; *ht_o = ht; *nt_o = nt; }
+        }
+    return best >= 0.75;        // narrow / ragged maps stay on the per-tap kernel
+}
+
+template <int BN>
+static int launch_wgrad_row3(const CUtensorMap& dym, const CUtensorMap& xhm, const WgradRow3Params& wp, int grid, size_t smem,
+                             cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv_wgrad_row3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(wgrad row3): %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    conv_wgrad_row3_kernel<BN><<<grid, kWgThreads, smem, stream>>>(dym, xhm, wp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_wgrad_row3 launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// returns 1 when it took the launch, 0 when the shape is not its case, < 0 on error
+static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, cudaStream_t stream) {
+    if (!(a->KH == 3 && a->KW == 3 && a->stride == 1 && a->pad == 1)) return 0;
+    if (getenv("VU_WGRAD_PER_TAP")) return 0;
+    WgradRow3Params wp{};
+    if (!wg_choose_tile_row3(a->N, a->H, a->W, &wp.wt, &wp.ht, &wp.nt)) return 0;
+    const int Ho = a->H, Wo = a->W;
+    wp.tiles_w = (Wo + wp.wt - 1) / wp.wt; wp.tiles_h = (Ho + wp.ht - 1) / wp.ht; wp.tiles_n = (a->N + wp.nt - 1) / wp.nt;
+    wp.num_pix_tiles = wp.tiles_w * wp.tiles_h * wp.tiles_n;
+    // measured on B200 (scripts/prof_wgrad.py): the row kernel wins from 2048 pixel tiles up (+30..60 %), the per-tap kernel
+    // below 512 (three times more work items keep the K splits long enough to amortise prologue + reductions)
+    if (wp.num_pix_tiles < 1024 && !getenv("VU_WGRAD_ROW3")) return 0;
+    wp.cout = a->Cout; wp.cin = a->Cin; wp.dw = dw; wp.dtype = a->dtype;
+    const int bn = (a->Cin > 64) ? 128 : 64;
+    wp.num_m_tiles = (a->Cout + 127) / 128;
+    wp.num_n_tiles = (a->Cin + bn - 1) / bn;
+    wp.b_box_bytes = (wp.wt + 2) * wp.ht * wp.nt * 128;
+    wp.b_atom_bytes = (wp.b_box_bytes + 1023) / 1024 * 1024;
+    wp.stage_bytes = kWgABytes + (bn / 64) * wp.b_atom_bytes;
+    const int smem_budget = 227 * 1024 - 1024 /*align slack*/ - 256 /*barriers*/;
+    wp.stages = smem_budget / wp.stage_bytes;
+    if (wp.stages > 4) wp.stages = 4;
+    if (wp.stages < 2) return 0;
+    const int base_items = 3 * wp.num_m_tiles * wp.num_n_tiles;
+    int ksplit = (2 * num_sms() + base_items - 1) / base_items;
+    if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
+    if (ksplit < 1) ksplit = 1;
+    wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;
+    wp.ksplit = (wp.num_pix_tiles + wp.tiles_per_split - 1) / wp.tiles_per_split;
+
+    CUtensorMap dym, xhm;
+    {
+        const uint32_t box[4] = {64u, (uint32_t)wp.wt, (uint32_t)wp.ht, (uint32_t)wp.nt};
+        const uint16_t* db = static_cast<const uint16_t*>(dy) + dy_coff;
+        const uint64_t pix = (uint64_t)dy_ctot * 2;
+        const uint64_t dims[4] = {(uint64_t)a->Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * Wo, pix * Wo * Ho};
+        int rc = encode_map(&dym, a->dtype, 4, db, dims, str, box);
+        if (rc) return rc;
+    }
+    {
+        const uint32_t box[4] = {64u, (uint32_t)(wp.wt + 2), (uint32_t)wp.ht, (uint32_t)wp.nt};
+        const uint16_t* xb = static_cast<const uint16_t*>(a->x) + a->x_coff;
+        const uint64_t pix = (uint64_t)a->x_ctot * 2;
+        const uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->N};
+        const uint64_t str[3] = {pix, pix * a->W, pix * a->W * a->H};
+        int rc = encode_map(&xhm, a->dtype, 4, xb, dims, str, box);
+        if (rc) return rc;
+    }
+    const int grid = base_items * wp.ksplit;
+    const size_t smem = 1024 + (size_t)wp.stages * wp.stage_bytes + 256;
+    int rc = (bn == 128) ? launch_wgrad_row3<128>(dym, xhm, wp, grid, smem, stream)
+                         : launch_wgrad_row3<64>(dym, xhm, wp, grid, smem, stream);
+    return rc ? rc : 1;
+}
+
 static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy_coff, float* dw, bool oihw,
                       vu_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -218,6 +447,10 @@ static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy
     if ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(dy)) & 15)
         return set_error(VU_ERR_ALIGN, "wgrad: pointers must be 16-byte aligned");
     const int Ho = (a->H + 2 * P - KH) / S + 1, Wo = (a->W + 2 * P - KW) / S + 1;
+    if (!oihw) {
+        const int rc = wgrad_row3_try(a, dy, dy_ctot, dy_coff, dw, stream);
+        if (rc != 0) return rc < 0 ? rc : 0;
+    }
 
     WgradParams wp{};
     wg_choose_tile(a->N, Ho, Wo, &wp.wt, &wp.ht, &wp.nt);

@@ -26,7 +26,8 @@ __global__ void __launch_bounds__(256)
 channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy,
                     int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
                     const float* __restrict__ mean, const float* __restrict__ invstd, size_t npix, int C8,
-                    double* __restrict__ sums, int dtype) {
+                    double* __restrict__ sums, int dtype, const float* __restrict__ gamma = nullptr,
+                    const float* __restrict__ relu_beta = nullptr) {
     extern __shared__ float sm[];   // [2][lanes][C8*8]
     const int lanes = 256 / C8;
     const int c8 = threadIdx.x % C8, pl = threadIdx.x / C8;
@@ -34,10 +35,15 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
     float a0[8], a1[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
-    float mu[8], is[8];
+    float mu[8], is[8], msc[8], msh[8];
     if (MODE == 1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { mu[j] = mean[c8 * 8 + j]; is[j] = invstd[c8 * 8 + j]; }
+        for (int j = 0; j < 8; ++j) {
+            mu[j] = mean[c8 * 8 + j]; is[j] = invstd[c8 * 8 + j];
+            // ReLU mask recomputed from x exactly as bn_apply_kernel computed the output (no read of y)
+            msc[j] = relu_beta ? is[j] * gamma[c8 * 8 + j] : 0.f;
+            msh[j] = relu_beta ? relu_beta[c8 * 8 + j] - mu[j] * msc[j] : 0.f;
+        }
     }
     if (pl < lanes) {
         const size_t step = (size_t)gridDim.x * lanes;
@@ -72,6 +78,9 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
                     unpack8(vy, o, dtype);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+                } else if (relu_beta != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) g[j] = fmaf(f[j], msc[j], msh[j]) > 0.f ? g[j] : 0.f;
                 }
 #pragma unroll
                 for (int j = 0; j < 8; ++j) { a0[j] += g[j]; a1[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], a1[j]); }
@@ -188,13 +197,13 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const double* __restrict__ sums, double count, uint16_t* __restrict__ dx, int dx_ctot, int dx_coff,
                     uint16_t* __restrict__ dz_out, int dz_ctot, int dz_coff, size_t npix, int C8, int dtype,
-                    float* __restrict__ dgamma, float* __restrict__ dbeta) {
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, const float* __restrict__ relu_beta) {
     const size_t total = npix * C8;
     const int C = C8 * 8;
     if (blockIdx.x == 0 && dgamma != nullptr)      // parameter gradients, accumulated (gradient accumulation steps)
         for (int c = threadIdx.x; c < C; c += blockDim.x) { dgamma[c] += (float)sums[C + c]; dbeta[c] += (float)sums[c]; }
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    float ka[8], kb[8], kc[8];
+    float ka[8], kb[8], kc[8], msc[8], msh[8];
     auto coeff = [&](int c8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -204,6 +213,8 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
             ka[j] = a;
             kb[j] = -a * m_dzx * is;
             kc[j] = -a * m_dz - kb[j] * mean[c];
+            msc[j] = is * gamma[c];                                   // same expressions as bn_apply_kernel
+            msh[j] = relu_beta ? relu_beta[c] - mean[c] * msc[j] : 0.f;
         }
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -220,6 +231,9 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
             unpack8(vy, o, dtype);
 #pragma unroll
             for (int j = 0; j < 8; ++j) g[j] = o[j] > 0.f ? g[j] : 0.f;
+        } else if (relu_beta != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[j] = fmaf(f[j], msc[j], msh[j]) > 0.f ? g[j] : 0.f;
         }
         if (dz_out != nullptr) *(reinterpret_cast<uint4*>(dz_out + p * dz_ctot + dz_coff) + c8) = pack8(g, dtype);
         float o[8];
@@ -313,7 +327,8 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
 extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot,
                          int dy_coff, const void* y_relu, int y_ctot, int y_coff, const float* mean,
                          const float* invstd, const float* gamma, double* sums, void* dx, int dx_ctot, int dx_coff,
-                         void* dz_out, int dz_ctot, int dz_coff, float* dgamma, float* dbeta, int dtype, vu_stream_t st) {
+                         void* dz_out, int dz_ctot, int dz_coff, float* dgamma, float* dbeta, const float* relu_beta, int dtype,
+                         vu_stream_t st) {
     if (!x || !dy || !mean || !invstd || !gamma || !sums || !dx || C < 8 || C > 1024 || (!dgamma != !dbeta))
         return set_error(VU_ERR_INVALID, "bn_bwd: bad args");
     VU_TR_ALIGN((C | x_ctot | x_coff | dy_ctot | dy_coff | y_ctot | y_coff | dx_ctot | dx_coff | dz_ctot | dz_coff) % 8, "bn_bwd");
@@ -322,19 +337,19 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
     cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), s);
     channel_sums_kernel<1><<<tr_grid(npix, lanes * 8, 8), 256, 2 * lanes * C * sizeof(float), s>>>(
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
-        mean, invstd, npix, C8, sums, dtype);
+        mean, invstd, npix, C8, sums, dtype, gamma, y_relu ? nullptr : relu_beta);
     VU_CHECK_LAUNCH("bn_bwd_reduce");
     const int grid = tr_grid(npix * C8, 256 * 2, 16);
     if (256 % C8 == 0)
         bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
             mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
-            C8, dtype, dgamma, dbeta);
+            C8, dtype, dgamma, dbeta, y_relu ? nullptr : relu_beta);
     else
         bn_bwd_apply_kernel<false><<<grid, 256, 0, s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
             mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
-            C8, dtype, dgamma, dbeta);
+            C8, dtype, dgamma, dbeta, y_relu ? nullptr : relu_beta);
     VU_CHECK_LAUNCH("bn_bwd_apply");
     return 0;
 }

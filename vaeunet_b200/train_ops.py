@@ -45,9 +45,11 @@ def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, res
 
 
 def bn_train_bwd(x_raw: Act, dy: Act, y_relu: Optional[Act], mean, invstd, gamma, want_dz: bool = False,
-                 dx: Optional[Act] = None, dgamma: Optional[torch.Tensor] = None, dbeta: Optional[torch.Tensor] = None):
+                 dx: Optional[Act] = None, dgamma: Optional[torch.Tensor] = None, dbeta: Optional[torch.Tensor] = None,
+                 relu_beta: Optional[torch.Tensor] = None):
     """-> (dx_raw, dgamma, dbeta, dz or None). y_relu: the post-ReLU output (mask) or None when there was no ReLU.
-    dgamma / dbeta (fp32 [C]) are ACCUMULATED into when given (the parameters' .grad), else returned fresh."""
+    dgamma / dbeta (fp32 [C]) are ACCUMULATED into when given (the parameters' .grad), else returned fresh.
+    relu_beta (with y_relu None): BN + ReLU without residual - the mask is recomputed from x_raw (no read of y)."""
     require_device()
     Cc, dev = x_raw.C, x_raw.t.device
     sums = _sums(dev, 2 * Cc)
@@ -62,7 +64,7 @@ def bn_train_bwd(x_raw: Act, dy: Act, y_relu: Optional[Act], mean, invstd, gamma
                            y.t.data_ptr() if y else None, y.ctot if y else 8, y.coff if y else 0, mean.data_ptr(),
                            invstd.data_ptr(), _f32(gamma).data_ptr(), sums.data_ptr(), dx.t.data_ptr(), dx.ctot, dx.coff,
                            dz.t.data_ptr() if dz else None, dz.ctot if dz else 8, dz.coff if dz else 0,
-                           _f32(dgamma).data_ptr(), _f32(dbeta).data_ptr(), x_raw.dt, _stream()), "vu_bn_bwd")
+                           _f32(dgamma).data_ptr(), _f32(dbeta).data_ptr(), _ptr(relu_beta), x_raw.dt, _stream()), "vu_bn_bwd")
     _count(3)
     return dx, dgamma, dbeta, dz
 

@@ -223,9 +223,12 @@ class TrainStep:
                                          Bf[bn + "running_var"], relu, residual, out)
         return y, (mean, invstd)
 
-    def _bn_bwd(self, x_raw: Act, dy: Act, y_relu: Optional[Act], st, bn: str, want_dz=False, dx: Optional[Act] = None):
-        dx, _, _, dz = T.bn_train_bwd(x_raw, dy, y_relu, st[0], st[1], self.P[bn + "weight"], want_dz, dx,
-                                      self.G[bn + "weight"], self.G[bn + "bias"])
+    def _bn_bwd(self, x_raw: Act, dy: Act, y_relu: Optional[Act], st, bn: str, want_dz=False, dx: Optional[Act] = None,
+                mask_from_x: bool = False):
+        """mask_from_x: the layer was BN + ReLU with no residual -> the ReLU mask is recomputed from x_raw (y is not read)."""
+        dx, _, _, dz = T.bn_train_bwd(x_raw, dy, None if mask_from_x else y_relu, st[0], st[1], self.P[bn + "weight"], want_dz,
+                                      dx, self.G[bn + "weight"], self.G[bn + "bias"],
+                                      relu_beta=self.P[bn + "bias"] if mask_from_x else None)
         return dx, dz
 
     def _wgrad(self, x: Act, dy: Act, name: str):
@@ -369,10 +372,10 @@ class TrainStep:
             p, a = r["p"], r["p"] + "attention."
             cat, cx, cs, skip = r["cat"], r["cx"], r["cs"], r["skip"]
             Hs, Ws = skip.H, skip.W
-            dy2raw, _ = self._bn_bwd(r["y2raw"], dy, r["y2"], r["st2"], p + "conv2.1.")
+            dy2raw, _ = self._bn_bwd(r["y2raw"], dy, r["y2"], r["st2"], p + "conv2.1.", mask_from_x=True)
             self._wgrad(r["y1"], dy2raw, p + "conv2.0")
             dy1 = self._dgrad(dy2raw, p + "conv2.0", Hs, Ws)
-            dy1raw, _ = self._bn_bwd(r["y1raw"], dy1, r["y1"], r["st1"], p + "conv1.1.")
+            dy1raw, _ = self._bn_bwd(r["y1raw"], dy1, r["y1"], r["st1"], p + "conv1.1.", mask_from_x=True)
             self._wgrad(cat, dy1raw, p + "conv1.0")
             dcat = self._dgrad(dy1raw, p + "conv1.0", Hs, Ws)
             # z_proj slice: per-image sums -> vector layer backward (accumulates into dz)
@@ -434,7 +437,7 @@ class TrainStep:
             dy2raw, dz_id = self._bn_bwd(r["y2raw"], dout, r["out"], r["st2"], q + "bn2.", want_dz=True)
             self._wgrad(r["y1"], dy2raw, q + "conv2")
             dy1 = self._dgrad(dy2raw, q + "conv2", r["y1"].H, r["y1"].W)
-            dy1raw, _ = self._bn_bwd(r["y1raw"], dy1, r["y1"], r["st1"], q + "bn1.")
+            dy1raw, _ = self._bn_bwd(r["y1raw"], dy1, r["y1"], r["st1"], q + "bn1.", mask_from_x=True)
             self._wgrad(x, dy1raw, q + "conv1")
             if "idraw" in r:
                 dx = self._dgrad(dy1raw, q + "conv1", x.H, x.W)
@@ -452,7 +455,7 @@ class TrainStep:
         f0 = S["f0"]
         df0 = T.maxpool_idx_bwd(S["pool_code"], dout, f0.H, f0.W, 3, 2, 1)
         T.add_(df0, dfeat[0])
-        dx0raw, _ = self._bn_bwd(S["x0raw"], df0, f0, S["st0"], "encoder.bn1.")
+        dx0raw, _ = self._bn_bwd(S["x0raw"], df0, f0, S["st0"], "encoder.bn1.", mask_from_x=True)
         xcol = S["xcol"]
         dw = ops.conv2d_wgrad(xcol, dx0raw, 1, 1, 0)                                   # [64, 1, 152] packed
         gw = G["encoder.conv1.weight"]
