@@ -121,27 +121,46 @@ unpack_wgrad_batched_kernel(const float* __restrict__ src_base, float* __restric
 // the fp32 OIHW master at src -> the forward bank [O][K*K][I] at dst_fwd and the data-gradient bank(s) at dst_bank
 // (same layouts as pack_conv_weight_kernel / pack_dgrad_weight_kernel). blockIdx.y = entry.
 struct PackEntry { long long src, dst_fwd, dst_bank; int O, I, K, stride; };
+// A block owns (entry, 32 output channels x 32 input channels): the 32 x (32*T) fp32 sub-matrix is read with coalesced
+// rows into shared memory and written out twice - forward bank rows (32 consecutive i) and data-gradient bank rows (32
+// consecutive o) - so both sides move 64..128-byte segments. blockIdx.y = entry, blockIdx.x strides over the tiles.
 __global__ void __launch_bounds__(256)
 pack_weights_batched_kernel(const float* __restrict__ src_base, uint16_t* __restrict__ dst_base,
                             const PackEntry* __restrict__ table, int dtype) {
+    __shared__ float tile[32][32 * 9 + 1];
     const PackEntry e = table[blockIdx.y];
     const float* w = src_base + e.src;
-    const int T = e.K * e.K;
-    const size_t n = (size_t)e.O * T * e.I;
+    const int T = e.K * e.K, K = e.K;
     uint16_t* fwd = dst_base + e.dst_fwd;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
-        const int i = idx % e.I, t = (idx / e.I) % T, o = idx / ((size_t)e.I * T);
-        fwd[idx] = f2h(w[((size_t)o * e.I + i) * T + t], dtype);
-    }
-    const int nbanks = (e.stride == 2 && e.K == 3) ? 4 : 1;
     uint16_t* bank = dst_base + e.dst_bank;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < n * nbanks; idx += (size_t)gridDim.x * blockDim.x) {
-        const int o = idx % e.O, t = (idx / e.O) % T, i = (idx / ((size_t)e.O * T)) % e.I, b = idx / n;
-        int r, s2;
-        if (e.stride == 1) { r = e.K - 1 - t / e.K; s2 = e.K - 1 - t % e.K; }
-        else if (e.K == 1) { r = 0; s2 = 0; }
-        else { r = dgrad_s2_src(b >> 1, t / 3); s2 = dgrad_s2_src(b & 1, t % 3); }
-        bank[idx] = f2h((r < 0 || s2 < 0) ? 0.f : w[(((size_t)o * e.I + i) * e.K + r) * e.K + s2], dtype);
+    const int tiles_o = (e.O + 31) / 32, tiles_i = (e.I + 31) / 32;
+    const int nbanks = (e.stride == 2 && K == 3) ? 4 : 1;
+    const size_t per_bank = (size_t)e.I * T * e.O;
+    for (int tl = blockIdx.x; tl < tiles_o * tiles_i; tl += gridDim.x) {
+        const int o0 = (tl / tiles_i) * 32, i0 = (tl % tiles_i) * 32;
+        const int ni = min(32, e.I - i0), no = min(32, e.O - o0);
+        const int rowlen = ni * T;
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < no * rowlen; idx += blockDim.x) {
+            const int oo = idx / rowlen, c = idx % rowlen;
+            tile[oo][c] = w[((size_t)(o0 + oo) * e.I + i0) * T + c];          // c = ii*T + t, contiguous in memory
+        }
+        __syncthreads();
+        // forward bank [O][T][I]
+        for (int idx = threadIdx.x; idx < no * T * ni; idx += blockDim.x) {
+            const int ii = idx % ni, t = (idx / ni) % T, oo = idx / (ni * T);
+            fwd[((size_t)(o0 + oo) * T + t) * e.I + i0 + ii] = f2h(tile[oo][ii * T + t], dtype);
+        }
+        // data-gradient bank(s) [b][I][T][O]
+        for (int idx = threadIdx.x; idx < nbanks * ni * T * no; idx += blockDim.x) {
+            const int oo = idx % no, t = (idx / no) % T, ii = (idx / (no * T)) % ni, bk = idx / (no * T * ni);
+            int r, s2;
+            if (e.stride == 1) { r = K - 1 - t / K; s2 = K - 1 - t % K; }
+            else if (K == 1) { r = 0; s2 = 0; }
+            else { r = dgrad_s2_src(bk >> 1, t / 3); s2 = dgrad_s2_src(bk & 1, t % 3); }
+            const float v = (r < 0 || s2 < 0) ? 0.f : tile[oo][ii * T + r * K + s2];
+            bank[bk * per_bank + ((size_t)(i0 + ii) * T + t) * e.O + o0 + oo] = f2h(v, dtype);
+        }
     }
 }
 
@@ -394,7 +413,7 @@ extern "C" int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_bas
         cudaFuncSetAttribute(unpack_wgrad_batched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         attr_set = true;
     }
-    dim3 grid(32, n_entries);
+    dim3 grid(128, n_entries);
     unpack_wgrad_batched_kernel<<<grid, 256, smem, (cudaStream_t)st>>>(packed_base, oihw_base, (const UnpackEntry*)table);
     VU_CHECK_LAUNCH("unpack_wgrad_batched");
     return 0;
@@ -403,7 +422,7 @@ extern "C" int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_bas
 extern "C" int vu_pack_weights_batched(const float* src_base, void* dst_base, const void* table, int n_entries, int dtype,
                                        vu_stream_t st) {
     if (!src_base || !dst_base || !table || n_entries < 1) return set_error(VU_ERR_INVALID, "pack_weights_batched: bad args");
-    dim3 grid(48, n_entries);
+    dim3 grid(416, n_entries);      // >= the tile count of the largest bank (800 x 512): one tile per block, empty blocks exit
     pack_weights_batched_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(src_base, (uint16_t*)dst_base, (const PackEntry*)table, dtype);
     VU_CHECK_LAUNCH("pack_weights_batched");
     return 0;

@@ -312,7 +312,10 @@ class TrainStep:
                 g1n = ops.broadcast_vec(g1v, ops.new_act(B, Hs, Ws, g1v.shape[1], dt, dev))
             else:
                 ops.bilinear_ac(x, Hs, Ws, out=xs)
-                r["g1raw"] = self._conv(xs, a + "W_g.0", bias=P[a + "W_g.0.bias"])
+                # W_g is a 1x1 conv + bias and bilinear weights sum to 1: W_g(up(x)) + b == up(W_g x + b), so the GEMM (and, by
+                # linearity, its weight / data gradients) runs at the LOW resolution of x: a quarter of the pixels
+                g1low = self._conv(x, a + "W_g.0", bias=P[a + "W_g.0.bias"])
+                r["g1raw"] = ops.bilinear_ac(g1low, Hs, Ws)
                 g1n, r["st_g"] = self._bn(r["g1raw"], a + "W_g.1.", False)
             r["x1raw"] = self._conv(skip, a + "W_x.0", bias=P[a + "W_x.0.bias"])
             r["s"], r["st_x"] = self._bn(r["x1raw"], a + "W_x.1.", True, residual=g1n)        # relu(g1 + x1)
@@ -401,11 +404,11 @@ class TrainStep:
                 self._vec_bwd(dg1v, r["g_saved"], a + "W_g.0.", a + "W_g.1.", False, dxv)
             else:
                 dg1raw, _ = self._bn_bwd(r["g1raw"], dg1n, None, r["st_g"], a + "W_g.1.")
-                xs = cat.slice(0, cx)
-                self._wgrad(xs, dg1raw, a + "W_g.0")
-                self._dgrad(dg1raw, a + "W_g.0", Hs, Ws, out=dxs, accumulate=True)
                 xin = r["x"]
+                dg1low = T.bilinear_ac_bwd(dg1raw, xin.H, xin.W)          # adjoint of the upsample, then W_g at low resolution
+                self._wgrad(xin, dg1low, a + "W_g.0")
                 dy = T.bilinear_ac_bwd(dxs, xin.H, xin.W)
+                self._dgrad(dg1low, a + "W_g.0", xin.H, xin.W, out=dy, accumulate=True)
             dfeat[3 - i] = dskip
         # z_initial, reparameterisation, heads
         self._vec_bwd(dxv, S["zi"], "z_initial.0.", "z_initial.1.", True, dz)
