@@ -67,8 +67,25 @@ typedef struct vu_conv_args {
      * y. Only for 3x3 s1 p1 convs with Cout in {64,128} on maps at least 96 wide (the smem tap-reuse kernel);
      * y may then be NULL (activation not materialised). NULL = off. */
     const float* fuse_w; float fuse_bias; float* fuse_out;
+    /* Optional position-dependent pre-scale bias, fp32 [N][9][Cout] (3x3 s1 p1 convs only): the exact contribution of
+     * input channels that are spatially CONSTANT per image (z_proj(z) in a DecoderBlock's concat, unet_resnet.py:93-98)
+     * and were therefore left out of x / w. Class = 3*rowclass + colclass of the output pixel (0 first row/col, 2 last,
+     * 1 interior): zero padding removes different taps on each border (vu_border_bias builds the table). NULL = off.
+     *   y = act(scale * (conv(x, w) + pos_bias[n][class(ho,wo)][co]) + bias + residual) */
+    const float* pos_bias;
 } vu_conv_args;
 int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
+
+/* pos_bias table for vu_conv_args: out[d][cls][co] = sum over the taps (r,s) that stay inside the image for border class
+ * cls, and over c < Cz, of w[co][coff + c][r][s] * z[d][c]. w: the conv's OIHW fp32 weight [Cout][Cin_total][3][3];
+ * z fp32 [D][Cz] (the constant channel values). */
+int vu_border_bias(const float* w_oihw, int Cout, int Cin_total, int coff, int Cz, const float* z, int D, float* out,
+                   vu_stream_t stream);
+
+/* The same table in two steps for fixed weights (inference): wsum fp32 [9][Cout][Cz] once, then one dot product per
+ * (image, class, output channel) per call (Cz % 4 == 0). */
+int vu_border_wsum(const float* w_oihw, int Cout, int Cin_total, int coff, int Cz, float* wsum, vu_stream_t stream);
+int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, vu_stream_t stream);
 
 /* Weight gradient of the same convolution (training step, train.py:397-399 loss.backward()):
  *   dw[co][r*KW+s][ci] += sum_{n,ho,wo} dy[n,ho,wo,dy_coff+co] * x[n, ho*stride+r-pad, wo*stride+s-pad, x_coff+ci]

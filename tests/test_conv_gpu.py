@@ -135,3 +135,32 @@ def test_conv_fused_output_rejected_off_path(cuda_dev):
     wp = ops.pack_conv_weight(torch.zeros(64, 64, 3, 3, device=dev), ops.F16)
     with pytest.raises(VaeUnetError):
         ops.conv2d(xa, wp, 3, 1, 1, None, None, True, fuse_w=torch.zeros(64, device=dev), fuse_out=torch.zeros(1, 8, 8, device=dev))
+
+
+@pytest.mark.parametrize("N,H,W,Cx,Cz,Cout", [(3, 20, 24, 192, 32, 64),      # implicit-GEMM kernel
+                                              (2, 9, 130, 192, 32, 64),       # tap-reuse kernel, ragged tile
+                                              (2, 32, 128, 320, 32, 128),     # tap-reuse kernel, Cout 128
+                                              (2, 16, 16, 768, 32, 512)])     # 256-column tiles
+def test_conv_pos_bias_constant_channels(cuda_dev, N, H, W, Cx, Cz, Cout):
+    """conv3x3 over [x | spatially constant z] == conv3x3 over x with the z term as a border-class bias (pos_bias)."""
+    from vaeunet_b200 import ops
+    g = torch.Generator().manual_seed(N * 1000 + W)
+    q = lambda t: t.half().float()
+    x = q(torch.randn(N, Cx, H, W, generator=g))
+    z = torch.randn(N, Cz, generator=g)
+    w = torch.randn(Cout, Cx + Cz, 3, 3, generator=g) / (9 * (Cx + Cz)) ** 0.5
+    w[:, :Cx] = q(w[:, :Cx])
+    scale = torch.rand(Cout, generator=g) + 0.5
+    bias = torch.randn(Cout, generator=g) * 0.1
+    full = torch.cat([x, z.view(N, Cz, 1, 1).expand(N, Cz, H, W)], 1)
+    ref = F.relu(F.conv2d(full, w, None, 1, 1) * scale.view(1, -1, 1, 1) + bias.view(1, -1, 1, 1))
+    d = cuda_dev
+    xa = ops.Act(x.permute(0, 2, 3, 1).contiguous().half().to(d))
+    wp = ops.pack_conv_weight(w[:, :Cx].contiguous().to(d), ops.F16)
+    pb = ops.border_bias(w.to(d), Cx, z.to(d))
+    pb2 = ops.border_bias_apply(ops.border_wsum(w.to(d), Cx, Cz), z.to(d))        # two-step form used by the engine
+    assert (pb - pb2).abs().max().item() < 1e-5
+    y = ops.conv2d(xa, wp, 3, 1, 1, scale.to(d), bias.to(d), True, pos_bias=pb)
+    got = y.t.float().cpu().permute(0, 3, 1, 2)
+    assert ((got - ref).norm() / ref.norm()).item() < 1e-3
+    assert (got - ref).abs().max().item() < 2e-3 * ref.abs().max().item() + 1e-3

@@ -30,6 +30,7 @@ class ConvArgs(C.Structure):
         ("out_up", C.c_int), ("out_dh", C.c_int), ("out_dw", C.c_int),
         ("dtype", C.c_int), ("max_ctas", C.c_int),
         ("fuse_w", C.c_void_p), ("fuse_bias", C.c_float), ("fuse_out", C.c_void_p),
+        ("pos_bias", C.c_void_p),
     ]
 
 
@@ -39,6 +40,9 @@ SIGNATURES = {
     "vu_version": [],
     "vu_device_check": [],
     "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
+    "vu_border_bias": [p, i, i, i, i, p, i, p, p],
+    "vu_border_wsum": [p, i, i, i, i, p, p],
+    "vu_border_bias_apply": [p, p, i, i, i, p, p],
     "vu_conv2d_wgrad": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_conv2d_wgrad_oihw": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_pack_weights_batched": [p, p, p, i, i, p],

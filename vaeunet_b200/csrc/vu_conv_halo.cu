@@ -35,6 +35,7 @@ struct HaloParams {
     uint16_t* y; int y_ctot, y_coff;
     int relu, dtype;
     const float* fuse_w; float fuse_bias; float* fuse_out;   // optional fused 1x1 Cout->1 output conv (fp32 [N,H,W])
+    const float* pos_bias;                                    // optional [N][9][BN] pre-scale bias by border class
 };
 
 template <int BN, int HT> struct HaloCfg {
@@ -228,7 +229,24 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                         for (int i = 0; i < 4; ++i) rv[i] = make_uint4(0, 0, 0, 0);
                     }
+                    float4 pb[8];
+                    if (p.pos_bias != nullptr) {
+                        const int hc = min(ho, p.h - 1), wc = min(wo, p.w - 1);
+                        const int cls = (hc == 0 ? 0 : (hc == p.h - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.w - 1 ? 2 : 1));
+                        const float4* pp = reinterpret_cast<const float4*>(p.pos_bias + (static_cast<size_t>(nb) * 9 + cls) * BN + ch0);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) pb[i] = __ldg(pp + i);
+                    }
                     tmem_ld_wait();
+                    if (p.pos_bias != nullptr) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) + pb[i].x);
+                            r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) + pb[i].y);
+                            r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) + pb[i].z);
+                            r[4 * i + 3] = __float_as_uint(__uint_as_float(r[4 * i + 3]) + pb[i].w);
+                        }
+                    }
                     const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
                     float v[32];
 #pragma unroll
@@ -326,6 +344,7 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     hp.y = static_cast<uint16_t*>(a->y); hp.y_ctot = a->y_ctot; hp.y_coff = a->y_coff;
     hp.relu = a->relu; hp.dtype = a->dtype;
     hp.fuse_w = a->fuse_w; hp.fuse_bias = a->fuse_bias; hp.fuse_out = a->fuse_out;
+    hp.pos_bias = a->pos_bias;
 
     CUtensorMap xm, wm;
     {

@@ -37,6 +37,7 @@ struct ConvKParams {
     uint16_t* y; int y_ctot, y_coff;
     int out_h, out_w, out_up, out_dh, out_dw;
     int relu, dtype;
+    const float* pos_bias;         // optional [n_img][9][cout] pre-scale bias by border class (3x3 s1 p1)
 };
 
 template <int BN> struct ConvCfg {
@@ -204,6 +205,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
                     for (int j = 0; j < 4; ++j) rv[j] = make_uint4(0, 0, 0, 0);
                 }
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+                if (p.pos_bias != nullptr) {
+                    const int hc = min(ho, p.ho - 1), wc = min(wo, p.wo - 1), nc = min(ni, p.n_img - 1);
+                    const int cls = (hc == 0 ? 0 : (hc == p.ho - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.wo - 1 ? 2 : 1));
+                    const float4* pp = reinterpret_cast<const float4*>(p.pos_bias + (static_cast<size_t>(nc) * 9 + cls) * p.cout + ch0);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 b = __ldg(pp + j);
+                        r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + b.x);
+                        r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + b.y);
+                        r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + b.z);
+                        r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     float v0 = __uint_as_float(r[2 * j]) * s_scale[ch0 + 2 * j] + s_bias[ch0 + 2 * j];
@@ -319,6 +333,9 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     kp.out_up = up; kp.out_dh = a->out_dh; kp.out_dw = a->out_dw;
     kp.out_h = Ho * up; kp.out_w = Wo * up;
     kp.relu = a->relu; kp.dtype = a->dtype;
+    kp.pos_bias = a->pos_bias;
+    if (a->pos_bias && !(KH == 3 && KW == 3 && S == 1 && P == 1 && up == 1 && a->H >= 2 && a->W >= 2))
+        return set_error(VU_ERR_UNSUPPORTED, "conv: pos_bias needs a 3x3 s1 p1 conv on a map of at least 2x2");
 
     // BN tile of 256/128/64/32 columns; the last N tile may be partial (filter rows beyond Cout are TMA zero fill, the
     // epilogue skips them). A k-iteration is L2->SM bound, so pick the width that moves the fewest operand rows:

@@ -157,6 +157,62 @@ final_conv1_kernel(const uint16_t* __restrict__ x, size_t npix, int x_ctot, int 
     }
 }
 
+// pos_bias table: out[d][cls][co] = sum_{(r,s) inside the image for class cls} sum_c w[co][coff+c][r][s] * z[d][c]
+// (row class 0 = first output row: tap row r = 0 falls in the zero padding; 2 = last row: r = 2 does; same for columns).
+__global__ void __launch_bounds__(256)
+border_bias_kernel(const float* __restrict__ w, int Cout, int Cin_total, int coff, int Cz, const float* __restrict__ z, int D,
+                   float* __restrict__ out) {
+    const size_t total = (size_t)D * 9 * Cout;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int co = idx % Cout, cls = (idx / Cout) % 9, d = idx / ((size_t)Cout * 9);
+        const int rc = cls / 3, cc = cls % 3;
+        const int r_lo = rc == 0 ? 1 : 0, r_hi = rc == 2 ? 1 : 2, s_lo = cc == 0 ? 1 : 0, s_hi = cc == 2 ? 1 : 2;
+        float acc = 0.f;
+        for (int c = 0; c < Cz; ++c) {
+            const float* wp = w + ((size_t)co * Cin_total + coff + c) * 9;
+            float t = 0.f;
+            for (int r = r_lo; r <= r_hi; ++r)
+                for (int q = s_lo; q <= s_hi; ++q) t += wp[r * 3 + q];
+            acc = fmaf(t, z[(size_t)d * Cz + c], acc);
+        }
+        out[idx] = acc;
+    }
+}
+
+// The same in two steps for weights that stay fixed (inference): wsum[cls][co][c] = sum of the in-image taps of
+// w[co][coff+c], built once; then out[d][cls][co] = <wsum[cls][co][:], z[d][:]> per call (Cz % 4 == 0, 16-byte rows).
+__global__ void __launch_bounds__(256)
+border_wsum_kernel(const float* __restrict__ w, int Cout, int Cin_total, int coff, int Cz, float* __restrict__ wsum) {
+    const size_t total = (size_t)9 * Cout * Cz;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int c = idx % Cz, co = (idx / Cz) % Cout, cls = idx / ((size_t)Cz * Cout);
+        const int rc = cls / 3, cc = cls % 3;
+        const int r_lo = rc == 0 ? 1 : 0, r_hi = rc == 2 ? 1 : 2, s_lo = cc == 0 ? 1 : 0, s_hi = cc == 2 ? 1 : 2;
+        const float* wp = w + ((size_t)co * Cin_total + coff + c) * 9;
+        float t = 0.f;
+        for (int r = r_lo; r <= r_hi; ++r)
+            for (int q = s_lo; q <= s_hi; ++q) t += wp[r * 3 + q];
+        wsum[idx] = t;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+border_bias_apply_kernel(const float* __restrict__ wsum, const float* __restrict__ z, int D, int Cout, int Cz,
+                         float* __restrict__ out) {
+    const size_t total = (size_t)D * 9 * Cout;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int co = idx % Cout, cls = (idx / Cout) % 9, d = idx / ((size_t)Cout * 9);
+        const float4* wp = reinterpret_cast<const float4*>(wsum + ((size_t)cls * Cout + co) * Cz);
+        const float4* zp = reinterpret_cast<const float4*>(z + (size_t)d * Cz);
+        float acc = 0.f;
+        for (int c = 0; c < Cz / 4; ++c) {
+            const float4 a = __ldg(wp + c), b = __ldg(zp + c);
+            acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
+        }
+        out[idx] = acc;
+    }
+}
+
 __global__ void reparameterize_kernel(const float* __restrict__ mu, const float* __restrict__ lv,
                                       const float* __restrict__ eps, float temperature, float* __restrict__ z,
                                       size_t n_per_sample, size_t total) {
@@ -240,6 +296,33 @@ extern "C" int vu_final_conv1(const void* x, int N, int H, int W, int C, int x_c
     else
         final_conv1_kernel<16><<<grid_cap((npix * 16 + 255) / 256), 256, 0, s>>>((const uint16_t*)x, npix, x_ctot, x_coff, w, bias, bias_dev, logits, c8, dtype);
     VU_CHECK_LAUNCH("final_conv1");
+    return 0;
+}
+
+extern "C" int vu_border_bias(const float* w_oihw, int Cout, int Cin_total, int coff, int Cz, const float* z, int D, float* out,
+                              vu_stream_t st) {
+    if (!w_oihw || !z || !out || Cout < 1 || Cz < 1 || D < 1 || coff < 0 || coff + Cz > Cin_total)
+        return set_error(VU_ERR_INVALID, "border_bias: bad args");
+    const size_t total = (size_t)D * 9 * Cout;
+    border_bias_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(w_oihw, Cout, Cin_total, coff, Cz, z, D, out);
+    VU_CHECK_LAUNCH("border_bias");
+    return 0;
+}
+
+extern "C" int vu_border_wsum(const float* w_oihw, int Cout, int Cin_total, int coff, int Cz, float* wsum, vu_stream_t st) {
+    if (!w_oihw || !wsum || Cout < 1 || Cz < 1 || coff < 0 || coff + Cz > Cin_total)
+        return set_error(VU_ERR_INVALID, "border_wsum: bad args");
+    const size_t total = (size_t)9 * Cout * Cz;
+    border_wsum_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(w_oihw, Cout, Cin_total, coff, Cz, wsum);
+    VU_CHECK_LAUNCH("border_wsum");
+    return 0;
+}
+
+extern "C" int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, vu_stream_t st) {
+    if (!wsum || !z || !out || D < 1 || Cout < 1 || Cz < 4 || Cz % 4) return set_error(VU_ERR_INVALID, "border_bias_apply: bad args (Cz % 4)");
+    const size_t total = (size_t)D * 9 * Cout;
+    border_bias_apply_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(wsum, z, D, Cout, Cz, out);
+    VU_CHECK_LAUNCH("border_bias_apply");
     return 0;
 }
 

@@ -59,8 +59,10 @@ def fold_bn(sd: Dict[str, torch.Tensor], bn: str, conv_bias: Optional[torch.Tens
 class ConvUnit:
     """conv (k x k, stride, pad) + folded BN (+ReLU, +residual) on the tcgen05 implicit-GEMM kernel."""
 
-    def __init__(self, sd, conv: str, bn: Optional[str], k: int, stride: int, pad: int, dev, dtype):
+    def __init__(self, sd, conv: str, bn: Optional[str], k: int, stride: int, pad: int, dev, dtype, cin_keep: Optional[int] = None):
         w = sd[conv + "weight"].detach().to(dev, torch.float32).contiguous()
+        if cin_keep is not None:                      # filter bank over the first cin_keep input channels only
+            w = w[:, :cin_keep].contiguous()
         cb = sd.get(conv + "bias")
         self.k, self.stride, self.pad = k, stride, pad
         self.cout, self.cin = w.shape[0], w.shape[1]
@@ -198,6 +200,17 @@ class DecoderBlockUnit:
         self.gate = GateUnit(sd, p + "attention.", dev, dtype) if (use_attention and use_skip) else None
         self.zproj = VecUnit(sd, p + "z_proj.0.", p + "z_proj.1.", dev) if use_latent else None
         self.zproj_conv = None
+        # Constant-latent fast path: z_proj(z) is spatially constant per decode, so its 3x3 conv contribution is a per-decode
+        # bias that only depends on the border class of the output pixel (zero padding). conv1 then runs over [x | skip_att]
+        # only (224 -> 192, 352 -> 320, 672 -> 640, 800 -> 768 channels: whole 64-channel K blocks) and the concat buffer
+        # loses its z slice; the z term is added in fp32 in the epilogue (ops.border_bias / conv2d(pos_bias=)).
+        self.conv1_xs = None
+        if use_latent:
+            self.w1_full = sd[p + "conv1.0.weight"].detach().to(dev, torch.float32).contiguous()
+            self.cin_xs = self.w1_full.shape[1] - latent_dim
+            if self.cin_xs % 8 == 0 and self.cin_xs > 0:
+                self.conv1_xs = ConvUnit(sd, p + "conv1.0.", p + "conv1.1.", 3, 1, 1, dev, dtype, cin_keep=self.cin_xs)
+                self.wsum_z = ops.border_wsum(self.w1_full, self.cin_xs, latent_dim)
 
     def __call__(self, x: Union[Act, ConstVec], skip: Optional[Act], z: Union[ConstVec, Act, None], psi_out=None,
                  final: Optional["FinalConvUnit"] = None):
@@ -215,8 +228,10 @@ class DecoderBlockUnit:
         has_skip = skip is not None and self.use_skip
         cs = skip.C if has_skip else 0
         cz = L if self.zproj is not None else 0
-        cat = ops.new_act(D, H, W, cx + cs + cz, self.dtype, self.dev)
-        if has_skip and self.gate is not None and psi_out is None and (cz == 0 or isinstance(z, ConstVec)):
+        fused = has_skip and self.gate is not None and psi_out is None and (cz == 0 or isinstance(z, ConstVec))
+        split_z = fused and cz > 0 and self.conv1_xs is not None and cx + cs == self.cin_xs and H >= 2 and W >= 2
+        cat = ops.new_act(D, H, W, cx + cs + (0 if split_z else cz), self.dtype, self.dev)
+        if fused:
             # fused producer: W_g runs at the LOW resolution of x, everything else is one pass over `cat`
             gt = self.gate
             if isinstance(x, ConstVec):
@@ -227,6 +242,9 @@ class DecoderBlockUnit:
                 g1_low = gt.wg(x, relu=False)
             x1 = gt.wx(skip, relu=False)
             zv = self.zproj(z.v, relu=True) if cz else None
+            if split_z:
+                ops.decoder_concat(x_low, g1_low, x1, skip, gt.psi_w, gt.psi_scale, gt.psi_bias, None, cat)
+                return self._convs(cat, final, pos_bias=ops.border_bias_apply(self.wsum_z, zv))
             ops.decoder_concat(x_low, g1_low, x1, skip, gt.psi_w, gt.psi_scale, gt.psi_bias, zv, cat)
             return self._convs(cat, final)
         xs = cat.slice(0, cx)
@@ -256,8 +274,8 @@ class DecoderBlockUnit:
                 self.zproj_conv(zu, relu=True, out=zs)
         return self._convs(cat, final)
 
-    def _convs(self, cat: Act, final):
-        y = self.conv1(cat, relu=True)
+    def _convs(self, cat: Act, final, pos_bias=None):
+        y = self.conv1(cat, relu=True) if pos_bias is None else self.conv1_xs(cat, relu=True, pos_bias=pos_bias)
         if final is not None and final.n_classes == 1 and self.conv2.can_fuse_output(y):
             logits = torch.empty((y.N, 1, y.H, y.W), dtype=torch.float32, device=self.dev)
             self.conv2(y, relu=True, fuse_w=final.w[0], fuse_bias=final.b[0], fuse_out=logits, store=False)

@@ -108,8 +108,9 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
            bias: Optional[torch.Tensor], relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None,
            out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0,
            fuse_w: Optional[torch.Tensor] = None, fuse_bias: float = 0.0, fuse_out: Optional[torch.Tensor] = None,
-           store: bool = True) -> Optional[Act]:
-    """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y."""
+           store: bool = True, pos_bias: Optional[torch.Tensor] = None) -> Optional[Act]:
+    """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y.
+    pos_bias: fp32 [N, 9, Cout] pre-scale bias by border class (`border_bias`): spatially constant input channels left out."""
     require_device()
     Cout = w_packed.shape[0]
     assert w_packed.shape[1] == k * k and w_packed.shape[2] == x.C, (tuple(w_packed.shape), k, x.C)
@@ -142,6 +143,11 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
         a.fuse_w = None; a.fuse_bias = 0.0; a.fuse_out = None
     a.out_up = out_up; a.out_dh = out_dh; a.out_dw = out_dw
     a.dtype = x.dt; a.max_ctas = max_ctas
+    if pos_bias is not None:
+        assert tuple(pos_bias.shape) == (x.N, 9, Cout), (tuple(pos_bias.shape), (x.N, 9, Cout))
+        a.pos_bias = _f32(pos_bias).data_ptr()
+    else:
+        a.pos_bias = None
     if CONV_TIMING is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -227,6 +233,47 @@ def conv2d_dgrad(dy: Act, banks, k: int, stride: int, H: int, W: int, out: Optio
     for ph in range(2):
         for pc in range(2):
             conv2d(dy, banks[ph * 2 + pc], 3, 1, 1, None, None, False, out=out, out_up=2, out_dh=ph, out_dw=pc)
+    return out
+
+
+def border_bias(w_oihw: torch.Tensor, coff: int, zvec: torch.Tensor) -> torch.Tensor:
+    """-> fp32 [D, 9, Cout]: exact 3x3 p1 conv contribution of the spatially constant channels [coff, coff+Cz) with per-image
+    values zvec [D, Cz], per border class of the output pixel (vu_border_bias); feeds conv2d(pos_bias=)."""
+    require_device()
+    w = _f32(w_oihw)
+    Cout, Cin_total, kh, kw = w.shape
+    assert kh == 3 and kw == 3
+    zvec = _f32(zvec.contiguous())
+    D, Cz = zvec.shape
+    out = torch.empty((D, 9, Cout), dtype=torch.float32, device=w.device)
+    check(load().vu_border_bias(w.data_ptr(), Cout, Cin_total, coff, Cz, zvec.data_ptr(), D, out.data_ptr(), _stream()),
+          "vu_border_bias")
+    _count()
+    return out
+
+
+def border_wsum(w_oihw: torch.Tensor, coff: int, Cz: int) -> torch.Tensor:
+    """-> fp32 [9, Cout, Cz]: per border class, the sum of the in-image taps of w[:, coff:coff+Cz] (built once per weight)."""
+    require_device()
+    w = _f32(w_oihw)
+    Cout, Cin_total = w.shape[:2]
+    out = torch.empty((9, Cout, Cz), dtype=torch.float32, device=w.device)
+    check(load().vu_border_wsum(w.data_ptr(), Cout, Cin_total, coff, Cz, out.data_ptr(), _stream()), "vu_border_wsum")
+    _count()
+    return out
+
+
+def border_bias_apply(wsum: torch.Tensor, zvec: torch.Tensor) -> torch.Tensor:
+    """wsum [9, Cout, Cz], zvec [D, Cz] -> pos_bias fp32 [D, 9, Cout]."""
+    require_device()
+    zvec = _f32(zvec.contiguous())
+    _, Cout, Cz = wsum.shape
+    D = zvec.shape[0]
+    assert zvec.shape[1] == Cz
+    out = torch.empty((D, 9, Cout), dtype=torch.float32, device=zvec.device)
+    check(load().vu_border_bias_apply(_f32(wsum).data_ptr(), zvec.data_ptr(), D, Cout, Cz, out.data_ptr(), _stream()),
+          "vu_border_bias_apply")
+    _count()
     return out
 
 
