@@ -256,6 +256,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layers", default=None, help="write a per-conv-shape timing table (csv) to this path")
     ap.add_argument("--dtype", default="f16", choices=["bf16", "f16"])
+    ap.add_argument("--graph", action="store_true", help="replay the MC step from a CUDA graph (engine.GraphedMC); measured: no gain, the step is GPU-bound")
     ap.add_argument("--workload", default="both", choices=["both", "mc", "train"],
                     help="mc: configs[1] only; train: configs[2] only (printed as the line's metric); both: MC line + 'train' object")
     args = ap.parse_args()
@@ -308,11 +309,18 @@ def main():
     eps_pool = [torch.randn(NS, B, 32, generator=g).to(dev) for _ in range(POOL)]
     out_host = {k: torch.empty((B, PATCH, PATCH), dtype=torch.float32).pin_memory() for k in ("mean", "std", "entropy")}
 
+    from vaeunet_b200.engine import GraphedMC
+    graphed = None if not args.graph else GraphedMC(eng, B, PATCH, PATCH, NS, TEMP)
+
     def step(i, e2e=False):
         j = i % POOL
-        x = host_pool[j].to(dev, non_blocking=True) if e2e else dev_pool[j]
-        with torch.no_grad():
-            res = eng.mc_predict(x, TEMP, NS, eps_pool[j])
+        if graphed is not None and ops.CONV_TIMING is None:
+            # e2e: the pinned host batch is copied straight into the graph's static input (H2D inside the timed region)
+            res = graphed(host_pool[j] if e2e else dev_pool[j], eps_pool[j])
+        else:
+            x = host_pool[j].to(dev, non_blocking=True) if e2e else dev_pool[j]
+            with torch.no_grad():
+                res = eng.mc_predict(x, TEMP, NS, eps_pool[j])
         if e2e:
             for k in out_host:
                 out_host[k].copy_(res[k], non_blocking=True)
@@ -406,7 +414,7 @@ def main():
                                "sample": f"median of {len(ts)} runs of ONE 512x512 patch, N=10 (oracle port of the reference, "
                                          f"fp32 PyTorch CPU, {threads} threads); run times {['%.2f' % t for t in ts]} s"}
     if args.workload == "both":
-        del eng, model, dev_pool, eps_pool
+        del graphed, eng, model, dev_pool, eps_pool
         torch.cuda.empty_cache()
         out["train"] = bench_train(args, dev, rank, world, dist)
     if rank == 0:

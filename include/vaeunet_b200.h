@@ -85,7 +85,8 @@ int vu_border_bias(const float* w_oihw, int Cout, int Cin_total, int coff, int C
 /* The same table in two steps for fixed weights (inference): wsum fp32 [9][Cout][Cz] once, then one dot product per
  * (image, class, output channel) per call (Cz % 4 == 0). */
 int vu_border_wsum(const float* w_oihw, int Cout, int Cin_total, int coff, int Cz, float* wsum, vu_stream_t stream);
-int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, vu_stream_t stream);
+int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, int accumulate /* out += */,
+                         vu_stream_t stream);
 
 /* Weight gradient of the same convolution (training step, train.py:397-399 loss.backward()):
  *   dw[co][r*KW+s][ci] += sum_{n,ho,wo} dy[n,ho,wo,dy_coff+co] * x[n, ho*stride+r-pad, wo*stride+s-pad, x_coff+ci]

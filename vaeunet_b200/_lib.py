@@ -42,7 +42,7 @@ SIGNATURES = {
     "vu_conv2d_fwd": [C.POINTER(ConvArgs), p],
     "vu_border_bias": [p, i, i, i, i, p, i, p, p],
     "vu_border_wsum": [p, i, i, i, i, p, p],
-    "vu_border_bias_apply": [p, p, i, i, i, p, p],
+    "vu_border_bias_apply": [p, p, i, i, i, p, i, p],
     "vu_conv2d_wgrad": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_conv2d_wgrad_oihw": [C.POINTER(ConvArgs), p, i, i, p, p],
     "vu_pack_weights_batched": [p, p, p, i, i, p],

@@ -213,6 +213,54 @@ border_bias_apply_kernel(const float* __restrict__ wsum, const float* __restrict
     }
 }
 
+// Tiled form for wide constant slices (block 0 of the decoder: the 512 channels of z_initial(z)): per border class a
+// [Cout x Cz] x [Cz x D] product, 64 x 32 outputs per block through shared memory, 4 x 2 per thread.
+__global__ void __launch_bounds__(256)
+border_bias_gemm_kernel(const float* __restrict__ wsum, const float* __restrict__ z, int D, int Cout, int Cz,
+                        float* __restrict__ out, int accumulate) {
+    __shared__ float As[64][33];
+    __shared__ float Zs[32][33];
+    const int cls = blockIdx.z, co0 = blockIdx.x * 64, d0 = blockIdx.y * 32;
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+    float acc[4][2] = {};
+    for (int c0 = 0; c0 < Cz; c0 += 32) {
+        for (int i = threadIdx.x; i < 64 * 32; i += 256) {
+            const int r = i / 32, c = i % 32;
+            As[r][c] = (co0 + r < Cout && c0 + c < Cz) ? wsum[((size_t)cls * Cout + co0 + r) * Cz + c0 + c] : 0.f;
+        }
+        for (int i = threadIdx.x; i < 32 * 32; i += 256) {
+            const int r = i / 32, c = i % 32;
+            Zs[r][c] = (d0 + r < D && c0 + c < Cz) ? z[(size_t)(d0 + r) * Cz + c0 + c] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) {
+            float a[4], b[2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[tx * 4 + i][k];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) b[j] = Zs[ty * 2 + j][k];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const int d = d0 + ty * 2 + j;
+        if (d >= D) continue;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int co = co0 + tx * 4 + i;
+            if (co >= Cout) continue;
+            float* o = out + ((size_t)d * 9 + cls) * Cout + co;
+            *o = accumulate ? *o + acc[i][j] : acc[i][j];
+        }
+    }
+}
+
 __global__ void reparameterize_kernel(const float* __restrict__ mu, const float* __restrict__ lv,
                                       const float* __restrict__ eps, float temperature, float* __restrict__ z,
                                       size_t n_per_sample, size_t total) {
@@ -318,10 +366,15 @@ extern "C" int vu_border_wsum(const float* w_oihw, int Cout, int Cin_total, int 
     return 0;
 }
 
-extern "C" int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, vu_stream_t st) {
+extern "C" int vu_border_bias_apply(const float* wsum, const float* z, int D, int Cout, int Cz, float* out, int accumulate,
+                                    vu_stream_t st) {
     if (!wsum || !z || !out || D < 1 || Cout < 1 || Cz < 4 || Cz % 4) return set_error(VU_ERR_INVALID, "border_bias_apply: bad args (Cz % 4)");
     const size_t total = (size_t)D * 9 * Cout;
-    border_bias_apply_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(wsum, z, D, Cout, Cz, out);
+    if (Cz >= 128 || accumulate) {
+        dim3 grid((Cout + 63) / 64, (D + 31) / 32, 9);
+        border_bias_gemm_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(wsum, z, D, Cout, Cz, out, accumulate);
+    } else
+        border_bias_apply_kernel<<<grid_cap((total + 255) / 256), 256, 0, (cudaStream_t)st>>>(wsum, z, D, Cout, Cz, out);
     VU_CHECK_LAUNCH("border_bias_apply");
     return 0;
 }

@@ -212,69 +212,81 @@ __global__ void nhwc_to_nchw_kernel(const uint16_t* __restrict__ x, float* __res
 }
 
 // ---------------------------------------------------------------- direct small-Cin convs
-// Generic direct conv for Cin <= 4 (stem 7x7 s2 p3; basic-UNet inc 3x3 s1 p1): a CTA computes a
-// 16x16 output tile for all Cout; input halo tile and the whole filter bank live in smem.
+// Generic direct conv for Cin <= 4 (stem 7x7 s2 p3; basic-UNet inc 3x3 s1 p1), fp32 weights and pixels. Persistent CTAs:
+// the whole filter bank is staged in shared memory ONCE per CTA (coalesced read, tap-major so a warp reads one row as a
+// broadcast), then the CTA walks over 16 x 32 output tiles; a thread owns two pixels of a row (16 columns apart) x 32 output
+// channels per pass, so every 16-byte weight read feeds 8 FMAs.
 template <int K, int S>
 __global__ void __launch_bounds__(256)
 small_cin_conv_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale,
-                      const float* __restrict__ bias, uint16_t* __restrict__ y, int Cin, int H, int W, int Cout,
+                      const float* __restrict__ bias, uint16_t* __restrict__ y, int N, int Cin, int H, int W, int Cout,
                       int Ho, int Wo, int pad, int y_ctot, int y_coff, int relu, int dtype) {
-    constexpr int TO = 16;
-    constexpr int TI = (TO - 1) * S + K;
+    constexpr int TOH = 16, TOW = 32;
+    constexpr int TIH = (TOH - 1) * S + K, TIW = (TOW - 1) * S + K;
     extern __shared__ float sm[];
-    float* s_in = sm;                         // [Cin][TI][TI+1]
-    float* s_w = sm + 4 * TI * (TI + 1);      // [Cin*K*K][Cout]  (tap-major so a warp reads one row)
-    const int n = blockIdx.z;
-    const int oh0 = blockIdx.y * TO, ow0 = blockIdx.x * TO;
+    float* s_in = sm;                              // [Cin][TIH][TIW+1]
+    float* s_w = sm + 4 * TIH * (TIW + 1);         // [Cin*K*K][Cout]
     const int tid = threadIdx.x;
-    const int ih0 = oh0 * S - pad, iw0 = ow0 * S - pad;
-    for (int i = tid; i < Cin * TI * TI; i += 256) {
-        const int c = i / (TI * TI), r = (i / TI) % TI, q = i % TI;
-        const int ih = ih0 + r, iw = iw0 + q;
-        float v = 0.0f;
-        if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = x[(((size_t)n * Cin + c) * H + ih) * W + iw];
-        s_in[(c * TI + r) * (TI + 1) + q] = v;
-    }
     const int KK = Cin * K * K;
-    for (int i = tid; i < KK * Cout; i += 256) {
-        const int co = i % Cout, t = i / Cout;   // t = (c*K + r)*K + s  == OIHW inner index
-        s_w[i] = w[(size_t)co * KK + t];
+    for (int i = tid; i < KK * Cout; i += 256) {   // i walks the OIHW tensor linearly (coalesced)
+        const int co = i / KK, t = i % KK;
+        s_w[t * Cout + co] = w[i];
     }
-    __syncthreads();
-    const int ty = tid / TO, tx = tid % TO;
-    const int oh = oh0 + ty, ow = ow0 + tx;
-    const bool valid = oh < Ho && ow < Wo;
-    for (int cb = 0; cb < Cout; cb += 32) {
-        float acc[32];
+    const int tiles_w = (Wo + TOW - 1) / TOW, tiles_h = (Ho + TOH - 1) / TOH;
+    const int total = tiles_w * tiles_h * N;
+    const int ty = tid / 16, tx = tid % 16;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n = tile / (tiles_w * tiles_h);
+        const int oh0 = ((tile / tiles_w) % tiles_h) * TOH, ow0 = (tile % tiles_w) * TOW;
+        const int ih0 = oh0 * S - pad, iw0 = ow0 * S - pad;
+        __syncthreads();
+        for (int i = tid; i < Cin * TIH * TIW; i += 256) {
+            const int c = i / (TIH * TIW), r = (i / TIW) % TIH, q = i % TIW;
+            const int ih = ih0 + r, iw = iw0 + q;
+            float v = 0.0f;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * Cin + c) * H + ih) * W + iw);
+            s_in[(c * TIH + r) * (TIW + 1) + q] = v;
+        }
+        __syncthreads();
+        const int oh = oh0 + ty;
+        for (int cb = 0; cb < Cout; cb += 32) {
+            float acc[2][32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) acc[j] = 0.0f;
-        for (int c = 0; c < Cin; ++c)
-            for (int r = 0; r < K; ++r)
+            for (int j = 0; j < 32; ++j) { acc[0][j] = 0.0f; acc[1][j] = 0.0f; }
+            for (int c = 0; c < Cin; ++c)
+                for (int r = 0; r < K; ++r) {
+                    const float* row = s_in + (c * TIH + ty * S + r) * (TIW + 1) + tx * S;
 #pragma unroll
-                for (int s = 0; s < K; ++s) {
-                    const float v = s_in[(c * TI + ty * S + r) * (TI + 1) + tx * S + s];
-                    const float4* wp = reinterpret_cast<const float4*>(s_w + ((c * K + r) * K + s) * Cout + cb);
+                    for (int q = 0; q < K; ++q) {
+                        const float v0 = row[q], v1 = row[q + 16 * S];
+                        const float4* wp = reinterpret_cast<const float4*>(s_w + ((c * K + r) * K + q) * Cout + cb);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 ww = wp[j];
-                        acc[4 * j] = fmaf(v, ww.x, acc[4 * j]);
-                        acc[4 * j + 1] = fmaf(v, ww.y, acc[4 * j + 1]);
-                        acc[4 * j + 2] = fmaf(v, ww.z, acc[4 * j + 2]);
-                        acc[4 * j + 3] = fmaf(v, ww.w, acc[4 * j + 3]);
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 ww = wp[j];
+                            acc[0][4 * j] = fmaf(v0, ww.x, acc[0][4 * j]);         acc[1][4 * j] = fmaf(v1, ww.x, acc[1][4 * j]);
+                            acc[0][4 * j + 1] = fmaf(v0, ww.y, acc[0][4 * j + 1]); acc[1][4 * j + 1] = fmaf(v1, ww.y, acc[1][4 * j + 1]);
+                            acc[0][4 * j + 2] = fmaf(v0, ww.z, acc[0][4 * j + 2]); acc[1][4 * j + 2] = fmaf(v1, ww.z, acc[1][4 * j + 2]);
+                            acc[0][4 * j + 3] = fmaf(v0, ww.w, acc[0][4 * j + 3]); acc[1][4 * j + 3] = fmaf(v1, ww.w, acc[1][4 * j + 3]);
+                        }
                     }
                 }
-        if (valid) {
-            uint32_t o[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float a = acc[2 * j] * scale[cb + 2 * j] + bias[cb + 2 * j];
-                float b = acc[2 * j + 1] * scale[cb + 2 * j + 1] + bias[cb + 2 * j + 1];
-                if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
-                o[j] = pack2h(a, b, dtype);
+            for (int h = 0; h < 2; ++h) {
+                const int ow = ow0 + tx + 16 * h;
+                if (oh < Ho && ow < Wo) {
+                    uint32_t o[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float a = acc[h][2 * j] * scale[cb + 2 * j] + bias[cb + 2 * j];
+                        float b = acc[h][2 * j + 1] * scale[cb + 2 * j + 1] + bias[cb + 2 * j + 1];
+                        if (relu) { a = fmaxf(a, 0.0f); b = fmaxf(b, 0.0f); }
+                        o[j] = pack2h(a, b, dtype);
+                    }
+                    uint4* op = reinterpret_cast<uint4*>(y + (((size_t)n * Ho + oh) * Wo + ow) * y_ctot + y_coff + cb);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) op[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                }
             }
-            uint4* op = reinterpret_cast<uint4*>(y + (((size_t)n * Ho + oh) * Wo + ow) * y_ctot + y_coff + cb);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) op[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
         }
     }
 }
@@ -283,20 +295,23 @@ template <int K, int S>
 static int launch_small_cin(const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
                             int Cin, int H, int W, int Cout, int pad, int y_ctot, int y_coff, int relu, int dtype,
                             cudaStream_t stream) {
-    constexpr int TI = 15 * S + K;
+    constexpr int TIH = 15 * S + K, TIW = 31 * S + K;
     if (Cin < 1 || Cin > 4) return set_error(VU_ERR_UNSUPPORTED, "small-cin conv: Cin must be 1..4 (got %d)", Cin);
     if (Cout % 32 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "small-cin conv: Cout %% 32, slices %% 8");
     if (!scale || !bias) return set_error(VU_ERR_INVALID, "small-cin conv: scale/bias required");
     const int Ho = (H + 2 * pad - K) / S + 1, Wo = (W + 2 * pad - K) / S + 1;
-    const size_t smem = (size_t)(4 * TI * (TI + 1) + Cin * K * K * Cout) * sizeof(float);
+    const size_t smem = (size_t)(4 * TIH * (TIW + 1) + Cin * K * K * Cout) * sizeof(float);
     static bool attr = false;
     if (!attr) {
         cudaFuncSetAttribute(small_cin_conv_kernel<K, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr = true;
     }
     if (smem > 200 * 1024) return set_error(VU_ERR_UNSUPPORTED, "small-cin conv: filter bank too large for smem");
-    dim3 grid((Wo + 15) / 16, (Ho + 15) / 16, N);
-    small_cin_conv_kernel<K, S><<<grid, 256, smem, stream>>>(x, w, scale, bias, static_cast<uint16_t*>(y), Cin, H, W,
+    const int total = ((Wo + 31) / 32) * ((Ho + 15) / 16) * N;
+    const int per_sm = (int)((220 * 1024) / (smem + 1024));
+    int grid = num_sms() * (per_sm < 1 ? 1 : (per_sm > 3 ? 3 : per_sm));
+    if (grid > total) grid = total;
+    small_cin_conv_kernel<K, S><<<grid, 256, smem, stream>>>(x, w, scale, bias, static_cast<uint16_t*>(y), N, Cin, H, W,
                                                            Cout, Ho, Wo, pad, y_ctot, y_coff, relu, dtype);
     VU_CHECK_LAUNCH("small_cin_conv");
     return 0;

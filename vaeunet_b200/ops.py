@@ -263,15 +263,18 @@ def border_wsum(w_oihw: torch.Tensor, coff: int, Cz: int) -> torch.Tensor:
     return out
 
 
-def border_bias_apply(wsum: torch.Tensor, zvec: torch.Tensor) -> torch.Tensor:
-    """wsum [9, Cout, Cz], zvec [D, Cz] -> pos_bias fp32 [D, 9, Cout]."""
+def border_bias_apply(wsum: torch.Tensor, zvec: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """wsum [9, Cout, Cz], zvec [D, Cz] -> pos_bias fp32 [D, 9, Cout] (added to `out` when given)."""
     require_device()
     zvec = _f32(zvec.contiguous())
     _, Cout, Cz = wsum.shape
     D = zvec.shape[0]
     assert zvec.shape[1] == Cz
-    out = torch.empty((D, 9, Cout), dtype=torch.float32, device=zvec.device)
-    check(load().vu_border_bias_apply(_f32(wsum).data_ptr(), zvec.data_ptr(), D, Cout, Cz, out.data_ptr(), _stream()),
+    acc = out is not None
+    if out is None:
+        out = torch.empty((D, 9, Cout), dtype=torch.float32, device=zvec.device)
+    assert tuple(out.shape) == (D, 9, Cout)
+    check(load().vu_border_bias_apply(_f32(wsum).data_ptr(), zvec.data_ptr(), D, Cout, Cz, _f32(out).data_ptr(), int(acc), _stream()),
           "vu_border_bias_apply")
     _count()
     return out
