@@ -310,7 +310,8 @@ def main():
     out_host = {k: torch.empty((B, PATCH, PATCH), dtype=torch.float32).pin_memory() for k in ("mean", "std", "entropy")}
 
     from vaeunet_b200.engine import GraphedMC
-    graphed = None if not args.graph else GraphedMC(eng, B, PATCH, PATCH, NS, TEMP)
+    OUTS = ("mean", "std", "entropy")          # configs[1]: mean / variance / entropy maps per patch
+    graphed = None if not args.graph else GraphedMC(eng, B, PATCH, PATCH, NS, TEMP, outs=OUTS)
 
     def step(i, e2e=False):
         j = i % POOL
@@ -320,7 +321,7 @@ def main():
         else:
             x = host_pool[j].to(dev, non_blocking=True) if e2e else dev_pool[j]
             with torch.no_grad():
-                res = eng.mc_predict(x, TEMP, NS, eps_pool[j])
+                res = eng.mc_predict(x, TEMP, NS, eps_pool[j], outs=OUTS)
         if e2e:
             for k in out_host:
                 out_host[k].copy_(res[k], non_blocking=True)

@@ -63,6 +63,7 @@ uncertainty_reduce_kernel(const float* __restrict__ in, int B, int Ns, int Hs, i
         Lerp ly, lx;
         if (!is_prob) { ly = make_lerp(sh, ho, Hs); lx = make_lerp(sw, wo, Ws); }
         float mean = 0.0f, m2 = 0.0f, sum_h = 0.0f;
+        const bool need_h = mi_o != nullptr;       // per-sample entropies only feed the mutual information
         for (int n = 0; n < Ns; ++n) {
             float p;
             if (is_prob) {
@@ -74,9 +75,9 @@ uncertainty_reduce_kernel(const float* __restrict__ in, int B, int Ns, int Hs, i
                 if (probs_o) probs_o[((b * Ns + n) * Ho + ho) * Wo + wo] = p;
             }
             const float d = p - mean;             // Welford
-            mean += d / (float)(n + 1);
+            mean += d * __frcp_rn((float)(n + 1));
             m2 += d * (p - mean);
-            sum_h += bin_entropy(p);
+            if (need_h) sum_h += bin_entropy(p);
         }
         const float var = (Ns > 1) ? m2 / (float)(Ns - 1) : __int_as_float(0x7fc00000);  // torch.std: NaN for N=1
         const float sd = sqrtf(fmaxf(var, 0.0f));
@@ -94,12 +95,13 @@ __global__ void moments_partial_kernel(const float* __restrict__ probs, int Ns, 
                                        float* __restrict__ m2_o, float* __restrict__ sh_o) {
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < npix; idx += (size_t)gridDim.x * blockDim.x) {
         float mean = 0.0f, m2 = 0.0f, sum_h = 0.0f;
+        const bool need_h = mi_o != nullptr;       // per-sample entropies only feed the mutual information
         for (int n = 0; n < Ns; ++n) {
             const float p = __ldg(probs + (size_t)n * npix + idx);
             const float d = p - mean;
-            mean += d / (float)(n + 1);
+            mean += d * __frcp_rn((float)(n + 1));
             m2 += d * (p - mean);
-            sum_h += bin_entropy(p);
+            if (need_h) sum_h += bin_entropy(p);
         }
         mean_o[idx] = mean; m2_o[idx] = m2; sh_o[idx] = sum_h;
     }

@@ -277,6 +277,8 @@ class UNetResNet(KernelModule):
         return lg
 
     # additive fast path
-    def mc_predict(self, images, temperature=1.0, num_samples=10, eps=None, return_samples=False):
+    def mc_predict(self, images, temperature=1.0, num_samples=10, eps=None, return_samples=False,
+                   outs=("mean", "std", "entropy", "mutual_info", "coeff_var")):
+        """`outs`: which maps of calculate_uncertainty_metrics (visualize_vae.py:90-117) to produce."""
         self._require_eval()
-        return self.engine().mc_predict(images.float().contiguous(), temperature, num_samples, eps, return_samples)
+        return self.engine().mc_predict(images.float().contiguous(), temperature, num_samples, eps, return_samples, outs)
