@@ -134,17 +134,20 @@ def bench_train(args, dev, rank, world, dist):
     devp = [(a.to(dev), b.to(dev)) for a, b in host]
     g = torch.Generator().manual_seed(7 + rank)
     eps = [torch.randn(B, 32, generator=g).to(dev) for _ in range(POOL)]
-    loss_host = torch.zeros(1).pin_memory()
+    from vaeunet_b200.pipeline import StagedInput, StagedOutput
+    inp, outp = StagedInput(dev, 2), StagedOutput(dev, 2)
 
     def step(i, e2e=False):
         j = i % POOL
-        if e2e:
-            x, m = host[j][0].to(dev, non_blocking=True), host[j][1].to(dev, non_blocking=True)
+        if e2e:      # images + masks from pinned host memory (next batch prefetched during this step), loss read back to the host
+            x, m = inp.push(*host[j])
+            inp.prefetch(*host[(i + 1) % POOL])
         else:
             x, m = devp[j]
         out = ts.step(x, m, 0.001, eps[j])
         if e2e:
-            loss_host.copy_(out["loss"].reshape(1), non_blocking=True)
+            inp.release()
+            outp.push({"loss": out["loss"].reshape(1)})
         return out
 
     def barrier():
@@ -161,8 +164,13 @@ def bench_train(args, dev, rank, world, dist):
         e0.record()
         for i in range(args.steps):
             step(args.warmup + i, e2e)
+        if e2e:
+            inp._pending = None
+            torch.cuda.current_stream().wait_stream(outp.stream)
         e1.record()
         barrier()
+        if e2e:
+            outp.flush()
         ms = e0.elapsed_time(e1)
         if dist is not None:
             t = torch.tensor([ms], device=dev)
@@ -307,24 +315,31 @@ def main():
     dev_pool = [h.to(dev) for h in host_pool]
     g = torch.Generator().manual_seed(99 + rank)
     eps_pool = [torch.randn(NS, B, 32, generator=g).to(dev) for _ in range(POOL)]
-    out_host = {k: torch.empty((B, PATCH, PATCH), dtype=torch.float32).pin_memory() for k in ("mean", "std", "entropy")}
 
     from vaeunet_b200.engine import GraphedMC
     OUTS = ("mean", "std", "entropy")          # configs[1]: mean / variance / entropy maps per patch
     graphed = None if not args.graph else GraphedMC(eng, B, PATCH, PATCH, NS, TEMP, outs=OUTS)
 
+    from vaeunet_b200.pipeline import StagedInput, StagedOutput
+    inp, outp = StagedInput(dev, 2), StagedOutput(dev, 2)
+
     def step(i, e2e=False):
         j = i % POOL
-        if graphed is not None and ops.CONV_TIMING is None:
-            # e2e: the pinned host batch is copied straight into the graph's static input (H2D inside the timed region)
-            res = graphed(host_pool[j] if e2e else dev_pool[j], eps_pool[j])
+        if e2e:
+            # public streaming path: pinned host batch -> device on the copy-in stream (the next batch is prefetched while this
+            # one computes), three maps -> pinned host buffers on the copy-out stream; all of it inside the timed region
+            x, = inp.push(host_pool[j])
+            inp.prefetch(host_pool[(i + 1) % POOL])
         else:
-            x = host_pool[j].to(dev, non_blocking=True) if e2e else dev_pool[j]
+            x = dev_pool[j]
+        if graphed is not None and ops.CONV_TIMING is None:
+            res = graphed(x, eps_pool[j])
+        else:
             with torch.no_grad():
                 res = eng.mc_predict(x, TEMP, NS, eps_pool[j], outs=OUTS)
         if e2e:
-            for k in out_host:
-                out_host[k].copy_(res[k], non_blocking=True)
+            inp.release()
+            outp.push({k: res[k] for k in OUTS})
         return res
 
     def barrier():
@@ -341,8 +356,13 @@ def main():
         e0.record()
         for i in range(args.steps):
             step(args.warmup + i, e2e)
+        if e2e:
+            inp._pending = None                                       # drop the prefetch issued by the last step
+            torch.cuda.current_stream().wait_stream(outp.stream)      # the last device->host copies are inside the timed region
         e1.record()
         barrier()
+        if e2e:
+            outp.flush()
         ms = e0.elapsed_time(e1)
         if dist is not None:
             t = torch.tensor([ms], device=dev)

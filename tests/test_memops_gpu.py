@@ -324,3 +324,24 @@ def test_ece_and_confusion(cuda_dev):
     pb = p > 0.5
     tb = gt > 0.5
     assert c.tolist() == [float((pb & tb).sum()), float((pb & ~tb).sum()), float((~pb & ~tb).sum()), float((~pb & tb).sum())]
+
+
+def test_staged_host_pipeline(cuda_dev):
+    """pipeline.StagedInput / StagedOutput: double-buffered copies on side streams deliver the right data in order."""
+    from vaeunet_b200.pipeline import StagedInput, StagedOutput
+    inp, outp = StagedInput(cuda_dev, 2), StagedOutput(cuda_dev, 2)
+    host = [torch.full((4, 3, 64, 64), float(i)).pin_memory() for i in range(7)]
+    got = []
+    for i, h in enumerate(host):
+        x, = inp.push(h)
+        if i + 1 < len(host):
+            inp.prefetch(host[i + 1])
+        y = x * 2 + 1                                   # stand-in for the device step (current stream)
+        for _ in range(20):
+            y = y + 0
+        inp.release()
+        outp.push({"y": y}, on_ready=lambda d: got.append(d["y"].clone()))
+    outp.flush()
+    assert len(got) == len(host)
+    for i, g in enumerate(got):
+        assert torch.equal(g, torch.full((4, 3, 64, 64), 2.0 * i + 1)), i
