@@ -73,6 +73,10 @@ typedef struct vu_conv_args {
      * 1 interior): zero padding removes different taps on each border (vu_border_bias builds the table). NULL = off.
      *   y = act(scale * (conv(x, w) + pos_bias[n][class(ho,wo)][co]) + bias + residual) */
     const float* pos_bias;
+    /* Optional per-channel statistics of the STORED output (after rounding to 16 bit): stat_sums[co] += sum y,
+     * stat_sums[Cout + co] += sum y^2 over all output pixels, fp64, accumulated (zero it first). The training step feeds them
+     * to vu_bn_finalize, so train-mode BatchNorm needs no separate statistics pass over the conv output. NULL = off. */
+    double* stat_sums;
 } vu_conv_args;
 int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 

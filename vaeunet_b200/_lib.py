@@ -31,6 +31,7 @@ class ConvArgs(C.Structure):
         ("dtype", C.c_int), ("max_ctas", C.c_int),
         ("fuse_w", C.c_void_p), ("fuse_bias", C.c_float), ("fuse_out", C.c_void_p),
         ("pos_bias", C.c_void_p),
+        ("stat_sums", C.c_void_p),
     ]
 
 

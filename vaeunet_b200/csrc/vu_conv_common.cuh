@@ -29,6 +29,23 @@ __device__ __forceinline__ float2 unpack2(uint32_t u, int dtype) {
     }
 }
 
+// Column sums of a 32 x 32 tile held one row per lane (a[i] = this lane's value for column i): a butterfly that halves the
+// number of live columns per lane at every step (16+8+4+2+1 = 31 shuffles). Returns, in lane l, the sum over the 32 lanes
+// of column l. Used by the conv epilogues to accumulate per-channel BatchNorm statistics of the tile they just produced.
+__device__ __forceinline__ float warp_column_sums32(float (&a)[32], int lane) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const bool hi = (lane & o) != 0;
+#pragma unroll
+        for (int i = 0; i < o; ++i) {
+            const float send = hi ? a[i] : a[i + o];
+            const float keep = hi ? a[i + o] : a[i];
+            a[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return a[0];
+}
+
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                     CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,

@@ -36,6 +36,7 @@ struct HaloParams {
     int relu, dtype;
     const float* fuse_w; float fuse_bias; float* fuse_out;   // optional fused 1x1 Cout->1 output conv (fp32 [N,H,W])
     const float* pos_bias;                                    // optional [N][9][BN] pre-scale bias by border class
+    double* stat_sums;                                        // optional [2*BN] fp64 sum / sum of squares of the stored outputs
 };
 
 template <int BN, int HT> struct HaloCfg {
@@ -47,7 +48,7 @@ template <int BN, int HT> struct HaloCfg {
     static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4;
+    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 5 * BN * 4;
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 232448, "smem budget");
 };
@@ -77,6 +78,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
     float* s_bias = s_scale + BN;
     float* s_fw = s_bias + BN;
+    float* s_sum = s_fw + BN;          // per-CTA partial BatchNorm statistics of the stored outputs
+    float* s_sq = s_sum + BN;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -97,6 +100,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
         s_fw[c] = p.fuse_w ? p.fuse_w[c] : 0.0f;
+        s_sum[c] = 0.0f; s_sq[c] = 0.0f;
     }
     tc_fence_before();
     __syncthreads();
@@ -280,6 +284,18 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         for (int i = 0; i < 4; ++i)
                             op[i] = make_uint4(outw[4 * i], outw[4 * i + 1], outw[4 * i + 2], outw[4 * i + 3]);
                     }
+                    if (p.stat_sums != nullptr) {      // statistics of the values as stored (rounded to 16 bit)
+                        float a[32], b[32];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const float2 f = unpack2(pack2(v[2 * i], v[2 * i + 1], dtype), dtype);
+                            a[2 * i] = valid ? f.x : 0.0f; a[2 * i + 1] = valid ? f.y : 0.0f;
+                            b[2 * i] = a[2 * i] * a[2 * i]; b[2 * i + 1] = a[2 * i + 1] * a[2 * i + 1];
+                        }
+                        const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
+                        atomicAdd(&s_sum[ch0 + lane], cs);
+                        atomicAdd(&s_sq[ch0 + lane], cq);
+                    }
                 }
                 if (fuse && valid) p.fuse_out[pix] = dot + p.fuse_bias;
             }
@@ -290,6 +306,15 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     tc_fence_before();
     __syncthreads();
+    if (p.stat_sums != nullptr) {
+        for (int c = threadIdx.x; c < BN; c += blockDim.x) {
+            const float a = s_sum[c], b = s_sq[c];
+            if (a != 0.0f || b != 0.0f) {
+                atomicAdd(&p.stat_sums[c], static_cast<double>(a));
+                atomicAdd(&p.stat_sums[BN + c], static_cast<double>(b));
+            }
+        }
+    }
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<Cfg::kTmemCols>(tmem_base);
@@ -345,6 +370,7 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     hp.relu = a->relu; hp.dtype = a->dtype;
     hp.fuse_w = a->fuse_w; hp.fuse_bias = a->fuse_bias; hp.fuse_out = a->fuse_out;
     hp.pos_bias = a->pos_bias;
+    hp.stat_sums = a->stat_sums;
 
     CUtensorMap xm, wm;
     {

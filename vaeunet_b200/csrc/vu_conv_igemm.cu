@@ -38,6 +38,7 @@ struct ConvKParams {
     int out_h, out_w, out_up, out_dh, out_dw;
     int relu, dtype;
     const float* pos_bias;         // optional [n_img][9][cout] pre-scale bias by border class (3x3 s1 p1)
+    double* stat_sums;             // optional [2*cout] fp64: sum / sum of squares of the stored outputs
 };
 
 template <int BN> struct ConvCfg {
@@ -47,7 +48,7 @@ template <int BN> struct ConvCfg {
     static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
     static constexpr int kBarBytes = 1024;  // barriers + tmem ptr
     static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes +
-                                      2 * kMaxCout * 4;
+                                      4 * kMaxCout * 4;   // scale, bias, per-CTA statistic partials
 };
 
 template <int BN>
@@ -70,6 +71,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
     float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
     float* s_bias = s_scale + kMaxCout;
+    float* s_sum = s_bias + kMaxCout;      // per-CTA partial sums of the stored outputs (BatchNorm statistics)
+    float* s_sq = s_sum + kMaxCout;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -88,6 +91,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     for (int c = threadIdx.x; c < p.cout; c += kThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
+        s_sum[c] = 0.0f; s_sq[c] = 0.0f;
     }
     tc_fence_before();
     __syncthreads();
@@ -235,6 +239,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
                     for (int j = 0; j < 4; ++j)
                         op[j] = make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
                 }
+                if (p.stat_sums != nullptr) {          // statistics of the values as stored (16-bit rounded); warp-uniform branch
+                    float a[32], b[32];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float2 f = unpack2(outw[j], p.dtype);
+                        a[2 * j] = valid ? f.x : 0.0f; a[2 * j + 1] = valid ? f.y : 0.0f;
+                        b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
+                    }
+                    const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
+                    atomicAdd(&s_sum[ch0 + lane], cs);
+                    atomicAdd(&s_sq[ch0 + lane], cq);
+                }
             }
             tc_fence_before();
             mbar_arrive(tempty_bar(acc));
@@ -243,6 +259,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
 
     tc_fence_before();
     __syncthreads();
+    if (p.stat_sums != nullptr && blockIdx.x < total_tiles)       // one fp64 flush of this CTA's partials
+        for (int c = threadIdx.x; c < p.cout; c += kThreads) {
+            atomicAdd(&p.stat_sums[c], (double)s_sum[c]);
+            atomicAdd(&p.stat_sums[p.cout + c], (double)s_sq[c]);
+        }
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<Cfg::kTmemCols>(tmem_base);
@@ -334,6 +355,8 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     kp.out_h = Ho * up; kp.out_w = Wo * up;
     kp.relu = a->relu; kp.dtype = a->dtype;
     kp.pos_bias = a->pos_bias;
+    kp.stat_sums = a->stat_sums;
+    if (a->stat_sums && up != 1) return set_error(VU_ERR_UNSUPPORTED, "conv: stat_sums with the pixel-shuffle store");
     if (a->pos_bias && !(KH == 3 && KW == 3 && S == 1 && P == 1 && up == 1 && a->H >= 2 && a->W >= 2))
         return set_error(VU_ERR_UNSUPPORTED, "conv: pos_bias needs a 3x3 s1 p1 conv on a map of at least 2x2");
 

@@ -95,13 +95,12 @@ __global__ void moments_partial_kernel(const float* __restrict__ probs, int Ns, 
                                        float* __restrict__ m2_o, float* __restrict__ sh_o) {
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < npix; idx += (size_t)gridDim.x * blockDim.x) {
         float mean = 0.0f, m2 = 0.0f, sum_h = 0.0f;
-        const bool need_h = mi_o != nullptr;       // per-sample entropies only feed the mutual information
         for (int n = 0; n < Ns; ++n) {
             const float p = __ldg(probs + (size_t)n * npix + idx);
             const float d = p - mean;
             mean += d * __frcp_rn((float)(n + 1));
             m2 += d * (p - mean);
-            if (need_h) sum_h += bin_entropy(p);
+            sum_h += bin_entropy(p);
         }
         mean_o[idx] = mean; m2_o[idx] = m2; sh_o[idx] = sum_h;
     }
