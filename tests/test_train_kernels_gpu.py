@@ -62,6 +62,32 @@ def test_conv_wgrad_row_kernel(cuda_dev, monkeypatch):
         assert ((got - wr.grad).norm() / wr.grad.norm()).item() < 2e-4, name
 
 
+def test_conv_epilogue_bn_statistics(cuda_dev):
+    """conv2d(stat_sums=): the per-channel sum / sum of squares accumulated in the conv epilogue equal the statistics
+    of the STORED (16-bit) output, on the tap-reuse kernel, the implicit GEMM (3x3 s1/s2, 1x1, bias, ragged pixel and
+    channel tiles) alike. Checked against fp64 sums of the output read back."""
+    from vaeunet_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    for name, N, H, W, Cin, Cout, k, stride, bias in [("halo64", 2, 64, 64, 64, 64, 3, 1, False), ("halo32", 1, 96, 160, 96, 32, 3, 1, False),
+                                                      ("ig128", 2, 32, 32, 64, 128, 3, 1, False), ("ig_s2", 2, 33, 31, 64, 128, 3, 2, False),
+                                                      ("ig_1x1_bias", 3, 20, 28, 128, 64, 1, 1, True), ("ig_320", 1, 16, 16, 64, 320, 3, 1, False),
+                                                      ("ig_512", 4, 8, 8, 256, 512, 3, 1, False)]:
+        for dt, tdt in ((ops.BF16, torch.bfloat16), (ops.F16, torch.float16)):
+            x = torch.randn(N, H, W, Cin, generator=g).to(tdt).to(cuda_dev)
+            w = (torch.randn(Cout, Cin, k, k, generator=g) / (Cin * k * k) ** 0.5).to(cuda_dev)
+            b = torch.randn(Cout, generator=g).to(cuda_dev) if bias else None
+            wp = ops.pack_conv_weight(w, dt)
+            sums = torch.zeros(2 * Cout, dtype=torch.float64, device=cuda_dev)
+            y = ops.conv2d(ops.Act(x), wp, k, stride, k // 2, None, b, False, stat_sums=sums)
+            y0 = ops.conv2d(ops.Act(x), wp, k, stride, k // 2, None, b, False)
+            assert torch.equal(y.t, y0.t), name                       # the statistics do not disturb the output
+            yd = y.t.double().reshape(-1, Cout)
+            ref = torch.cat([yd.sum(0), (yd * yd).sum(0)])
+            scale = torch.cat([yd.abs().sum(0), (yd * yd).sum(0)]) + 1e-9
+            err = ((sums - ref).abs() / scale).max().item()
+            assert err < 2e-6, f"{name} {tdt}: {err}"                  # fp32 partials per CTA, fp64 across CTAs
+
+
 @pytest.mark.parametrize("case", [c for c in CASES if c[2] % 2 == 0 or c[7] == 1], ids=lambda c: c[0].replace("wg", "dg"))
 def test_conv_dgrad(case, cuda_dev):
     from vaeunet_b200 import ops

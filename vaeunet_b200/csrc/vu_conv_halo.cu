@@ -48,7 +48,7 @@ template <int BN, int HT> struct HaloCfg {
     static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 5 * BN * 4;
+    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4 + 2 * BN * 8;
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 232448, "smem budget");
 };
@@ -78,8 +78,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
     float* s_bias = s_scale + BN;
     float* s_fw = s_bias + BN;
-    float* s_sum = s_fw + BN;          // per-CTA partial BatchNorm statistics of the stored outputs
-    float* s_sq = s_sum + BN;
+    double* s_sum = reinterpret_cast<double*>(s_fw + BN);   // per-CTA partial BatchNorm statistics of the stored outputs
+    double* s_sq = s_sum + BN;                              // (fp64: see vu_conv_igemm.cu)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -100,7 +100,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
         s_fw[c] = p.fuse_w ? p.fuse_w[c] : 0.0f;
-        s_sum[c] = 0.0f; s_sq[c] = 0.0f;
+        s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
     tc_fence_before();
     __syncthreads();
@@ -293,8 +293,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             b[2 * i] = a[2 * i] * a[2 * i]; b[2 * i + 1] = a[2 * i + 1] * a[2 * i + 1];
                         }
                         const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
-                        atomicAdd(&s_sum[ch0 + lane], cs);
-                        atomicAdd(&s_sq[ch0 + lane], cq);
+                        atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
+                        atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
                     }
                 }
                 if (fuse && valid) p.fuse_out[pix] = dot + p.fuse_bias;
@@ -308,10 +308,10 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     __syncthreads();
     if (p.stat_sums != nullptr) {
         for (int c = threadIdx.x; c < BN; c += blockDim.x) {
-            const float a = s_sum[c], b = s_sq[c];
-            if (a != 0.0f || b != 0.0f) {
-                atomicAdd(&p.stat_sums[c], static_cast<double>(a));
-                atomicAdd(&p.stat_sums[BN + c], static_cast<double>(b));
+            const double a = s_sum[c], b = s_sq[c];
+            if (a != 0.0 || b != 0.0) {
+                atomicAdd(&p.stat_sums[c], a);
+                atomicAdd(&p.stat_sums[BN + c], b);
             }
         }
     }

@@ -48,7 +48,7 @@ template <int BN> struct ConvCfg {
     static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
     static constexpr int kBarBytes = 1024;  // barriers + tmem ptr
     static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes +
-                                      4 * kMaxCout * 4;   // scale, bias, per-CTA statistic partials
+                                      2 * kMaxCout * 4 + 2 * kMaxCout * 8;   // scale, bias; per-CTA fp64 statistic partials
 };
 
 template <int BN>
@@ -71,8 +71,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
     float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
     float* s_bias = s_scale + kMaxCout;
-    float* s_sum = s_bias + kMaxCout;      // per-CTA partial sums of the stored outputs (BatchNorm statistics)
-    float* s_sq = s_sum + kMaxCout;
+    // per-CTA partial sums of the stored outputs (BatchNorm statistics). fp64: the warp-level column sums are computed in
+    // a fixed order, so everything whose order depends on scheduling is accumulated in double and the result is
+    // reproducible to ~1e-16 (a train-mode BatchNorm over a handful of values amplifies fp32-level noise)
+    double* s_sum = reinterpret_cast<double*>(s_bias + kMaxCout);
+    double* s_sq = s_sum + kMaxCout;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -91,7 +94,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     for (int c = threadIdx.x; c < p.cout; c += kThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
-        s_sum[c] = 0.0f; s_sq[c] = 0.0f;
+        s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
     tc_fence_before();
     __syncthreads();
@@ -248,8 +251,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
                         b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
                     }
                     const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
-                    atomicAdd(&s_sum[ch0 + lane], cs);
-                    atomicAdd(&s_sq[ch0 + lane], cq);
+                    atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
+                    atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
                 }
             }
             tc_fence_before();
@@ -261,8 +264,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     __syncthreads();
     if (p.stat_sums != nullptr && blockIdx.x < total_tiles)       // one fp64 flush of this CTA's partials
         for (int c = threadIdx.x; c < p.cout; c += kThreads) {
-            atomicAdd(&p.stat_sums[c], (double)s_sum[c]);
-            atomicAdd(&p.stat_sums[p.cout + c], (double)s_sq[c]);
+            atomicAdd(&p.stat_sums[c], s_sum[c]);
+            atomicAdd(&p.stat_sums[p.cout + c], s_sq[c]);
         }
     if (warp == 1) {
         tc_fence_after();

@@ -122,17 +122,14 @@ vec_layer_fwd_kernel(const float* __restrict__ z, const float* __restrict__ w, c
     }
 }
 
-// dy -> (ReLU mask from y) -> BN backward over the M rows -> dy_raw; dw[c,l] += sum_m dy_raw z, db[c] += sum_m dy_raw,
-// dgamma / dbeta += (parameter gradients accumulate); dz[m,l] += sum_c dy_raw[m,c] w[c,l] (atomics across the channel blocks).
-__global__ void __launch_bounds__(256)
-vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ w,
-                     const float* __restrict__ y_raw, const float* __restrict__ y, int M, int L, int C,
-                     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ invstd,
-                     int relu, float* __restrict__ dz, float* __restrict__ dw, float* __restrict__ db,
-                     float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    __shared__ float s_d[kVecM][33];
-    const int c0 = blockIdx.x * 32;
-    for (int i = threadIdx.x; i < M * 32; i += 256) {
+// dy -> (ReLU mask from y) -> BN backward over the M rows -> dy_raw tile s_d[m][0..31] of channels c0..c0+31 (all threads of
+// the block take part; ends with a __syncthreads). When `grads` is set, thread cl < 32 also accumulates dgamma / dbeta / db.
+__device__ __forceinline__ void vec_dy_raw_tile(float (*s_d)[33], int c0, const float* __restrict__ dy,
+                                                const float* __restrict__ y_raw, const float* __restrict__ y, int M, int C,
+                                                const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                const float* __restrict__ invstd, int relu, bool grads, float* __restrict__ db,
+                                                float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    for (int i = threadIdx.x; i < M * 32; i += blockDim.x) {
         const int m = i / 32, cl = i % 32, c = c0 + cl;
         float g = 0.f;
         if (c < C) {
@@ -150,20 +147,32 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
                 const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
                 s0 += s_d[m][cl]; s1 += (double)s_d[m][cl] * xh;
             }
-            if (dgamma) { dgamma[c] += (float)s1; dbeta[c] += (float)s0; }
+            if (grads && dgamma) { dgamma[c] += (float)s1; dbeta[c] += (float)s0; }
             const float m0 = (float)(s0 / M), m1 = (float)(s1 / M);
             for (int m = 0; m < M; ++m) {
                 const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
                 s_d[m][cl] = gamma[c] * invstd[c] * (s_d[m][cl] - m0 - xh * m1);
             }
         }
-        if (db) {
+        if (grads && db) {
             float s = 0.f;
             for (int m = 0; m < M; ++m) s += s_d[m][cl];
             db[c] += s;
         }
     }
     __syncthreads();
+}
+
+// dw[c,l] += sum_m dy_raw z, db[c] += sum_m dy_raw, dgamma / dbeta += (parameter gradients accumulate). One block per 32
+// channels.
+__global__ void __launch_bounds__(256)
+vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ y_raw,
+                     const float* __restrict__ y, int M, int L, int C, const float* __restrict__ gamma,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ dw,
+                     float* __restrict__ db, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    __shared__ float s_d[kVecM][33];
+    const int c0 = blockIdx.x * 32;
+    vec_dy_raw_tile(s_d, c0, dy, y_raw, y, M, C, gamma, mean, invstd, relu, true, db, dgamma, dbeta);
     if (dw != nullptr)
         for (int i = threadIdx.x; i < 32 * L; i += 256) {
             const int cl = i / L, l = i % L, c = c0 + cl;
@@ -172,13 +181,38 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
             for (int m = 0; m < M; ++m) acc = fmaf(s_d[m][cl], z[(size_t)m * L + l], acc);
             dw[(size_t)c * L + l] += acc;
         }
-    if (dz != nullptr)
-        for (int i = threadIdx.x; i < M * L; i += 256) {
-            const int m = i / L, l = i % L;
-            float acc = 0.f;
-            for (int cl = 0; cl < 32 && c0 + cl < C; ++cl) acc = fmaf(s_d[m][cl], w[(size_t)(c0 + cl) * L + l], acc);
-            atomicAdd(&dz[(size_t)m * L + l], acc);
+}
+
+// dz[m,l] += sum_c dy_raw[m,c] w[c,l]. One block per 32 columns l; it walks the channels in a fixed order (dy_raw tiles are
+// recomputed per block: M*C values), so the input gradient is bit-reproducible from run to run - it feeds the BatchNorm
+// backward of the 2x2 / 4x4 encoder maps, which amplifies fp32 atomics-order noise by orders of magnitude.
+__global__ void __launch_bounds__(256)
+vec_layer_dz_kernel(const float* __restrict__ dy, const float* __restrict__ w, const float* __restrict__ y_raw,
+                    const float* __restrict__ y, int M, int L, int C, const float* __restrict__ gamma,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ dz) {
+    __shared__ float s_d[kVecM][33];
+    const int ll = threadIdx.x % 32, mg = threadIdx.x / 32;     // thread: column l, rows mg, mg + 8, ...
+    const int l = blockIdx.x * 32 + ll;
+    float acc[kVecM / 8];
+#pragma unroll
+    for (int j = 0; j < kVecM / 8; ++j) acc[j] = 0.f;
+    for (int c0 = 0; c0 < C; c0 += 32) {
+        vec_dy_raw_tile(s_d, c0, dy, y_raw, y, M, C, gamma, mean, invstd, relu, false, nullptr, nullptr, nullptr);
+        if (l < L) {
+            const int nc = min(32, C - c0);
+            for (int cl = 0; cl < nc; ++cl) {
+                const float wv = __ldg(w + (size_t)(c0 + cl) * L + l);
+#pragma unroll
+                for (int j = 0; j < kVecM / 8; ++j)
+                    if (mg + 8 * j < M) acc[j] = fmaf(s_d[mg + 8 * j][cl], wv, acc[j]);
+            }
         }
+        __syncthreads();                                        // the next tile overwrites s_d
+    }
+    if (l < L)
+#pragma unroll
+        for (int j = 0; j < kVecM / 8; ++j)
+            if (mg + 8 * j < M) dz[(size_t)(mg + 8 * j) * L + l] += acc[j];
 }
 
 // z = mu + eps * exp(.5 lv) * T  ->  dmu += dz (summed over samples), dlv += dz * eps * .5 * exp(.5 lv) * T
@@ -326,9 +360,13 @@ extern "C" int vu_vec_layer_bwd(const float* dy, const float* z, const float* w,
                                 int L, int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dz,
                                 float* dw, float* db, float* dgamma, float* dbeta, vu_stream_t st) {
     if (!dy || !z || !w || !y_raw || !y || M < 1 || M > kVecM) return set_error(VU_ERR_INVALID, "vec_layer_bwd: bad args (M <= 64)");
-    vec_layer_bwd_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, z, w, y_raw, y, M, L, C, gamma, mean, invstd, relu, dz,
-                                                                      dw, db, dgamma, dbeta);
+    vec_layer_bwd_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, z, y_raw, y, M, L, C, gamma, mean, invstd, relu, dw,
+                                                                      db, dgamma, dbeta);
     VU_CHECK_LAUNCH("vec_layer_bwd");
+    if (dz != nullptr) {
+        vec_layer_dz_kernel<<<(L + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, w, y_raw, y, M, L, C, gamma, mean, invstd, relu, dz);
+        VU_CHECK_LAUNCH("vec_layer_dz");
+    }
     return 0;
 }
 

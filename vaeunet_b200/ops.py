@@ -108,9 +108,12 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
            bias: Optional[torch.Tensor], relu: bool, out: Optional[Act] = None, residual: Optional[Act] = None,
            out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0,
            fuse_w: Optional[torch.Tensor] = None, fuse_bias: float = 0.0, fuse_out: Optional[torch.Tensor] = None,
-           store: bool = True, pos_bias: Optional[torch.Tensor] = None) -> Optional[Act]:
+           store: bool = True, pos_bias: Optional[torch.Tensor] = None,
+           stat_sums: Optional[torch.Tensor] = None) -> Optional[Act]:
     """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y.
-    pos_bias: fp32 [N, 9, Cout] pre-scale bias by border class (`border_bias`): spatially constant input channels left out."""
+    pos_bias: fp32 [N, 9, Cout] pre-scale bias by border class (`border_bias`): spatially constant input channels left out.
+    stat_sums: ZEROED fp64 [2*Cout]; the epilogue adds per-channel sum / sum of squares of the stored outputs (the
+    statistics a following train-mode BatchNorm needs: bn_train_fwd(sums=))."""
     require_device()
     Cout = w_packed.shape[0]
     assert w_packed.shape[1] == k * k and w_packed.shape[2] == x.C, (tuple(w_packed.shape), k, x.C)
@@ -148,6 +151,11 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
         a.pos_bias = _f32(pos_bias).data_ptr()
     else:
         a.pos_bias = None
+    if stat_sums is not None:
+        assert stat_sums.dtype == torch.float64 and stat_sums.numel() == 2 * Cout and stat_sums.is_contiguous() and store
+        a.stat_sums = stat_sums.data_ptr()
+    else:
+        a.stat_sums = None
     if CONV_TIMING is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

@@ -22,12 +22,18 @@ def _sums(dev, n=2048) -> torch.Tensor:
 
 
 def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, residual: Optional[Act] = None,
-                 out: Optional[Act] = None, update_running: bool = True):
-    """Train-mode BatchNorm2d (+residual, +ReLU). -> (y, mean, invstd)."""
+                 out: Optional[Act] = None, update_running: bool = True, sums: Optional[torch.Tensor] = None):
+    """Train-mode BatchNorm2d (+residual, +ReLU). -> (y, mean, invstd).
+    sums: fp64 [2C] per-channel sum / sum of squares of x already accumulated by the producing conv
+    (ops.conv2d(stat_sums=)); the statistics pass over x is skipped."""
     require_device()
     Cc, dev = x.C, x.t.device
-    sums = _sums(dev, 2 * Cc)
-    check(load().vu_bn_stats(x.t.data_ptr(), _npix(x), Cc, x.ctot, x.coff, sums.data_ptr(), x.dt, _stream()), "vu_bn_stats")
+    if sums is None:
+        sums = _sums(dev, 2 * Cc)
+        check(load().vu_bn_stats(x.t.data_ptr(), _npix(x), Cc, x.ctot, x.coff, sums.data_ptr(), x.dt, _stream()), "vu_bn_stats")
+        _count(2)
+    else:
+        assert sums.dtype == torch.float64 and sums.numel() == 2 * Cc
     mean = torch.empty(Cc, dtype=torch.float32, device=dev)
     invstd = torch.empty(Cc, dtype=torch.float32, device=dev)
     check(load().vu_bn_finalize(sums.data_ptr(), float(_npix(x)), Cc, BN_EPS, BN_MOMENTUM, mean.data_ptr(), invstd.data_ptr(),
@@ -40,7 +46,7 @@ def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, res
                              _f32(gamma).data_ptr(), _f32(beta).data_ptr(), r.t.data_ptr() if r else None,
                              r.ctot if r else 8, r.coff if r else 0, int(relu), out.t.data_ptr(), out.ctot, out.coff, x.dt,
                              _stream()), "vu_bn_apply")
-    _count(4)
+    _count(2)
     return out, mean, invstd
 
 
@@ -242,7 +248,7 @@ def vec_layer_bwd(dy, saved, w, gamma, relu: bool, dz: Optional[torch.Tensor], w
     check(load().vu_vec_layer_bwd(_f32(dy.contiguous()).data_ptr(), z.data_ptr(), _f32(w).data_ptr(), y_raw.data_ptr(),
                                   y.data_ptr(), M, L, Cc, _ptr(gamma), _ptr(mean), _ptr(invstd), int(relu), _ptr(dz),
                                   dw.data_ptr(), _ptr(db), _ptr(dg), _ptr(dbeta), _stream()), "vu_vec_layer_bwd")
-    _count()
+    _count(2 if dz is not None else 1)
     return dw, db, dg, dbeta
 
 

@@ -33,6 +33,11 @@ from ._lib import VaeUnetError
 from .engine import RESNET34_STAGES
 from .ops import Act
 
+import os
+
+# BatchNorm forward statistics accumulated in the epilogue of the producing conv (VU_FUSE_BN_STATS=0: separate pass)
+FUSE_BN_STATS = os.environ.get("VU_FUSE_BN_STATS", "1") != "0"
+
 _ALIGN = 64   # floats: every parameter starts on a 256-byte boundary of the flat buffers
 
 
@@ -186,6 +191,10 @@ class TrainStep:
             goff[name] = total
             total += (self.P[c.name].numel() + _ALIGN - 1) // _ALIGN * _ALIGN
         self.flat_gp = torch.zeros(total, dtype=torch.float32, device=self.dev)
+        # one fp64 (sum, sum of squares) pair per output channel of every conv that feeds a BatchNorm
+        self.stat_ws = torch.zeros(2 * (64 + sum(c.w16.shape[0] for c in self.convs.values())), dtype=torch.float64,
+                                   device=self.dev)
+        self._stat_off = 0
         self.GP = {}
         for name, c in self.convs.items():
             O, I = self.P[c.name].shape[:2]
@@ -213,14 +222,27 @@ class TrainStep:
         ops._count(2)
 
     # ------------------------------------------------------------------ small helpers
-    def _conv(self, x: Act, name: str, bias: Optional[torch.Tensor] = None, out: Optional[Act] = None) -> Act:
+    def _stat_slot(self, cout: int) -> torch.Tensor:
+        """fp64 [2*cout] slice of the per-step statistics workspace (zeroed once at the start of forward())."""
+        o = self._stat_off
+        self._stat_off = o + 2 * cout
+        assert self._stat_off <= self.stat_ws.numel(), "statistics workspace too small"
+        return self.stat_ws[o:o + 2 * cout]
+
+    def _conv(self, x: Act, name: str, bias: Optional[torch.Tensor] = None, out: Optional[Act] = None,
+              stats: bool = False) -> Act:
+        """stats: the conv epilogue also accumulates the BatchNorm statistics of its output (picked up by _bn)."""
         c = self.convs[name]
-        return ops.conv2d(x, c.w16, c.k, c.stride, c.k // 2, None, bias, False, out=out)
+        sums = self._stat_slot(c.w16.shape[0]) if stats and FUSE_BN_STATS else None
+        y = ops.conv2d(x, c.w16, c.k, c.stride, c.k // 2, None, bias, False, out=out, stat_sums=sums)
+        y.stat_sums = sums
+        return y
 
     def _bn(self, x_raw: Act, bn: str, relu: bool, residual: Optional[Act] = None, out: Optional[Act] = None):
         P, Bf = self.P, self.Bf
         y, mean, invstd = T.bn_train_fwd(x_raw, P[bn + "weight"], P[bn + "bias"], Bf[bn + "running_mean"],
-                                         Bf[bn + "running_var"], relu, residual, out)
+                                         Bf[bn + "running_var"], relu, residual, out,
+                                         sums=getattr(x_raw, "stat_sums", None))
         return y, (mean, invstd)
 
     def _bn_bwd(self, x_raw: Act, dy: Act, y_relu: Optional[Act], st, bn: str, want_dz=False, dx: Optional[Act] = None,
@@ -259,7 +281,11 @@ class TrainStep:
         S: dict = {"images": images, "B": B, "H": H, "W": W}
         # stem 7x7 s2 on the tensor cores: im2col patches (147 -> 152 columns) x 1x1 filter bank
         xcol = T.im2col_small_cin(images, 7, 2, 3, dt)
-        x0raw = ops.conv2d(xcol, self.stem_w16, 1, 1, 0, None, None, False)
+        self.stat_ws.zero_()
+        self._stat_off = 0
+        sums0 = self._stat_slot(self.stem_w16.shape[0]) if FUSE_BN_STATS else None
+        x0raw = ops.conv2d(xcol, self.stem_w16, 1, 1, 0, None, None, False, stat_sums=sums0)
+        x0raw.stat_sums = sums0
         S["xcol"] = xcol
         f0, st0 = self._bn(x0raw, "encoder.bn1.", True)
         pool, pool_code = T.maxpool_idx_fwd(f0, 3, 2, 1)
@@ -272,13 +298,13 @@ class TrainStep:
                 q = f"encoder.layer{li}.{b}."
                 r = {"q": q, "x": x}
                 if (q + "downsample.0") in self.convs:
-                    r["idraw"] = self._conv(x, q + "downsample.0")
+                    r["idraw"] = self._conv(x, q + "downsample.0", stats=True)
                     idt, r["st_ds"] = self._bn(r["idraw"], q + "downsample.1.", False)
                 else:
                     idt = x
-                r["y1raw"] = self._conv(x, q + "conv1")
+                r["y1raw"] = self._conv(x, q + "conv1", stats=True)
                 r["y1"], r["st1"] = self._bn(r["y1raw"], q + "bn1.", True)
-                r["y2raw"] = self._conv(r["y1"], q + "conv2")
+                r["y2raw"] = self._conv(r["y1"], q + "conv2", stats=True)
                 r["out"], r["st2"] = self._bn(r["y2raw"], q + "bn2.", True, residual=idt)
                 x = r["out"]
                 blocks.append(r)
@@ -317,7 +343,7 @@ class TrainStep:
                 g1low = self._conv(x, a + "W_g.0", bias=P[a + "W_g.0.bias"])
                 r["g1raw"] = ops.bilinear_ac(g1low, Hs, Ws)
                 g1n, r["st_g"] = self._bn(r["g1raw"], a + "W_g.1.", False)
-            r["x1raw"] = self._conv(skip, a + "W_x.0", bias=P[a + "W_x.0.bias"])
+            r["x1raw"] = self._conv(skip, a + "W_x.0", bias=P[a + "W_x.0.bias"], stats=True)
             r["s"], r["st_x"] = self._bn(r["x1raw"], a + "W_x.1.", True, residual=g1n)        # relu(g1 + x1)
             r["psi_raw"] = ops.final_conv1(r["s"], P[a + "psi.0.weight"].view(-1), 0.0, bias_dev=P[a + "psi.0.bias"])
             r["psi"], r["psi_stat"] = T.map_bn_sigmoid_fwd(r["psi_raw"], P[a + "psi.1.weight"], P[a + "psi.1.bias"],
@@ -325,9 +351,9 @@ class TrainStep:
             T.scale_by_map(skip, r["psi"], cat.slice(cx, cs))
             zv, r["zp_saved"] = self._vec(z, p + "z_proj.0.", p + "z_proj.1.", True, float(B * Hs * Ws))
             ops.broadcast_vec(zv, cat.slice(cx + cs, L))
-            r["y1raw"] = self._conv(cat, p + "conv1.0")
+            r["y1raw"] = self._conv(cat, p + "conv1.0", stats=True)
             r["y1"], r["st1"] = self._bn(r["y1raw"], p + "conv1.1.", True)
-            r["y2raw"] = self._conv(r["y1"], p + "conv2.0")
+            r["y2raw"] = self._conv(r["y1"], p + "conv2.0", stats=True)
             r["y2"], r["st2"] = self._bn(r["y2raw"], p + "conv2.1.", True)
             x = r["y2"]
             dec.append(r)
