@@ -29,6 +29,14 @@ CASES = [
     ("halo_128_res", 2, 32, 128, 128, 128, 3, 1, True, True, (0, 0), (0, 0), "bf16"),
     ("halo_odd_slices", 2, 35, 175, 96, 64, 3, 1, True, True, (32, 160), (64, 192), "f16"),
     ("halo_352_128_w128", 1, 128, 128, 352, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    # CTA-pair kernel (256-pixel tiles over two SMs): odd number of 128-pixel tiles (the peer's last tile is empty), many
+    # tiles per pair, partial last filter tile (Cout 320 with 256-column tiles), residual + channel slices
+    ("pair_odd_tiles", 3, 16, 16, 256, 256, 3, 1, True, True, (0, 0), (0, 0), "bf16"),
+    ("pair_odd_tiles_7", 7, 8, 16, 128, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("pair_persistent", 16, 64, 64, 128, 128, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("pair_cout320", 2, 32, 32, 128, 320, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("pair_slices_res", 2, 32, 32, 192, 256, 3, 1, True, True, (64, 320), (128, 512), "f16"),
+    ("pair_1x1_s2", 4, 32, 32, 128, 256, 1, 2, False, False, (0, 0), (0, 0), "bf16"),
 ]
 
 

@@ -51,6 +51,88 @@ template <int BN> struct ConvCfg {
                                       2 * kMaxCout * 4 + 2 * kMaxCout * 8;   // scale, bias; per-CTA fp64 statistic partials
 };
 
+// Epilogue of one 128-pixel x BN tile: TMEM -> registers -> (pos_bias, scale/bias, residual, ReLU) -> 16-bit NHWC store,
+// plus the optional BatchNorm statistics of the stored values. Called by the four epilogue warps (q = TMEM lane quarter);
+// `taddr` addresses this warp's lanes of the accumulator.
+template <int BN>
+__device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_t taddr, int n_tile, int m_tile, int q, int lane,
+                                                   const float* s_scale, const float* s_bias, double* s_sum, double* s_sq) {
+    const int m = q * 32 + lane;              // row of the tile = pixel
+    const int w_l = m % p.wt;
+    const int h_l = (m / p.wt) % p.ht;
+    const int n_l = m / (p.wt * p.ht);
+    const int wb = m_tile % p.tiles_w;
+    const int hb = (m_tile / p.tiles_w) % p.tiles_h;
+    const int nb = m_tile / (p.tiles_w * p.tiles_h);
+    const int wo = wb * p.wt + w_l, ho = hb * p.ht + h_l, ni = nb * p.nt + n_l;
+    const bool valid = (wo < p.wo) && (ho < p.ho) && (ni < p.n_img);
+    const size_t opix = (static_cast<size_t>(ni) * p.out_h + (ho * p.out_up + p.out_dh)) * p.out_w +
+                        (wo * p.out_up + p.out_dw);
+    const size_t rpix = (static_cast<size_t>(ni) * p.ho + ho) * p.wo + wo;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+        const int ch0 = n_tile * BN + c * 32;
+        if (ch0 >= p.cout) break;             // partial last N tile (Cout is a multiple of 32; warp-uniform)
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        uint32_t outw[16];
+        uint4 rv[4];
+        if (p.residual != nullptr && valid) {
+            const uint4* rp = reinterpret_cast<const uint4*>(
+                p.residual + rpix * p.res_ctot + p.res_coff + ch0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+        }
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+        if (p.pos_bias != nullptr) {
+            const int hc = min(ho, p.ho - 1), wc = min(wo, p.wo - 1), nc = min(ni, p.n_img - 1);
+            const int cls = (hc == 0 ? 0 : (hc == p.ho - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.wo - 1 ? 2 : 1));
+            const float4* pp = reinterpret_cast<const float4*>(p.pos_bias + (static_cast<size_t>(nc) * 9 + cls) * p.cout + ch0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 b = __ldg(pp + j);
+                r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + b.x);
+                r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + b.y);
+                r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + b.z);
+                r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            float v0 = __uint_as_float(r[2 * j]) * s_scale[ch0 + 2 * j] + s_bias[ch0 + 2 * j];
+            float v1 = __uint_as_float(r[2 * j + 1]) * s_scale[ch0 + 2 * j + 1] + s_bias[ch0 + 2 * j + 1];
+            if (p.residual != nullptr) {
+                float2 rr = unpack2(rw[j], p.dtype);
+                v0 += rr.x; v1 += rr.y;
+            }
+            if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
+            outw[j] = pack2(v0, v1, p.dtype);
+        }
+        if (valid) {
+            uint4* op = reinterpret_cast<uint4*>(p.y + opix * p.y_ctot + p.y_coff + ch0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                op[j] = make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
+        }
+        if (p.stat_sums != nullptr) {          // statistics of the values as stored (16-bit rounded); warp-uniform branch
+            float a[32], b[32];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float2 f = unpack2(outw[j], p.dtype);
+                a[2 * j] = valid ? f.x : 0.0f; a[2 * j + 1] = valid ? f.y : 0.0f;
+                b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
+            }
+            const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
+            atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
+            atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
+        }
+    }
+}
+
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
@@ -172,89 +254,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     } else {
         // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
-        const int m = q * 32 + lane;              // row of the tile = pixel
-        const int w_l = m % p.wt;
-        const int h_l = (m / p.wt) % p.ht;
-        const int n_l = m / (p.wt * p.ht);
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
             const int acc = tcount & 1;
             const uint32_t accph = (tcount >> 1) & 1;
             const int n_tile = tile % p.num_n_tiles;
             const int m_tile = tile / p.num_n_tiles;
-            const int wb = m_tile % p.tiles_w;
-            const int hb = (m_tile / p.tiles_w) % p.tiles_h;
-            const int nb = m_tile / (p.tiles_w * p.tiles_h);
-            const int wo = wb * p.wt + w_l, ho = hb * p.ht + h_l, ni = nb * p.nt + n_l;
-            const bool valid = (wo < p.wo) && (ho < p.ho) && (ni < p.n_img);
-            const size_t opix = (static_cast<size_t>(ni) * p.out_h + (ho * p.out_up + p.out_dh)) * p.out_w +
-                                (wo * p.out_up + p.out_dw);
-            const size_t rpix = (static_cast<size_t>(ni) * p.ho + ho) * p.wo + wo;
             mbar_wait(tfull_bar(acc), accph);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                const int ch0 = n_tile * BN + c * 32;
-                if (ch0 >= p.cout) break;             // partial last N tile (Cout is a multiple of 32; warp-uniform)
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(taddr + c * 32, r);
-                tmem_ld_wait();
-                uint32_t outw[16];
-                uint4 rv[4];
-                if (p.residual != nullptr && valid) {
-                    const uint4* rp = reinterpret_cast<const uint4*>(
-                        p.residual + rpix * p.res_ctot + p.res_coff + ch0);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) rv[j] = make_uint4(0, 0, 0, 0);
-                }
-                const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
-                if (p.pos_bias != nullptr) {
-                    const int hc = min(ho, p.ho - 1), wc = min(wo, p.wo - 1), nc = min(ni, p.n_img - 1);
-                    const int cls = (hc == 0 ? 0 : (hc == p.ho - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.wo - 1 ? 2 : 1));
-                    const float4* pp = reinterpret_cast<const float4*>(p.pos_bias + (static_cast<size_t>(nc) * 9 + cls) * p.cout + ch0);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 b = __ldg(pp + j);
-                        r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + b.x);
-                        r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + b.y);
-                        r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + b.z);
-                        r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    float v0 = __uint_as_float(r[2 * j]) * s_scale[ch0 + 2 * j] + s_bias[ch0 + 2 * j];
-                    float v1 = __uint_as_float(r[2 * j + 1]) * s_scale[ch0 + 2 * j + 1] + s_bias[ch0 + 2 * j + 1];
-                    if (p.residual != nullptr) {
-                        float2 rr = unpack2(rw[j], p.dtype);
-                        v0 += rr.x; v1 += rr.y;
-                    }
-                    if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
-                    outw[j] = pack2(v0, v1, p.dtype);
-                }
-                if (valid) {
-                    uint4* op = reinterpret_cast<uint4*>(p.y + opix * p.y_ctot + p.y_coff + ch0);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        op[j] = make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
-                }
-                if (p.stat_sums != nullptr) {          // statistics of the values as stored (16-bit rounded); warp-uniform branch
-                    float a[32], b[32];
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float2 f = unpack2(outw[j], p.dtype);
-                        a[2 * j] = valid ? f.x : 0.0f; a[2 * j + 1] = valid ? f.y : 0.0f;
-                        b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
-                    }
-                    const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
-                    atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
-                    atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
-                }
-            }
+            conv_epilogue_tile<BN>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q, lane,
+                                   s_scale, s_bias, s_sum, s_sq);
             tc_fence_before();
             mbar_arrive(tempty_bar(acc));
         }
@@ -270,6 +279,182 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// CTA-pair variant (cluster of 2, tcgen05 cta_group::2): one 256-pixel x BN tile per pair. Each CTA stages its own 128
+// pixel rows of A and HALF of the filter rows of B; the leader's MMA reads both halves, so a k-iteration moves
+// 16 KB + BN*64 B per SM through L2 instead of 16 KB + BN*128 B. The mid-resolution layers (K = 9*Cin deep, 128..512
+// channels) sit on the L2->SM cap (~6300 B/clk chip-wide, profiles/r1a_conv_800to512_32sq.summary.txt), not on the tensor pipe.
+//   full[s]   : leader's barrier, 2 arrivals (both producers) + the bytes of both CTAs' loads
+//   empty[s]  : per CTA, released by the leader's MMA commit (multicast to both CTAs)
+//   tfull[a]  : per CTA, same multicast commit; each CTA's epilogue drains its own TMEM lanes
+//   tempty[a] : leader's barrier, 256 arrivals (the epilogue threads of both CTAs)
+// ------------------------------------------------------------------------------------------
+template <int BN> struct PairCfg {
+    static constexpr int kBBytes = (BN / 2) * kBlockK * 2;          // this CTA's half of the filter rows
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (BN == 256) ? 6 : 8;
+    static constexpr int kTmemCols = 2 * BN;
+    static constexpr int kBarBytes = 1024;
+    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + 2 * kMaxCout * 4 + 2 * kMaxCout * 8;
+    static_assert(kSmemBytes <= 232448, "smem budget");
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
+                       const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a3,
+                       const __grid_constant__ CUtensorMap map_w, const ConvKParams p) {
+    using Cfg = PairCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+    const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * Cfg::kStages + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * Cfg::kStages + 4);
+    volatile uint32_t* tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
+    float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
+    float* s_bias = s_scale + kMaxCout;
+    double* s_sum = reinterpret_cast<double*>(s_bias + kMaxCout);
+    double* s_sq = s_sum + kMaxCout;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();              // 0 = leader (issues the MMAs)
+    const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_a0);
+        tma_prefetch_desc(&map_w);
+        for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(full_bar(s), 2); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 256); }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+        tmem_relinquish_pair();
+    }
+    for (int c = threadIdx.x; c < p.cout; c += kThreads) {
+        s_scale[c] = p.scale ? p.scale[c] : 1.0f;
+        s_bias[c] = p.bias ? p.bias[c] : 0.0f;
+        s_sum[c] = 0.0; s_sq[c] = 0.0;
+    }
+    tc_fence_before();
+    cluster_sync_all();                                   // barrier inits + TMEM allocation visible to the peer
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    const int m_pairs = (p.num_m_tiles + 1) >> 1;
+    const int total_tiles = m_pairs * p.num_n_tiles;      // pair tiles
+    const int k_iters = p.num_taps * p.kblocks;
+
+    if (warp == 0) {
+        // ===================== TMA producer (one lane per CTA) =====================
+        if (lane == 0) {
+            const CUtensorMap* maps[4] = {&map_a0, &map_a1, &map_a2, &map_a3};
+            const uint32_t leader_full0 = mapa_cluster(full_bar(0), 0);
+            uint32_t it = 0;
+            for (int tile = pair_id; tile < total_tiles; tile += num_pairs) {
+                const int n_tile = tile % p.num_n_tiles;
+                const int m_tile = 2 * (tile / p.num_n_tiles) + (int)rank;   // may be one past the end: loads zero fill
+                const int wb = m_tile % p.tiles_w;
+                const int hb = (m_tile / p.tiles_w) % p.tiles_h;
+                const int nb = m_tile / (p.tiles_w * p.tiles_h);
+                const int w0 = wb * p.wt, h0 = hb * p.ht, n0 = nb * p.nt;
+                for (int tap = 0; tap < p.num_taps; ++tap) {
+                    const CUtensorMap* ma = maps[p.tap_map[tap]];
+                    const int ww = w0 + p.tap_dw[tap], hh = h0 + p.tap_dh[tap];
+                    const int widx = p.tap_widx[tap];
+                    for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
+                        const int s = it % Cfg::kStages;
+                        const uint32_t ph = (it / Cfg::kStages) & 1;
+                        mbar_wait(empty_bar(s), ph ^ 1);
+                        const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                        if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * Cfg::kStageBytes);
+                        else mbar_arrive_cluster(leader_full0 + 8u * s);
+                        tma_load_4d_pair(sa, ma, full_bar(s), kb * kBlockK, ww, hh, n0);
+                        tma_load_3d_pair(sa + kABytes, &map_w, full_bar(s), kb * kBlockK, widx,
+                                         n_tile * BN + (int)rank * (BN / 2));
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: leader CTA only =====================
+        if (rank == 0) {
+            const uint32_t idesc = umma_idesc_f16(2 * kTileM, BN, p.dtype == 0 ? 1u : 0u);
+            uint32_t it = 0, tcount = 0;
+            for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
+                const int acc = tcount & 1;
+                const uint32_t accph = (tcount >> 1) & 1;
+                mbar_wait(tempty_bar(acc), accph ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int ki = 0; ki < k_iters; ++ki, ++it) {
+                    const int s = it % Cfg::kStages;
+                    const uint32_t ph = (it / Cfg::kStages) & 1;
+                    mbar_wait(full_bar(s), ph);
+                    tc_fence_after();
+                    const uint32_t sa = smem_base + s * Cfg::kStageBytes;
+                    const uint64_t adesc = umma_desc_k_sw128(sa);
+                    const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
+                    const int kb = ki % p.kblocks;
+                    const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
+                    if (elect_one()) {
+                        if (nk == 4) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_f16_ss_pair(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
+                        } else {
+                            for (int k = 0; k < nk; ++k)
+                                umma_f16_ss_pair(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (ki | k) != 0);
+                        }
+                        umma_commit_pair(empty_bar(s), 3);
+                        if (ki == k_iters - 1) umma_commit_pair(tfull_bar(acc), 3);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue: each CTA drains its own 128 TMEM lanes =====================
+        const int q = warp & 3;
+        const uint32_t leader_tempty0 = mapa_cluster(tempty_bar(0), 0);
+        uint32_t tcount = 0;
+        for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
+            const int acc = tcount & 1;
+            const uint32_t accph = (tcount >> 1) & 1;
+            const int n_tile = tile % p.num_n_tiles;
+            const int m_tile = 2 * (tile / p.num_n_tiles) + (int)rank;
+            mbar_wait(tfull_bar(acc), accph);
+            tc_fence_after();
+            if (m_tile < p.num_m_tiles)
+                conv_epilogue_tile<BN>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q, lane,
+                                       s_scale, s_bias, s_sum, s_sq);
+            tc_fence_before();
+            mbar_arrive_cluster(leader_tempty0 + 8u * acc);
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();                                   // no CTA leaves while the peer may still signal it / read its smem
+    if (p.stat_sums != nullptr)
+        for (int c = threadIdx.x; c < p.cout; c += kThreads) {
+            const double a = s_sum[c], b = s_sq[c];
+            if (a != 0.0 || b != 0.0) {
+                atomicAdd(&p.stat_sums[c], a);
+                atomicAdd(&p.stat_sums[p.cout + c], b);
+            }
+        }
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
     }
 }
 
@@ -311,6 +496,38 @@ static int launch_conv(const CUtensorMap* am, const CUtensorMap& wm, const ConvK
     conv_igemm_kernel<BN><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(am[0], am[1], am[2], am[3], wm, kp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_igemm launch: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// CTA pairs: cluster of 2 along x. -> 0 launched, >0 error; `max_clusters` is how many pairs can be co-resident.
+template <int BN>
+static int launch_conv_pair(const CUtensorMap* am, const CUtensorMap& wm, const ConvKParams& kp, int max_ctas,
+                            cudaStream_t stream) {
+    using Cfg = PairCfg<BN>;
+    static int max_clusters = -1;
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = stream;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (max_clusters < 0) {
+        cudaError_t e = cudaFuncSetAttribute(conv_igemm_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::kSmemBytes);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        cfg.gridDim = dim3(2 * (num_sms() / 2));
+        int n = 0;
+        e = cudaOccupancyMaxActiveClusters(&n, conv_igemm_pair_kernel<BN>, &cfg);
+        if (e != cudaSuccess || n < 1) return set_error(VU_ERR_CUDA, "cudaOccupancyMaxActiveClusters: %s", cudaGetErrorString(e));
+        max_clusters = n;
+    }
+    int pairs = ((kp.num_m_tiles + 1) / 2) * kp.num_n_tiles;
+    int cap = max_clusters;
+    if (max_ctas > 0 && max_ctas / 2 < cap) cap = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
+    if (pairs > cap) pairs = cap;
+    cfg.gridDim = dim3(2 * pairs);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_igemm_pair_kernel<BN>, am[0], am[1], am[2], am[3], wm, kp);
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_igemm_pair launch: %s", cudaGetErrorString(e));
     return 0;
 }
 
@@ -420,15 +637,22 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
     }
     for (int i = nmaps; i < 4; ++i) am[i] = am[0];
 
+    // CTA pairs (256-pixel tiles, half of the filter rows per SM) for the wide tiles: fewer operand bytes per MMA through L2
+    static const int pair_mode = getenv("VU_CONV_PAIR") ? atoi(getenv("VU_CONV_PAIR")) : 1;
+    const bool pair = pair_mode != 0 && bn >= 128 && kp.num_m_tiles >= 2;
+
     // weight map: [Cout][taps][Cin]
     CUtensorMap wm;
     {
         const uint64_t dims[3] = {(uint64_t)a->Cin, (uint64_t)(KH * KW), (uint64_t)a->Cout};
         const uint64_t str[2] = {(uint64_t)a->Cin * 2, (uint64_t)a->Cin * 2 * KH * KW};
-        const uint32_t wbox[3] = {(uint32_t)kBlockK, 1u, (uint32_t)bn};
+        const uint32_t wbox[3] = {(uint32_t)kBlockK, 1u, (uint32_t)(pair ? bn / 2 : bn)};
         int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
         if (rc) return rc;
     }
+    if (pair)
+        return bn == 256 ? launch_conv_pair<256>(am, wm, kp, a->max_ctas, stream)
+                         : launch_conv_pair<128>(am, wm, kp, a->max_ctas, stream);
     switch (bn) {
         case 256: return launch_conv<256>(am, wm, kp, a->max_ctas, stream);
         case 128: return launch_conv<128>(am, wm, kp, a->max_ctas, stream);
