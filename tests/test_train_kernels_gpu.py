@@ -183,7 +183,8 @@ def test_maxpool_bilinear_bwd(cuda_dev):
     assert (_nchw(y2) - yz.detach()).abs().max() == 0
     dx2 = T.maxpool_idx_bwd(code, _act(ops, dyz, d), 13, 14, 3, 2, 1)
     assert (_nchw(dx2) - xzr.grad).abs().max() <= 1e-2 * xzr.grad.abs().max()
-    for (hs, ws, ho, wo) in [(8, 8, 16, 16), (11, 9, 22, 17), (1, 1, 5, 6), (16, 16, 32, 32)]:
+    for (hs, ws, ho, wo) in [(8, 8, 16, 16), (11, 9, 22, 17), (1, 1, 5, 6), (16, 16, 32, 32), (64, 64, 128, 128),
+                             (5, 7, 17, 20), (32, 48, 63, 97)]:     # x2 (unrolled tap kernel), x3 and odd sizes
         x = torch.randn(2, 24, hs, ws, generator=g).requires_grad_(True)
         y = F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
         dy = _q(torch.randn(y.shape, generator=g))

@@ -350,15 +350,17 @@ __global__ void maxpool_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __
 // ---------------------------------------------------------------- bilinear, align_corners=True
 // Coordinate arithmetic follows ATen's upsample_bilinear2d (area_pixel_compute_scale /
 // _source_index with align_corners): scale = (in-1)/(out-1) in fp32, src = scale*dst.
-__global__ void bilinear_ac_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ y, int N, int Hs, int Ws,
+// I = index type: 32-bit arithmetic whenever the element count allows (64-bit div/mod costs more than the memory traffic)
+template <typename I>
+__global__ void __launch_bounds__(256) bilinear_ac_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __restrict__ y, int N, int Hs, int Ws,
                                         int C8, int x_ctot, int x_coff, int Ho, int Wo, int Hd, int Wd, int pad_t,
                                         int pad_l, int y_ctot, int y_coff, float sh, float sw, int dtype) {
-    const size_t total = (size_t)N * Ho * Wo * C8;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const I total = (I)N * Ho * Wo * C8;
+    for (I idx = blockIdx.x * (I)blockDim.x + threadIdx.x; idx < total; idx += (I)gridDim.x * blockDim.x) {
         const int c8 = idx % C8;
         const int wo = (idx / C8) % Wo;
-        const int ho = (idx / ((size_t)C8 * Wo)) % Ho;
-        const int n = idx / ((size_t)C8 * Wo * Ho);
+        const int ho = (idx / ((I)C8 * Wo)) % Ho;
+        const int n = idx / ((I)C8 * Wo * Ho);
         const float h1r = sh * ho;
         const int h1 = (int)h1r;
         const int h1p = (h1 < Hs - 1) ? 1 : 0;
@@ -542,8 +544,12 @@ extern "C" int vu_bilinear_ac_nhwc(const void* x, void* y, int N, int Hs, int Ws
     const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
     const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
     const size_t total = (size_t)N * Ho * Wo * (C / 8);
-    bilinear_ac_nhwc_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(
-        (const uint16_t*)x, (uint16_t*)y, N, Hs, Ws, C / 8, x_ctot, x_coff, Ho, Wo, Hd, Wd, pad_t, pad_l, y_ctot, y_coff, sh, sw, dtype);
+    if (total < (1ull << 31))
+        bilinear_ac_nhwc_kernel<uint32_t><<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, (uint16_t*)y, N, Hs, Ws, C / 8, x_ctot, x_coff, Ho, Wo, Hd, Wd, pad_t, pad_l, y_ctot, y_coff, sh, sw, dtype);
+    else
+        bilinear_ac_nhwc_kernel<size_t><<<grid_for(total, 256), 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, (uint16_t*)y, N, Hs, Ws, C / 8, x_ctot, x_coff, Ho, Wo, Hd, Wd, pad_t, pad_l, y_ctot, y_coff, sh, sw, dtype);
     VU_CHECK_LAUNCH("bilinear");
     return 0;
 }

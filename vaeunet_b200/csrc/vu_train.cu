@@ -159,10 +159,7 @@ bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const fl
         }
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (FIXED) coeff((int)(idx % C8));
-    auto one = [&](size_t i, const uint4& vx, const uint4& vr) {
-        const int c8 = (int)(i % C8);
-        const size_t p = i / C8;
+    auto one = [&](size_t p, int c8, const uint4& vx, const uint4& vr) {
         if (!FIXED) coeff(c8);
         float f[8], r[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         unpack8(vx, f, dtype);
@@ -174,18 +171,32 @@ bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const fl
         }
         *(reinterpret_cast<uint4*>(y + p * y_ctot + y_coff) + c8) = pack8(f, dtype);
     };
-    auto ldx = [&](size_t i) { return __ldg(reinterpret_cast<const uint4*>(x + (i / C8) * x_ctot + x_coff) + (i % C8)); };
-    auto ldr = [&](size_t i) {
-        return res ? __ldg(reinterpret_cast<const uint4*>(res + (i / C8) * res_ctot + res_coff) + (i % C8)) : make_uint4(0, 0, 0, 0);
+    auto ldx = [&](size_t p, int c8) { return __ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8); };
+    auto ldr = [&](size_t p, int c8) {
+        return res ? __ldg(reinterpret_cast<const uint4*>(res + p * res_ctot + res_coff) + c8) : make_uint4(0, 0, 0, 0);
     };
-    for (; idx + 3 * stride < total; idx += 4 * stride) {
-        uint4 vx[4], vr[4];
+    if (FIXED) {
+        // 256 % C8 == 0: the thread's channel group never changes and its pixel index advances by a constant; no
+        // division in the loop (64-bit div/mod per element made these kernels instruction-bound, not HBM-bound)
+        const int c8 = threadIdx.x % C8;
+        const size_t pstep = stride / C8;
+        size_t p = idx / C8;
+        coeff(c8);
+        for (; p + 3 * pstep < npix; p += 4 * pstep) {
+            uint4 vx[4], vr[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { vx[u] = ldx(idx + u * stride); vr[u] = ldr(idx + u * stride); }
+            for (int u = 0; u < 4; ++u) { vx[u] = ldx(p + u * pstep, c8); vr[u] = ldr(p + u * pstep, c8); }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) one(idx + u * stride, vx[u], vr[u]);
+            for (int u = 0; u < 4; ++u) one(p + u * pstep, c8, vx[u], vr[u]);
+        }
+        for (; p < npix; p += pstep) one(p, c8, ldx(p, c8), ldr(p, c8));
+    } else {
+        for (; idx < total; idx += stride) {
+            const size_t p = idx / C8;
+            const int c8 = (int)(idx % C8);
+            one(p, c8, ldx(p, c8), ldr(p, c8));
+        }
     }
-    for (; idx < total; idx += stride) one(idx, ldx(idx), ldr(idx));
 }
 
 // dx = gamma * invstd * (dz - mean(dz) - xh * mean(dz * xh)) = ka * dz + kb * x + kc,  dz = dy * (y > 0 if y).
@@ -203,12 +214,14 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
     if (blockIdx.x == 0 && dgamma != nullptr)      // parameter gradients, accumulated (gradient accumulation steps)
         for (int c = threadIdx.x; c < C; c += blockDim.x) { dgamma[c] += (float)sums[C + c]; dbeta[c] += (float)sums[c]; }
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const float inv_count = (float)(1.0 / count);
     float ka[8], kb[8], kc[8], msc[8], msh[8];
     auto coeff = [&](int c8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = c8 * 8 + j;
-            const float m_dz = (float)(sums[c] / count), m_dzx = (float)(sums[C + c] / count);
+            // fp32 from here on: every thread runs this prologue and fp64 division is ~100x slower than an fp32 multiply
+            const float m_dz = (float)sums[c] * inv_count, m_dzx = (float)sums[C + c] * inv_count;
             const float is = invstd[c], a = gamma[c] * is;
             ka[j] = a;
             kb[j] = -a * m_dzx * is;
@@ -218,10 +231,7 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
         }
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (FIXED) coeff((int)(idx % C8));
-    auto one = [&](size_t i, const uint4& vx, const uint4& vg, const uint4& vy) {
-        const int c8 = (int)(i % C8);
-        const size_t p = i / C8;
+    auto one = [&](size_t p, int c8, const uint4& vx, const uint4& vg, const uint4& vy) {
         if (!FIXED) coeff(c8);
         float f[8], g[8];
         unpack8(vx, f, dtype);
@@ -241,23 +251,37 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
         for (int j = 0; j < 8; ++j) o[j] = fmaf(ka[j], g[j], fmaf(kb[j], f[j], kc[j]));
         *(reinterpret_cast<uint4*>(dx + p * dx_ctot + dx_coff) + c8) = pack8(o, dtype);
     };
-    auto ld = [&](const uint16_t* t, int ctot, int coff, size_t i) {
-        return __ldg(reinterpret_cast<const uint4*>(t + (i / C8) * ctot + coff) + (i % C8));
+    auto ld = [&](const uint16_t* t, int ctot, int coff, size_t p, int c8) {
+        return __ldg(reinterpret_cast<const uint4*>(t + p * ctot + coff) + c8);
     };
-    for (; idx + stride < total; idx += 2 * stride) {
-        uint4 vx[2], vg[2], vy[2];
+    if (FIXED) {     // fixed channel group, constant pixel step: no division in the loop (see bn_apply_kernel)
+        const int c8 = threadIdx.x % C8;
+        const size_t pstep = stride / C8;
+        size_t p = idx / C8;
+        coeff(c8);
+        for (; p + 3 * pstep < npix; p += 4 * pstep) {       // 8..12 independent 16-byte loads in flight per thread
+            uint4 vx[4], vg[4], vy[4];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            const size_t i = idx + u * stride;
-            vx[u] = ld(x, x_ctot, x_coff, i);
-            vg[u] = ld(dy, dy_ctot, dy_coff, i);
-            vy[u] = y ? ld(y, y_ctot, y_coff, i) : make_uint4(0, 0, 0, 0);
+            for (int u = 0; u < 4; ++u) {
+                const size_t q = p + u * pstep;
+                vx[u] = ld(x, x_ctot, x_coff, q, c8);
+                vg[u] = ld(dy, dy_ctot, dy_coff, q, c8);
+                vy[u] = y ? ld(y, y_ctot, y_coff, q, c8) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) one(p + u * pstep, c8, vx[u], vg[u], vy[u]);
         }
-        one(idx, vx[0], vg[0], vy[0]);
-        one(idx + stride, vx[1], vg[1], vy[1]);
+        for (; p < npix; p += pstep)
+            one(p, c8, ld(x, x_ctot, x_coff, p, c8), ld(dy, dy_ctot, dy_coff, p, c8),
+                y ? ld(y, y_ctot, y_coff, p, c8) : make_uint4(0, 0, 0, 0));
+    } else {
+        for (; idx < total; idx += stride) {
+            const size_t p = idx / C8;
+            const int c8 = (int)(idx % C8);
+            one(p, c8, ld(x, x_ctot, x_coff, p, c8), ld(dy, dy_ctot, dy_coff, p, c8),
+                y ? ld(y, y_ctot, y_coff, p, c8) : make_uint4(0, 0, 0, 0));
+        }
     }
-    for (; idx < total; idx += stride)
-        one(idx, ld(x, x_ctot, x_coff, idx), ld(dy, dy_ctot, dy_coff, idx), y ? ld(y, y_ctot, y_coff, idx) : make_uint4(0, 0, 0, 0));
 }
 
 // dst += src (gradient accumulation over the consumers of an activation)
@@ -339,7 +363,7 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
         mean, invstd, npix, C8, sums, dtype, gamma, y_relu ? nullptr : relu_beta);
     VU_CHECK_LAUNCH("bn_bwd_reduce");
-    const int grid = tr_grid(npix * C8, 256 * 2, 16);
+    const int grid = tr_grid(npix * C8, 256 * 4, 16);
     if (256 % C8 == 0)
         bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,

@@ -184,6 +184,67 @@ bilinear_bwd_kernel(const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff, u
     }
 }
 
+// Fast path for the x2 upsamples of the model (scale >= 0.4). The destination rows / columns whose footprint contains a
+// source pixel are CONSECUTIVE and at most kBilTaps = 5 (d*scale in (s-1, s+1): an interval of length 2/scale <= 5), so the
+// taps are d0 .. d0+4 with d0 the first non-zero weight (same fp32 index arithmetic as the forward kernel); zero rows are
+// skipped, the five column loads of a row are issued together.
+constexpr int kBilTaps = 5;
+__device__ __forceinline__ int lerp_taps(int s, float scale, int in_size, int out_size, float (&w)[kBilTaps]) {
+    int lo, hi;
+    dst_range(s, scale, out_size, lo, hi);
+    int d0 = lo;
+    while (d0 < hi && lerp_weight(d0, s, scale, in_size) == 0.f) ++d0;
+#pragma unroll
+    for (int k = 0; k < kBilTaps; ++k) w[k] = (d0 + k <= hi) ? lerp_weight(d0 + k, s, scale, in_size) : 0.f;
+    return d0;
+}
+
+template <typename I>
+__global__ void __launch_bounds__(256)
+bilinear_bwd_taps_kernel(const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff, uint16_t* __restrict__ dx, int dx_ctot,
+                         int dx_coff, int N, int Hs, int Ws, int Ho, int Wo, int C8, float sh, float sw, int accumulate,
+                         int dtype) {
+    const I total = (I)N * Hs * Ws * C8;
+    for (I idx = blockIdx.x * (I)blockDim.x + threadIdx.x; idx < total; idx += (I)gridDim.x * blockDim.x) {
+        const int c8 = idx % C8;
+        const int ws = (idx / C8) % Ws;
+        const int hs = (idx / ((I)C8 * Ws)) % Hs;
+        const int n = idx / ((I)C8 * Ws * Hs);
+        float rw[kBilTaps], cw[kBilTaps];
+        const int r0 = lerp_taps(hs, sh, Hs, Ho, rw);
+        const int c0 = lerp_taps(ws, sw, Ws, Wo, cw);
+        const uint16_t* base = dy + ((size_t)n * Ho * Wo + c0) * dy_ctot + dy_coff + c8 * 8;
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < kBilTaps; ++i) {
+            if (rw[i] == 0.f) continue;
+            const uint16_t* row = base + (size_t)(r0 + i) * Wo * dy_ctot;
+            uint4 v[kBilTaps];
+#pragma unroll
+            for (int k = 0; k < kBilTaps; ++k)
+                v[k] = (cw[k] != 0.f) ? __ldg(reinterpret_cast<const uint4*>(row + (size_t)k * dy_ctot)) : make_uint4(0, 0, 0, 0);
+            float t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < kBilTaps; ++k) {
+                float g[8];
+                unpack8(v[k], g, dtype);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) t[q] = fmaf(cw[k], g[q], t[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] = fmaf(rw[i], t[q], acc[q]);
+        }
+        uint4* dp = reinterpret_cast<uint4*>(dx + (((size_t)n * Hs + hs) * Ws + ws) * dx_ctot + dx_coff) + c8;
+        if (accumulate) {
+            float o[8];
+            unpack8(*dp, o, dtype);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] += o[q];
+        }
+        *dp = pack8(acc, dtype);
+    }
+}
+
 __global__ void __launch_bounds__(256)
 resize_map_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int N, int Hs, int Ws, int Ho, int Wo,
                       float sh, float sw) {
@@ -353,9 +414,15 @@ extern "C" int vu_bilinear_ac_bwd(const void* dy, void* dx, int N, int Hs, int W
     VU_TB_ALIGN((C | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "bilinear_bwd");
     const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
     const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
-    bilinear_bwd_kernel<<<tb_grid((size_t)N * Hs * Ws * (C / 8)), 256, 0, (cudaStream_t)st>>>(
-        (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, C / 8, sh, sw, accumulate,
-        dtype);
+    // a source pixel is touched by at most 2/scale + 1 destination rows: the unrolled kernel covers the x2 upsamples
+    if (sh >= 0.4f && sw >= 0.4f && (size_t)N * Hs * Ws * (C / 8) < (1ull << 31))
+        bilinear_bwd_taps_kernel<uint32_t><<<tb_grid((size_t)N * Hs * Ws * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, C / 8, sh, sw, accumulate,
+            dtype);
+    else
+        bilinear_bwd_kernel<<<tb_grid((size_t)N * Hs * Ws * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, C / 8, sh, sw, accumulate,
+            dtype);
     VU_CHECK_LAUNCH("bilinear_bwd");
     return 0;
 }
