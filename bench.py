@@ -419,7 +419,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": "patches/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": B * 3 * PATCH * PATCH * 4, "d2h_bytes_per_step": 3 * B * PATCH * PATCH * 4},
         "gpu_launches": launches,
-        "roofline": {"bound": "tensor", "kernel": "conv_igemm_kernel<BN> (tcgen05 implicit GEMM, all conv layers)",
+        "roofline": {"bound": "tensor", "kernel": "conv_igemm_pair_kernel<BN> / conv_igemm_kernel<BN> / conv3x3_halo_kernel (tcgen05 implicit GEMM, all conv layers)",
                      "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained,
                      "peak_source": f"{src} bf16_tflops_sustained (kernel timed inside a long step); burst {burst}",
                      "launches_per_step": n_conv // 2, "conv_ms_per_step": conv_ms / 2,

@@ -314,7 +314,9 @@ int vu_vec_layer_fwd(const float* z, const float* w, const float* b, int M, int 
                      float* running_var, int relu, float* y_raw, float* y, float* mean, float* invstd, vu_stream_t stream);
 int vu_vec_layer_bwd(const float* dy, const float* z, const float* w, const float* y_raw, const float* y, int M, int L,
                      int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dz /* += */,
-                     float* dw /* += */, float* db /* += */, float* dgamma /* += */, float* dbeta /* += */, vu_stream_t stream);
+                     float* dw /* += */, float* db /* += */, float* dgamma /* += */, float* dbeta /* += */,
+                     float* scratch /* M*C floats, required when dz != NULL: gradient w.r.t. the pre-BN output */,
+                     vu_stream_t stream);
 /* z = mu + eps*exp(.5 logvar)*T: dmu += sum_s dz, dlogvar += sum_s dz*eps*.5*exp(.5 logvar)*T. */
 int vu_reparam_bwd(const float* dz, const float* eps, const float* logvar, float temperature, float* dmu,
                    float* dlogvar, size_t n_per_sample, int num_samples, vu_stream_t stream);

@@ -95,7 +95,7 @@ SIGNATURES = {
     "vu_map_bn_sigmoid_bwd": [p, p, p, p, p, sz, p, p, p, p, p],
     "vu_map_sum": [p, sz, p, p],
     "vu_vec_layer_fwd": [p, p, p, i, i, i, p, p, f, f, C.c_double, p, p, i, p, p, p, p, p],
-    "vu_vec_layer_bwd": [p, p, p, p, p, i, i, i, p, p, p, i, p, p, p, p, p, p],
+    "vu_vec_layer_bwd": [p, p, p, p, p, i, i, i, p, p, p, i, p, p, p, p, p, p, p],
     "vu_reparam_bwd": [p, p, p, f, p, p, sz, i, p],
     "vu_im2col_small_cin": [p, p, i, i, i, i, i, i, i, i, i, p],
     "vu_pack_rows_padded": [p, p, i, i, i, i, p],

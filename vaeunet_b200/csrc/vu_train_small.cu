@@ -169,10 +169,16 @@ __global__ void __launch_bounds__(256)
 vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ y_raw,
                      const float* __restrict__ y, int M, int L, int C, const float* __restrict__ gamma,
                      const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ dw,
-                     float* __restrict__ db, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+                     float* __restrict__ db, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     float* __restrict__ dy_raw_out) {
     __shared__ float s_d[kVecM][33];
     const int c0 = blockIdx.x * 32;
     vec_dy_raw_tile(s_d, c0, dy, y_raw, y, M, C, gamma, mean, invstd, relu, true, db, dgamma, dbeta);
+    if (dy_raw_out != nullptr)                 // [M][C] for the input-gradient kernel
+        for (int i = threadIdx.x; i < M * 32; i += 256) {
+            const int m = i / 32, cl = i % 32;
+            if (c0 + cl < C) dy_raw_out[(size_t)m * C + c0 + cl] = s_d[m][cl];
+        }
     if (dw != nullptr)
         for (int i = threadIdx.x; i < 32 * L; i += 256) {
             const int cl = i / L, l = i % L, c = c0 + cl;
@@ -183,36 +189,28 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
         }
 }
 
-// dz[m,l] += sum_c dy_raw[m,c] w[c,l]. One block per 32 columns l; it walks the channels in a fixed order (dy_raw tiles are
-// recomputed per block: M*C values), so the input gradient is bit-reproducible from run to run - it feeds the BatchNorm
-// backward of the 2x2 / 4x4 encoder maps, which amplifies fp32 atomics-order noise by orders of magnitude.
+// dz[m,l] += sum_c dy_raw[m,c] w[c,l] from the [M][C] pre-BN gradient the kernel above wrote. One block per 32 columns l,
+// channels walked in a fixed order (no atomics): the input gradient is bit-reproducible from run to run - it feeds the
+// BatchNorm backward of the 2x2 / 4x4 encoder maps, which amplifies fp32 atomics-order noise by orders of magnitude.
 __global__ void __launch_bounds__(256)
-vec_layer_dz_kernel(const float* __restrict__ dy, const float* __restrict__ w, const float* __restrict__ y_raw,
-                    const float* __restrict__ y, int M, int L, int C, const float* __restrict__ gamma,
-                    const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ dz) {
-    __shared__ float s_d[kVecM][33];
+vec_layer_dz_kernel(const float* __restrict__ dy_raw, const float* __restrict__ w, int M, int L, int C,
+                    float* __restrict__ dz) {
     const int ll = threadIdx.x % 32, mg = threadIdx.x / 32;     // thread: column l, rows mg, mg + 8, ...
     const int l = blockIdx.x * 32 + ll;
+    if (l >= L) return;
     float acc[kVecM / 8];
 #pragma unroll
     for (int j = 0; j < kVecM / 8; ++j) acc[j] = 0.f;
-    for (int c0 = 0; c0 < C; c0 += 32) {
-        vec_dy_raw_tile(s_d, c0, dy, y_raw, y, M, C, gamma, mean, invstd, relu, false, nullptr, nullptr, nullptr);
-        if (l < L) {
-            const int nc = min(32, C - c0);
-            for (int cl = 0; cl < nc; ++cl) {
-                const float wv = __ldg(w + (size_t)(c0 + cl) * L + l);
-#pragma unroll
-                for (int j = 0; j < kVecM / 8; ++j)
-                    if (mg + 8 * j < M) acc[j] = fmaf(s_d[mg + 8 * j][cl], wv, acc[j]);
-            }
-        }
-        __syncthreads();                                        // the next tile overwrites s_d
-    }
-    if (l < L)
+#pragma unroll 4
+    for (int c = 0; c < C; ++c) {
+        const float wv = __ldg(w + (size_t)c * L + l);
 #pragma unroll
         for (int j = 0; j < kVecM / 8; ++j)
-            if (mg + 8 * j < M) dz[(size_t)(mg + 8 * j) * L + l] += acc[j];
+            if (mg + 8 * j < M) acc[j] = fmaf(__ldg(dy_raw + (size_t)(mg + 8 * j) * C + c), wv, acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < kVecM / 8; ++j)
+        if (mg + 8 * j < M) dz[(size_t)(mg + 8 * j) * L + l] += acc[j];
 }
 
 // z = mu + eps * exp(.5 lv) * T  ->  dmu += dz (summed over samples), dlv += dz * eps * .5 * exp(.5 lv) * T
@@ -358,13 +356,14 @@ extern "C" int vu_vec_layer_fwd(const float* z, const float* w, const float* b, 
 
 extern "C" int vu_vec_layer_bwd(const float* dy, const float* z, const float* w, const float* y_raw, const float* y, int M,
                                 int L, int C, const float* gamma, const float* mean, const float* invstd, int relu, float* dz,
-                                float* dw, float* db, float* dgamma, float* dbeta, vu_stream_t st) {
+                                float* dw, float* db, float* dgamma, float* dbeta, float* scratch, vu_stream_t st) {
     if (!dy || !z || !w || !y_raw || !y || M < 1 || M > kVecM) return set_error(VU_ERR_INVALID, "vec_layer_bwd: bad args (M <= 64)");
+    if (dz && !scratch) return set_error(VU_ERR_INVALID, "vec_layer_bwd: dz needs the M*C scratch buffer");
     vec_layer_bwd_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, z, y_raw, y, M, L, C, gamma, mean, invstd, relu, dw,
-                                                                      db, dgamma, dbeta);
+                                                                      db, dgamma, dbeta, dz ? scratch : nullptr);
     VU_CHECK_LAUNCH("vec_layer_bwd");
     if (dz != nullptr) {
-        vec_layer_dz_kernel<<<(L + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, w, y_raw, y, M, L, C, gamma, mean, invstd, relu, dz);
+        vec_layer_dz_kernel<<<(L + 31) / 32, 256, 0, (cudaStream_t)st>>>(scratch, w, M, L, C, dz);
         VU_CHECK_LAUNCH("vec_layer_dz");
     }
     return 0;

@@ -247,7 +247,9 @@ def vec_layer_bwd(dy, saved, w, gamma, relu: bool, dz: Optional[torch.Tensor], w
     assert dw.numel() == Cc * L and dw.is_contiguous()
     check(load().vu_vec_layer_bwd(_f32(dy.contiguous()).data_ptr(), z.data_ptr(), _f32(w).data_ptr(), y_raw.data_ptr(),
                                   y.data_ptr(), M, L, Cc, _ptr(gamma), _ptr(mean), _ptr(invstd), int(relu), _ptr(dz),
-                                  dw.data_ptr(), _ptr(db), _ptr(dg), _ptr(dbeta), _stream()), "vu_vec_layer_bwd")
+                                  dw.data_ptr(), _ptr(db), _ptr(dg), _ptr(dbeta),
+                                  torch.empty(M * Cc, dtype=torch.float32, device=dev).data_ptr() if dz is not None else None,
+                                  _stream()), "vu_vec_layer_bwd")
     _count(2 if dz is not None else 1)
     return dw, db, dg, dbeta
 
