@@ -522,6 +522,54 @@ def threshold_metrics(pred: Tensor, target: Tensor, epsilon: float = 1e-6) -> Di
             "accuracy": ((p == t).float().sum() / p.numel()).item()}
 
 
+def evaluate_metrics(sd: SD, cfg: ResNetCfg, batches: Sequence[Tuple[Tensor, Tensor]], eps: Sequence[Tensor],
+                     max_samples: Optional[int] = None):
+    """evaluate.evaluate, evaluate.py:19-101 (tensor part): eval-mode forward of every (images, masks) batch (the VAE forward
+    samples z, unet_resnet.py:211-213: eps[i] is the draw of batch i), `get_all_metrics` on the RAW logits (:76, the
+    threshold-logits-at-0.5 quirk), metrics summed and divided by the number of batches (:97), capped by max_samples
+    (:27-28,33-34). Predictions of another size than the masks are resized with align_corners=False (:67-73).
+    -> (metrics_avg, [sigmoid(logits) of the batches whose samples the reference keeps for plotting, :79-88])."""
+    n = len(batches)
+    if max_samples is not None and max_samples < n:
+        n = max_samples
+    sums: Dict[str, float] = {}
+    kept = []
+    for i, (images, masks) in enumerate(batches):
+        if i >= n:
+            break
+        logits, _, _ = unetresnet_forward(sd, cfg, images, eps[i])      # normalize() has mean 0 / std 1: identity (:15-16)
+        if logits.shape != masks.shape:
+            logits = F.interpolate(logits, size=masks.shape[2:], mode="bilinear", align_corners=False)
+        m = threshold_metrics(logits, masks)
+        if len(kept) < 4:
+            kept.append(torch.sigmoid(logits))
+        for k, v in m.items():
+            sums[k] = sums.get(k, 0) + v
+    return {k: v / n for k, v in sums.items()}, kept
+
+
+def generate_ensemble_prediction(sd: SD, cfg: ResNetCfg, image: Tensor, temps: Sequence[float], samples_per_temp: int,
+                                 eps: Tensor, weighted: bool = True, patch_size: int = 512, overlap: int = 100) -> Tensor:
+    """visualize_vae.generate_ensemble_prediction, visualize_vae.py:1083-1163: weights 1/(|T-1|+0.5) (or 1), normalised
+    (:1098-1109); per temperature the mean over samples_per_temp tile-blended probability maps of
+    z = mu + eps*exp(.5 logvar)*T (:1131-1152, mu/logvar of the WHOLE image, :1122-1123), weighted sum over temperatures
+    (:1155). eps [len(temps)*samples_per_temp, B, L] in the order the reference draws them (temperature-major)."""
+    w = torch.tensor([1.0 / (abs(t - 1.0) + 0.5) if weighted else 1.0 for t in temps])
+    w = w / w.sum()
+    mu, logvar = unetresnet_encode(sd, image)
+    should_sample = cfg.latent_injection != "none"                        # :1112
+    out = torch.zeros(1, 1, image.shape[2], image.shape[3])
+    k = 0
+    for ti, t in enumerate(temps):
+        acc = torch.zeros_like(out)
+        for _ in range(samples_per_temp):
+            z = mu + eps[k] * (torch.exp(0.5 * logvar) * t) if should_sample else mu
+            k += 1
+            acc += predict_with_patches(sd, cfg, image, z, patch_size, overlap)
+        out += acc / samples_per_temp * w[ti]
+    return out
+
+
 # --------------------------------------------------------------------------------------
 # losses (utils/loss.py)
 # --------------------------------------------------------------------------------------

@@ -187,6 +187,46 @@ def test_predict_paths(model, cuda_dev):
     assert rel(um["mean"], um_r["mean"]) < tol
 
 
+def test_evaluate_validation_pass(model, cuda_dev):
+    """evaluate.evaluate (evaluate.py:19-101) - same averaged metrics as the oracle restatement (pinned to
+    the unmodified reference by tests/test_oracle_golden.py::test_evaluate), incl. max_samples and dict batches."""
+    from vaeunet_b200.evaluate import evaluate
+    m, sd = model
+    seeds = [900, 901, 902]
+    batches = [synthetic_fundus(2, 64, 80, seed=s) for s in seeds]
+    g = torch.Generator().manual_seed(77)
+    eps = [torch.randn(2, 32, generator=g) for _ in seeds]
+    ref, kept = O.evaluate_metrics(sd, CFG, batches, eps)
+    got, samples = evaluate(m, batches, cuda_dev, amp=False, eps=eps)
+    report(f"evaluate {m.dt_name}: " + " ".join(f"{k} {got[k]:.5f}/{ref[k]:.5f}" for k in ref))
+    for k, v in ref.items():
+        assert abs(got[k] - v) <= 2e-2 * max(abs(v), 1e-3), (k, got[k], v)       # thresholded counts: pixels near logit 0.5 flip
+    assert len(samples) == 4 and samples[0][1].shape == (1, 64, 80)
+    assert abs(float(samples[0][1].mean()) - kept[0][0].mean().item()) < 5e-3
+    ref2, _ = O.evaluate_metrics(sd, CFG, batches, eps, max_samples=2)
+    got2, _ = evaluate(m, [dict(image=a, mask=b) for a, b in batches], cuda_dev, amp=False, max_samples=2, eps=eps)
+    for k, v in ref2.items():
+        assert abs(got2[k] - v) <= 2e-2 * max(abs(v), 1e-3), (k, got2[k], v)
+
+
+def test_temperature_ensemble(model, cuda_dev):
+    """visualize_vae.generate_ensemble_prediction (:1083-1163) - all (T, sample) draws in one tiled sweep."""
+    from vaeunet_b200 import predict as P
+    m, sd = model
+    x, _ = synthetic_fundus(1, 100, 120, seed=910)
+    temps = [0.5, 1.0, 2.5]
+    eps = torch.randn(6, 1, 32, generator=torch.Generator().manual_seed(12))
+    tol = TOLS[m.dt_name]["out"]
+    for weighted in (True, False):
+        ref = O.generate_ensemble_prediction(sd, CFG, x, temps, 2, eps, weighted, 64, 16)
+        got = P.generate_ensemble_prediction(m, x.to(cuda_dev), temps, 2, weighted, 64, 16, 4, eps=eps.to(cuda_dev))
+        assert got.shape == ref.shape == (1, 1, 100, 120)
+        report(f"ensemble {m.dt_name} weighted={weighted}: rel={rel(got, ref):.5f} maxabs={(got.cpu() - ref).abs().max().item():.5f}")
+        assert rel(got, ref) < tol and (got.cpu() - ref).abs().max() < 2 * tol
+    w = P.ensemble_weights(temps, True)
+    assert abs(w.sum().item() - 1.0) < 1e-6 and w[1] > w[0] > w[2]
+
+
 # The injection-mode and basic-UNet fixtures are fully seeded-random networks (no fitted output stage):
 # they amplify rounding noise ~10x more than fixture_resnet -> TOLS[dt]["random"].
 _TDT = {"bf16": torch.bfloat16, "f16": torch.float16}

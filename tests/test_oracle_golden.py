@@ -191,3 +191,34 @@ def test_losses_metrics_misc():
         assert torch.allclose(um[k], U[k], rtol=1e-5, atol=1e-6), k
     S = g["sample"]
     assert torch.allclose(O.sample_from_latent(K["mu"], K["lv"], 1.7, S["eps"]), S["z"], rtol=1e-6, atol=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# evaluate() and the temperature ensemble, pinned by tests/golden/make_golden_next.py
+# ---------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def gold_next():
+    return torch.load(G / "golden_next.pt", map_location="cpu", weights_only=False)
+
+
+def test_evaluate(gold_next, sd):
+    g = gold_next["evaluate"]
+    B, H, W = g["shape"]
+    batches = [synthetic_fundus(B, H, W, seed=s) for s in g["seeds"]]
+    avg, kept = O.evaluate_metrics(sd, CFG, batches, g["eps"])
+    for k, v in g["avg"].items():
+        assert abs(avg[k] - v) <= 1e-6 * max(1.0, abs(v)), (k, avg[k], v)
+    avg2, _ = O.evaluate_metrics(sd, CFG, batches, g["eps"], max_samples=2)
+    for k, v in g["avg_max2"].items():
+        assert abs(avg2[k] - v) <= 1e-6 * max(1.0, abs(v)), (k, avg2[k], v)
+    assert (kept[0][0] - g["sample0_pred"]).abs().max() < 1e-5
+
+
+def test_temperature_ensemble(gold_next, sd):
+    g = gold_next["ensemble"]
+    H, W = g["shape"]
+    x, _ = synthetic_fundus(1, H, W, seed=g["seed"])
+    out = O.generate_ensemble_prediction(sd, CFG, x, g["temps"], g["samples_per_temp"], g["eps"], True, g["patch"], g["overlap"])
+    assert (out - g["out"]).abs().max() < 1e-5
+    out_u = O.generate_ensemble_prediction(sd, CFG, x, g["temps"], g["samples_per_temp"], g["eps"], False, g["patch"], g["overlap"])
+    assert (out_u - g["out_unweighted"]).abs().max() < 1e-5

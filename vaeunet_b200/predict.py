@@ -9,7 +9,7 @@ the encoder ONCE per tile batch and decodes all N samples as one batched pass)."
 from __future__ import annotations
 
 import math
-from typing import Dict, Optional
+from typing import Sequence, Dict, Optional
 
 import torch
 
@@ -150,3 +150,35 @@ def segmentation_distribution(model, img, num_samples=32, patch_size=None, overl
             segs = ops.resize_logits(lg.reshape(num_samples, lg.shape[2], lg.shape[3]), img.shape[2], img.shape[3],
                                      ops.SIG_POST)
     return segs.unsqueeze(1), mu, logvar
+
+
+def ensemble_weights(temps: Sequence[float], weighted: bool = True) -> torch.Tensor:
+    """visualize_vae.py:1098-1109: 1 / (|T - 1| + 0.5) per temperature (or 1), normalised to sum 1."""
+    w = torch.tensor([1.0 / (abs(float(t) - 1.0) + 0.5) if weighted else 1.0 for t in temps], dtype=torch.float32)
+    return w / w.sum()
+
+
+def generate_ensemble_prediction(model, image, temps=(0.5, 1.0, 2.0, 3.0), samples_per_temp=5, weighted=True, patch_size=512,
+                                 overlap=100, batch_size=4, eps: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """visualize_vae.generate_ensemble_prediction (visualize_vae.py:1083-1163): temperature-weighted mean of tile-blended
+    probability maps, samples_per_temp draws z = mu + eps*exp(.5 logvar)*T per temperature. -> [1,1,H,W].
+
+    The reference re-encodes the image per temperature and runs len(temps)*samples_per_temp sequential tiled predictions, each
+    re-running the encoder on every tile. Here mu/logvar are computed once and ALL draws go through one tiled sweep
+    (`blended_samples`): the encoder runs once per tile and the decodes of every (T, sample) pair share its features.
+    eps (additive): [len(temps)*samples_per_temp, 1, L], temperature-major (the reference's draw order)."""
+    model.eval()
+    T, S = len(temps), int(samples_per_temp)
+    with torch.no_grad():
+        mu, logvar = model.encode(image)
+        if getattr(model, "latent_injection", "all") != "none":                       # :1112
+            if eps is None:
+                eps = torch.randn(T * S, *mu.shape, device=mu.device)
+            eps = eps.float().contiguous().to(mu.device)
+            z = torch.cat([ops.reparameterize(mu, logvar, eps[t * S:(t + 1) * S].contiguous(), float(temps[t]))
+                           for t in range(T)])                                        # [T*S, 1, L]
+        else:
+            z = mu.unsqueeze(0).expand(T * S, -1, -1).contiguous()
+        segs = blended_samples(model, image, z[:, 0].contiguous(), patch_size, overlap, batch_size)     # [T*S, H, W]
+        w = (ensemble_weights(temps, weighted) / S).to(segs.device).repeat_interleave(S)                # weight of every draw
+        return (segs * w.view(-1, 1, 1)).sum(0)[None, None]
