@@ -106,10 +106,17 @@ decoder_concat_kernel(const CatParams p, int segs_per_row, uint32_t num_segs, in
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t HW = (uint32_t)p.H * p.W;
     for (uint32_t seg = blockIdx.x; seg < num_segs; seg += gridDim.x) {
-        const uint32_t row = seg / segs_per_row;                 // = d * H + ho
-        const int wseg = seg - row * segs_per_row;
-        const uint32_t d = row / p.H;
-        const int ho = row - d * p.H;
+        // seg enumerates (patch, ho, 64-pixel segment, sample): the `rep` decodes of one patch take the same skip / x1 rows,
+        // so they are adjacent in the grid-stride order and those rows are read from DRAM once, not once per decode
+        // (ncu at 160 decodes: 1.61 GB read for 0.70 GB of distinct inputs with the decode-major order)
+        const uint32_t r = seg % (uint32_t)p.rep;
+        const uint32_t q = seg / (uint32_t)p.rep;
+        const uint32_t prow = q / segs_per_row;                  // = patch * H + ho
+        const int wseg = q - prow * segs_per_row;
+        const uint32_t pb = prow / p.H;
+        const int ho = prow - pb * p.H;
+        const uint32_t d = pb * p.rep + r;
+        const uint32_t row = d * p.H + ho;
         const int wo0 = (wseg * kCatWarps + warp) * kCatPix;
         if (wo0 >= p.W) continue;                                // warp-uniform
         const int npx = min(kCatPix, p.W - wo0);
