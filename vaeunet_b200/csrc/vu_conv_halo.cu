@@ -39,12 +39,15 @@ struct HaloParams {
     double* stat_sums;                                        // optional [2*BN] fp64 sum / sum of squares of the stored outputs
 };
 
-template <int BN, int HT> struct HaloCfg {
+// PAIR: cluster of two CTAs, tcgen05 cta_group::2 - each CTA stages its own pixel tile and HALF of the filter rows of a tap;
+// the leader's M = 256 MMA reads both (see conv_igemm_pair_kernel). Per MMA an SM then reads 4 KB + BN*16 B of smem operands
+// instead of 4 KB + BN*32 B: the Cout = 64 layers are bound by that read port.
+template <int BN, int HT, bool PAIR = false> struct HaloCfg {
     static constexpr int kARows = (HT + 2) * kHaloPitch;
     static constexpr int kABytes = kARows * 128;                       // what one TMA box delivers
     static constexpr int kAStride = (kABytes + 1023) / 1024 * 1024;   // stage pitch (1024-aligned: swizzle atom)
     static constexpr int kAStages = 2;
-    static constexpr int kBBytes = BN * 128;
+    static constexpr int kBBytes = (PAIR ? BN / 2 : BN) * 128;
     static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
@@ -53,11 +56,11 @@ template <int BN, int HT> struct HaloCfg {
     static_assert(kSmemBytes <= 232448, "smem budget");
 };
 
-template <int BN, int HT>
+template <int BN, int HT, bool PAIR>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                     const HaloParams p) {
-    using Cfg = HaloCfg<BN, HT>;
+    using Cfg = HaloCfg<BN, HT, PAIR>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -83,18 +86,25 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    // PAIR: work items are pairs of tiles (2t, 2t+1); full barriers live in the leader (rank 0) and take both producers,
+    // empty / accumulator-full barriers are per CTA (multicast commit), accumulator-empty lives in the leader
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    const int item0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int item_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int num_items = PAIR ? (p.num_tiles + 1) / 2 : p.num_tiles;
+    auto tile_of = [&](int item) { return PAIR ? 2 * item + (int)rank : item; };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_x);
         tma_prefetch_desc(&map_w);
-        for (int s = 0; s < Cfg::kAStages; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
-        for (int s = 0; s < Cfg::kBStages; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(t_full(a), 1); mbar_init(t_empty(a), 128); }
+        for (int s = 0; s < Cfg::kAStages; ++s) { mbar_init(a_full(s), PAIR ? 2 : 1); mbar_init(a_empty(s), 1); }
+        for (int s = 0; s < Cfg::kBStages; ++s) { mbar_init(b_full(s), PAIR ? 2 : 1); mbar_init(b_empty(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(t_full(a), 1); mbar_init(t_empty(a), PAIR ? 256 : 128); }
         fence_barrier_init();
     }
     if (warp == 1) {
-        tmem_alloc<Cfg::kTmemCols>(tmem_slot);
-        tmem_relinquish();
+        if constexpr (PAIR) { tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot); tmem_relinquish_pair(); }
+        else { tmem_alloc<Cfg::kTmemCols>(tmem_slot); tmem_relinquish(); }
     }
     for (int c = threadIdx.x; c < BN; c += kHaloThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
@@ -103,7 +113,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -111,7 +121,9 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // ===================== A producer: one halo'd input tile per (tile, K block) =====================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            const uint32_t leader_a_full0 = PAIR ? mapa_cluster(a_full(0), 0) : 0u;
+            for (int item = item0; item < num_items; item += item_step) {
+                const int tile = tile_of(item);               // PAIR: may be one past the end (loads are zero fill)
                 const int wb = tile % p.tiles_w;
                 const int hb = (tile / p.tiles_w) % p.tiles_h;
                 const int nb = tile / (p.tiles_w * p.tiles_h);
@@ -119,12 +131,19 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     const int s = it % Cfg::kAStages;
                     const uint32_t ph = (it / Cfg::kAStages) & 1;
                     mbar_wait(a_empty(s), ph ^ 1);
-                    mbar_arrive_expect_tx(a_full(s), Cfg::kABytes);
+                    if (!PAIR) mbar_arrive_expect_tx(a_full(s), Cfg::kABytes);
+                    else if (rank == 0) mbar_arrive_expect_tx(a_full(s), 2 * Cfg::kABytes);
+                    else mbar_arrive_cluster(leader_a_full0 + 8u * s);
                     // one TMA op per tile row: several ops in flight fill the tile ~4x faster than one big box
 #pragma unroll
-                    for (int i = 0; i < HT + 2; ++i)
-                        tma_load_4d(a_base + s * Cfg::kAStride + i * (kHaloPitch * 128), &map_x, a_full(s), kb * 64,
-                                    wb * kHaloWT - 1, hb * HT - 1 + i, nb);
+                    for (int i = 0; i < HT + 2; ++i) {
+                        if constexpr (PAIR)
+                            tma_load_4d_pair(a_base + s * Cfg::kAStride + i * (kHaloPitch * 128), &map_x, a_full(s), kb * 64,
+                                             wb * kHaloWT - 1, hb * HT - 1 + i, nb);
+                        else
+                            tma_load_4d(a_base + s * Cfg::kAStride + i * (kHaloPitch * 128), &map_x, a_full(s), kb * 64,
+                                        wb * kHaloWT - 1, hb * HT - 1 + i, nb);
+                    }
                 }
             }
         }
@@ -132,25 +151,38 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         // ===================== B producer: one [BN x 64ch] filter tap per stage =====================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            const uint32_t leader_b_full0 = PAIR ? mapa_cluster(b_full(0), 0) : 0u;
+            for (int item = item0; item < num_items; item += item_step) {
                 for (int kb = 0; kb < p.kblocks; ++kb) {
                     for (int tap = 0; tap < 9; ++tap, ++it) {
                         const int s = it % Cfg::kBStages;
                         const uint32_t ph = (it / Cfg::kBStages) & 1;
                         mbar_wait(b_empty(s), ph ^ 1);
-                        mbar_arrive_expect_tx(b_full(s), Cfg::kBBytes);
-                        tma_load_3d(b_base + s * Cfg::kBBytes, &map_w, b_full(s), kb * 64, tap, 0);
+                        if constexpr (PAIR) {
+                            if (rank == 0) mbar_arrive_expect_tx(b_full(s), 2 * Cfg::kBBytes);
+                            else mbar_arrive_cluster(leader_b_full0 + 8u * s);
+                            tma_load_3d_pair(b_base + s * Cfg::kBBytes, &map_w, b_full(s), kb * 64, tap, (int)rank * (BN / 2));
+                        } else {
+                            mbar_arrive_expect_tx(b_full(s), Cfg::kBBytes);
+                            tma_load_3d(b_base + s * Cfg::kBBytes, &map_w, b_full(s), kb * 64, tap, 0);
+                        }
                     }
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 && (!PAIR || rank == 0)) {
         // ===================== MMA issuer: the whole warp walks the pipeline, one elected lane issues =====
         // (issuing under elect.sync instead of `lane == 0` lets ptxas emit bare UTCHMMA without a per-MMA
         //  uniform-branch loop; the tap loop is unrolled so descriptor offsets are immediates)
-        const uint32_t idesc = umma_idesc_f16(128, BN, p.dtype == 0 ? 1u : 0u);
+        const uint32_t idesc = umma_idesc_f16(PAIR ? 256 : 128, BN, p.dtype == 0 ? 1u : 0u);
+        auto mma = [&](uint32_t d, uint64_t a, uint64_t b, uint32_t acc_flag) {
+            if constexpr (PAIR) umma_f16_ss_pair(d, a, b, idesc, acc_flag); else umma_f16_ss(d, a, b, idesc, acc_flag);
+        };
+        auto commit = [&](uint32_t bar) {
+            if constexpr (PAIR) umma_commit_pair(bar, 3); else umma_commit(bar);
+        };
         uint32_t ita = 0, itb = 0, tcount = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+        for (int item = item0; item < num_items; item += item_step, ++tcount) {
             const int acc = tcount & 1;
             const uint32_t accph = (tcount >> 1) & 1;
             mbar_wait(t_empty(acc), accph ^ 1);
@@ -177,25 +209,25 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                             for (int k = 0; k < 4; ++k)
 #pragma unroll
                                 for (int j = 0; j < HT; ++j)
-                                    umma_f16_ss(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
-                                                bdesc + 2u * k, idesc, (kb | tap | k) != 0);
+                                    mma(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
+                                        bdesc + 2u * k, (kb | tap | k) != 0);
                         } else {
                             for (int k = 0; k < nk; ++k)
 #pragma unroll
                                 for (int j = 0; j < HT; ++j)
-                                    umma_f16_ss(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
-                                                bdesc + 2u * k, idesc, (kb | tap | k) != 0);
+                                    mma(tmem_d + j * BN, a0 + (uint32_t)(((j + r) * kHaloPitch + s) * 8 + 2 * k),
+                                        bdesc + 2u * k, (kb | tap | k) != 0);
                         }
-                        umma_commit(b_empty(sb));
-                        if (tap == 8) umma_commit(a_empty(sa));
+                        commit(b_empty(sb));
+                        if (tap == 8) commit(a_empty(sa));
                     }
                     __syncwarp();
                 }
             }
-            if (elect_one()) umma_commit(t_full(acc));
+            if (elect_one()) commit(t_full(acc));
             __syncwarp();
         }
-    } else {
+    } else if (warp >= 3) {
         // ===================== epilogue: warps 3..6 cover the four TMEM lane quarters =====================
         const int q = warp & 3;
         const int m = q * 32 + lane;              // pixel within the tile row
@@ -203,7 +235,9 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         const bool fuse = p.fuse_out != nullptr;  // 1x1 Cout->1 output conv on the fp32 activations (final_conv)
         const int dtype = p.dtype;
         uint32_t tcount = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+        const uint32_t leader_t_empty0 = PAIR ? mapa_cluster(t_empty(0), 0) : 0u;
+        for (int item = item0; item < num_items; item += item_step, ++tcount) {
+            const int tile = tile_of(item);
             const int acc = tcount & 1;
             const uint32_t accph = (tcount >> 1) & 1;
             const int wb = tile % p.tiles_w;
@@ -213,7 +247,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_wait(t_full(acc), accph);
             tc_fence_after();
 #pragma unroll 1
-            for (int j = 0; j < HT; ++j) {
+            for (int j = 0; j < (tile < p.num_tiles ? HT : 0); ++j) {      // PAIR: the peer's tile past the end is empty
                 const int ho = hb * HT + j;
                 const bool valid = (wo < p.w) && (ho < p.h);
                 const size_t pix = (static_cast<size_t>(nb) * p.h + ho) * p.w + wo;
@@ -300,12 +334,12 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                 if (fuse && valid) p.fuse_out[pix] = dot + p.fuse_bias;
             }
             tc_fence_before();
-            mbar_arrive(t_empty(acc));
+            if constexpr (PAIR) mbar_arrive_cluster(leader_t_empty0 + 8u * acc); else mbar_arrive(t_empty(acc));
         }
     }
 
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     if (p.stat_sums != nullptr) {
         for (int c = threadIdx.x; c < BN; c += blockDim.x) {
             const double a = s_sum[c], b = s_sq[c];
@@ -317,17 +351,17 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     }
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+        if constexpr (PAIR) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base); else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
     }
 }
 
 template <int BN, int HT>
 static int launch_halo(const CUtensorMap& xm, const CUtensorMap& wm, const HaloParams& hp, int max_ctas,
                        cudaStream_t stream) {
-    using Cfg = HaloCfg<BN, HT>;
+    using Cfg = HaloCfg<BN, HT, false>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(halo): %s", cudaGetErrorString(e));
         attr_set = true;
@@ -335,9 +369,41 @@ static int launch_halo(const CUtensorMap& xm, const CUtensorMap& wm, const HaloP
     int grid = hp.num_tiles;
     const int cap = (max_ctas > 0) ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    conv3x3_halo_kernel<BN, HT><<<grid, kHaloThreads, Cfg::kSmemBytes, stream>>>(xm, wm, hp);
+    conv3x3_halo_kernel<BN, HT, false><<<grid, kHaloThreads, Cfg::kSmemBytes, stream>>>(xm, wm, hp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv3x3_halo launch: %s", cudaGetErrorString(e));
+    return 1;
+}
+
+// CTA pairs (cluster of 2 along x); `wm` must have a box of BN/2 filter rows.
+template <int BN, int HT>
+static int launch_halo_pair(const CUtensorMap& xm, const CUtensorMap& wm, const HaloParams& hp, int max_ctas,
+                            cudaStream_t stream) {
+    using Cfg = HaloCfg<BN, HT, true>;
+    static int max_clusters = -1;
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.blockDim = dim3(kHaloThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = stream;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (max_clusters < 0) {
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::kSmemBytes);
+        if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(halo pair): %s", cudaGetErrorString(e));
+        cfg.gridDim = dim3(2 * (num_sms() / 2));
+        int n = 0;
+        e = cudaOccupancyMaxActiveClusters(&n, conv3x3_halo_kernel<BN, HT, true>, &cfg);
+        if (e != cudaSuccess || n < 1) return set_error(VU_ERR_CUDA, "cudaOccupancyMaxActiveClusters(halo): %s", cudaGetErrorString(e));
+        max_clusters = n;
+    }
+    int pairs = (hp.num_tiles + 1) / 2;
+    int cap = max_clusters;
+    if (max_ctas > 0 && max_ctas / 2 < cap) cap = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
+    if (pairs > cap) pairs = cap;
+    cfg.gridDim = dim3(2 * pairs);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_halo_kernel<BN, HT, true>, xm, wm, hp);
+    if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv3x3_halo pair launch: %s", cudaGetErrorString(e));
     return 1;
 }
 
@@ -372,6 +438,10 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     hp.pos_bias = a->pos_bias;
     hp.stat_sums = a->stat_sums;
 
+    // CTA pairs (cta_group::2) for the tap-reuse kernel as well; VU_HALO_PAIR=0 selects single CTAs (A/B runs)
+    static const int pair_mode = getenv("VU_HALO_PAIR") ? atoi(getenv("VU_HALO_PAIR")) : 1;
+    const bool pair = pair_mode != 0 && hp.num_tiles >= 2;
+
     CUtensorMap xm, wm;
     {
         const uint16_t* xb = static_cast<const uint16_t*>(a->x) + a->x_coff;
@@ -385,9 +455,16 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     {
         const uint64_t dims[3] = {(uint64_t)a->Cin, 9u, (uint64_t)a->Cout};
         const uint64_t str[2] = {(uint64_t)a->Cin * 2, (uint64_t)a->Cin * 2 * 9};
-        const uint32_t wbox[3] = {64u, 1u, (uint32_t)a->Cout};
+        const uint32_t wbox[3] = {64u, 1u, (uint32_t)(pair ? a->Cout / 2 : a->Cout)};
         int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
         if (rc) return rc;
+    }
+    if (pair) {
+        if (a->Cout == 64) {
+            if (ht == 4) return launch_halo_pair<64, 4>(xm, wm, hp, a->max_ctas, stream);
+            return launch_halo_pair<64, 2>(xm, wm, hp, a->max_ctas, stream);
+        }
+        return launch_halo_pair<128, 2>(xm, wm, hp, a->max_ctas, stream);
     }
     if (a->Cout == 64) {
         if (ht == 4) return launch_halo<64, 4>(xm, wm, hp, a->max_ctas, stream);
