@@ -294,3 +294,30 @@ def test_stem_wgrad_and_adamw(cuda_dev):
         T.sumsq(gi.to(d), ss, True)
         T.adamw_step(p, gi.to(d), m, v, 1e-3, (0.9, 0.999), 1e-8, 1e-2, step, ss, 1.0)
     assert (p.cpu() - pt.detach()).abs().max() < 1e-5
+
+
+def test_batched_weight_packing(cuda_dev):
+    """vu_pack_weights_batched (one launch per step for all 50 filter banks, forward + data-gradient layouts) is bit-identical
+    to the single-tensor packers vu_pack_conv_weight / vu_pack_dgrad_weight for every convolution of the model."""
+    from vaeunet_b200 import ops, testing
+    from vaeunet_b200.training import TrainStep
+    from vaeunet_b200.unet import UNetResNet
+    sd, kw = testing.resnet_fixture()
+    model = UNetResNet(**kw)
+    model.load_state_dict(sd)
+    model = model.to(cuda_dev).train()
+    for dt in (ops.BF16, ops.F16):
+        ts = TrainStep(model, dtype=dt, loss_scale=1.0)
+        ts.repack()
+        torch.cuda.synchronize()
+        strides = set()
+        for name, c in ts.convs.items():
+            w = ts.P[c.name]
+            assert torch.equal(c.w16, ops.pack_conv_weight(w, dt)), name
+            ref = ops.pack_dgrad_weights(w, c.stride, dt)
+            got = c.banks if isinstance(c.banks, (list, tuple)) else [c.banks]
+            ref = ref if isinstance(ref, (list, tuple)) else [ref]
+            for a, b in zip(got, ref):
+                assert torch.equal(a.reshape(-1), b.reshape(-1)), name
+            strides.add((c.k, c.stride))
+        assert {(3, 1), (3, 2), (1, 1), (1, 2)} <= strides

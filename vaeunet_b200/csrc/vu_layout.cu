@@ -136,30 +136,35 @@ pack_weights_batched_kernel(const float* __restrict__ src_base, uint16_t* __rest
     const int tiles_o = (e.O + 31) / 32, tiles_i = (e.I + 31) / 32;
     const int nbanks = (e.stride == 2 && K == 3) ? 4 : 1;
     const size_t per_bank = (size_t)e.I * T * e.O;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int tl = blockIdx.x; tl < tiles_o * tiles_i; tl += gridDim.x) {
         const int o0 = (tl / tiles_i) * 32, i0 = (tl % tiles_i) * 32;
         const int ni = min(32, e.I - i0), no = min(32, e.O - o0);
         const int rowlen = ni * T;
         __syncthreads();
-        for (int idx = threadIdx.x; idx < no * rowlen; idx += blockDim.x) {
-            const int oo = idx / rowlen, c = idx % rowlen;
-            tile[oo][c] = w[((size_t)(o0 + oo) * e.I + i0) * T + c];          // c = ii*T + t, contiguous in memory
+        // no per-element div/mod anywhere: a warp takes whole rows, a lane a fixed (row, column) pair and walks the taps
+        for (int oo = warp; oo < no; oo += 8) {
+            const float* src = w + ((size_t)(o0 + oo) * e.I + i0) * T;      // ni*T contiguous floats
+            for (int c = lane; c < rowlen; c += 32) tile[oo][c] = src[c];
         }
         __syncthreads();
-        // forward bank [O][T][I]
-        for (int idx = threadIdx.x; idx < no * T * ni; idx += blockDim.x) {
-            const int ii = idx % ni, t = (idx / ni) % T, oo = idx / (ni * T);
-            fwd[((size_t)(o0 + oo) * T + t) * e.I + i0 + ii] = f2h(tile[oo][ii * T + t], dtype);
+        // forward bank [O][T][I]: lane = input channel (64-byte segments), warp strides over (output channel, tap)
+        for (int q = warp; q < no * T; q += 8) {
+            const int oo = q / T, t = q - oo * T;                           // once per 32 elements
+            if (lane < ni) fwd[((size_t)(o0 + oo) * T + t) * e.I + i0 + lane] = f2h(tile[oo][lane * T + t], dtype);
         }
-        // data-gradient bank(s) [b][I][T][O]
-        for (int idx = threadIdx.x; idx < nbanks * ni * T * no; idx += blockDim.x) {
-            const int oo = idx % no, t = (idx / no) % T, ii = (idx / (no * T)) % ni, bk = idx / (no * T * ni);
+        // data-gradient bank(s) [b][I][T][O]: lane = output channel, warp strides over (bank, input channel, tap)
+        for (int q = warp; q < nbanks * ni * T; q += 8) {
+            const int bk = q / (ni * T), rem = q - bk * (ni * T);
+            const int ii = rem / T, t = rem - ii * T;
             int r, s2;
             if (e.stride == 1) { r = K - 1 - t / K; s2 = K - 1 - t % K; }
             else if (K == 1) { r = 0; s2 = 0; }
             else { r = dgrad_s2_src(bk >> 1, t / 3); s2 = dgrad_s2_src(bk & 1, t % 3); }
-            const float v = (r < 0 || s2 < 0) ? 0.f : tile[oo][ii * T + r * K + s2];
-            bank[bk * per_bank + ((size_t)(i0 + ii) * T + t) * e.O + o0 + oo] = f2h(v, dtype);
+            if (lane < no) {
+                const float v = (r < 0 || s2 < 0) ? 0.f : tile[lane][ii * T + r * K + s2];
+                bank[bk * per_bank + ((size_t)(i0 + ii) * T + t) * e.O + o0 + lane] = f2h(v, dtype);
+            }
         }
     }
 }
@@ -439,7 +444,8 @@ extern "C" int vu_unpack_wgrad_batched(const float* packed_base, float* oihw_bas
 extern "C" int vu_pack_weights_batched(const float* src_base, void* dst_base, const void* table, int n_entries, int dtype,
                                        vu_stream_t st) {
     if (!src_base || !dst_base || !table || n_entries < 1) return set_error(VU_ERR_INVALID, "pack_weights_batched: bad args");
-    dim3 grid(416, n_entries);      // >= the tile count of the largest bank (800 x 512): one tile per block, empty blocks exit
+    dim3 grid(104, n_entries);      // blocks stride over an entry's 32x32 tiles (<= 400 for 800 x 512: four rounds); most
+                                    // entries have fewer tiles than that and their surplus blocks exit at once
     pack_weights_batched_kernel<<<grid, 256, 0, (cudaStream_t)st>>>(src_base, (uint16_t*)dst_base, (const PackEntry*)table, dtype);
     VU_CHECK_LAUNCH("pack_weights_batched");
     return 0;
