@@ -97,16 +97,17 @@ maxpool_idx_fwd_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, u
     }
 }
 
+template <typename I>   // 32-bit index arithmetic whenever the element count allows
 __global__ void __launch_bounds__(256)
 maxpool_idx_bwd_kernel(const uint8_t* __restrict__ code, const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff,
                        uint16_t* __restrict__ dx, int dx_ctot, int dx_coff, int N, int H, int W, int C8, int k, int s, int p,
                        int Ho, int Wo, int dtype) {
-    const size_t total = (size_t)N * H * W * C8;
-    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const I total = (I)N * H * W * C8;
+    for (I idx = blockIdx.x * (I)blockDim.x + threadIdx.x; idx < total; idx += (I)gridDim.x * blockDim.x) {
         const int c8 = idx % C8;
         const int iw = (idx / C8) % W;
-        const int ih = (idx / ((size_t)C8 * W)) % H;
-        const int n = idx / ((size_t)C8 * W * H);
+        const int ih = (idx / ((I)C8 * W)) % H;
+        const int n = idx / ((I)C8 * W * H);
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         const int ho_lo = max(0, (ih + p - k + s) / s), ho_hi = min(Ho - 1, (ih + p) / s);
         const int wo_lo = max(0, (iw + p - k + s) / s), wo_hi = min(Wo - 1, (iw + p) / s);
@@ -401,9 +402,14 @@ extern "C" int vu_maxpool_idx_bwd(const void* code, const void* dy, void* dx, in
     if (!code || !dy || !dx || k < 1 || k > 3) return set_error(VU_ERR_INVALID, "maxpool_idx_bwd: bad args (k <= 3)");
     VU_TB_ALIGN((C | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "maxpool_idx_bwd");
     const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
-    maxpool_idx_bwd_kernel<<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
-        (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W, C / 8, k, s, p,
-        Ho, Wo, dtype);
+    if ((size_t)N * H * W * (C / 8) < (1ull << 31))
+        maxpool_idx_bwd_kernel<uint32_t><<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+            (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W, C / 8, k, s, p,
+            Ho, Wo, dtype);
+    else
+        maxpool_idx_bwd_kernel<size_t><<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
+            (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W, C / 8, k, s, p,
+            Ho, Wo, dtype);
     VU_CHECK_LAUNCH("maxpool_idx_bwd");
     return 0;
 }
