@@ -59,14 +59,15 @@ latent_head_kernel(const uint16_t* __restrict__ f4, int HW, int C, int f_ctot, i
     extern __shared__ float sm[];
     float* s_mean = sm;          // [C]
     float* s_out = sm + C;       // [2L]
+    float* s_part = sm + C + 2 * L;   // [lanes_per][C] per-lane partial sums
     const int b = blockIdx.x;
     const int C8 = C / 8;
-    // phase 1: thread t owns channel group t % C8, strides over pixels; partials reduced through smem atomics
-    for (int c = threadIdx.x; c < C; c += blockDim.x) s_mean[c] = 0.0f;
-    __syncthreads();
+    const int lanes_per = blockDim.x / C8 > 0 ? blockDim.x / C8 : 1;
+    // phase 1: thread t owns channel group t % C8 and strides over pixels; the lanes' partials are combined in a FIXED order
+    // (smem atomics made mu / logvar differ by an ulp from run to run, which every decode then amplifies through its
+    // 16-bit roundings: sharded and unsharded MC could not agree bit for bit)
     {
         const int c8 = threadIdx.x % C8;
-        const int lanes_per = blockDim.x / C8 > 0 ? blockDim.x / C8 : 1;
         const int pl = threadIdx.x / C8;
         float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (pl < lanes_per) {
@@ -78,12 +79,16 @@ latent_head_kernel(const uint16_t* __restrict__ f4, int HW, int C, int f_ctot, i
                 for (int j = 0; j < 8; ++j) acc[j] += f[j];
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) atomicAdd(&s_mean[c8 * 8 + j], acc[j]);
+            for (int j = 0; j < 8; ++j) s_part[pl * C + c8 * 8 + j] = acc[j];
         }
     }
     __syncthreads();
     const float inv = 1.0f / (float)HW;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) s_mean[c] *= inv;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float t = 0.0f;
+        for (int l = 0; l < lanes_per; ++l) t += s_part[l * C + c];
+        s_mean[c] = t * inv;
+    }
     __syncthreads();
     // phase 2
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -314,7 +319,9 @@ extern "C" int vu_latent_head(const void* f4, int B, int h, int w, int C, int f_
     if (C % 8 || f_ctot % 8 || f_coff % 8) return set_error(VU_ERR_ALIGN, "latent_head: channels %% 8");
     if (C / 8 > 256) return set_error(VU_ERR_UNSUPPORTED, "latent_head: C <= 2048");
     if (B < 1 || L < 1 || Ns < 0) return set_error(VU_ERR_INVALID, "latent_head: bad sizes");
-    const size_t smem = (size_t)(C + 2 * L) * sizeof(float);
+    const int lanes_per = 256 / (C / 8) > 0 ? 256 / (C / 8) : 1;
+    const size_t smem = (size_t)(C + 2 * L + (size_t)lanes_per * C) * sizeof(float);
+    if (smem > 48 * 1024) return set_error(VU_ERR_UNSUPPORTED, "latent_head: C / L too large for shared memory");
     latent_head_kernel<<<B, 256, smem, (cudaStream_t)st>>>((const uint16_t*)f4, h * w, C, f_ctot, f_coff, w_mu, b_mu, w_lv,
                                                            b_lv, eps, temperature, Ns, B, L, mu, logvar, z, dtype);
     VU_CHECK_LAUNCH("latent_head");
