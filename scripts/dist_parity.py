@@ -46,12 +46,11 @@ def report(name, res, ref, ms, ms_ref):
     dist.all_reduce(errs, op=dist.ReduceOp.MAX)
     if rank == 0:
         e = errs.tolist()
-        # The merge itself (Chan / reduce-scatter) is exact to fp32 rounding (tests/test_distributed_cpu.py). On the device
-        # a decode's 16-bit activations depend on how many decodes share a launch (tile-width / kernel selection changes
-        # the fp32 summation order by an ulp, which flips 16-bit roundings: scripts/check_batch_invariance.py measures
-        # 5e-4 of the logit range per sample), so sharded vs unsharded is held to the 16-bit bar of BASELINE.json
-        # (1e-2 relative), with the fp32 bar (1e-4) reported beside it.
-        ok = max(e[0], e[1], e[2]) < 1e-2
+        # The merge itself (Chan / reduce-scatter) is exact to fp32 rounding (tests/test_distributed_cpu.py), and since the
+        # latent head's global-average pool sums its partials in a fixed order, a decode's logits are bit-identical
+        # whatever the number of decodes sharing a launch (scripts/check_batch_invariance.py: 0.0 for every sample) - so
+        # sharded vs unsharded is held to the fp32 bar (1e-4 relative; measured 2e-8 .. 2e-7, profiles/r1i_dist_parity_2gpu.log).
+        ok = max(e[0], e[1], e[2]) < 1e-4
         exact = e[0] < 1e-4 and e[2] < 1e-4 and e[4] < 2e-6
         print(f"{name}: world {world}: rel L2 vs unsharded mean {e[0]:.1e} std {e[1]:.1e} entropy {e[2]:.1e}; "
               f"max-abs mean {e[3]:.1e} std {e[4]:.1e} entropy {e[5]:.1e} {'PASS' if ok else 'FAIL'} (fp32 bar: {'met' if exact else 'not met'}); "
