@@ -162,6 +162,25 @@ def test_mc_predict(model, cuda_dev, B, S, N, T):
     assert ref["std"].max() > 1e-3            # the fixture really has sample-to-sample variation
 
 
+@pytest.mark.parametrize("S", [512, 200])
+def test_mc_decode_batch_invariance(model, cuda_dev, S):
+    """One decode's logits do not depend on how many other decodes share the launch, bit for bit, and are reproducible run
+    to run - the property sample-sharded MC (distributed.py, BASELINE config 4) relies on for sharded == unsharded. The
+    latent head sums its global-average-pool partials in a fixed order for this reason (vu_gate_latent.cu)."""
+    m, _ = model
+    x, _ = synthetic_fundus(1, S, seed=21)
+    xf = x.to(cuda_dev).float().contiguous()
+    eps = torch.randn(15, 1, 32, generator=torch.Generator().manual_seed(3)).to(cuda_dev)
+    eng = m.engine()
+    full = eng.mc_logits(xf, 2.0, 15, eps, True)[0].clone()
+    again = eng.mc_logits(xf, 2.0, 15, eps, True)[0].clone()
+    a = eng.mc_logits(xf, 2.0, 8, eps[:8], True)[0].clone()
+    b = eng.mc_logits(xf, 2.0, 7, eps[8:], True)[0].clone()
+    assert torch.equal(full, again)
+    assert torch.equal(full.reshape(15, -1), torch.cat([a, b], dim=1).reshape(15, -1))
+    assert full.reshape(15, -1).std(dim=0).max() > 0      # the samples really differ from each other
+
+
 def test_predict_paths(model, cuda_dev):
     from vaeunet_b200 import predict as P
     m, sd = model
