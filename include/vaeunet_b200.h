@@ -77,6 +77,9 @@ typedef struct vu_conv_args {
      * stat_sums[Cout + co] += sum y^2 over all output pixels, fp64, accumulated (zero it first). The training step feeds them
      * to vu_bn_finalize, so train-mode BatchNorm needs no separate statistics pass over the conv output. NULL = off. */
     double* stat_sums;
+    /* Optional bit mask of the filter taps to run (bit r*KW+s; 0 = all taps): taps whose filter rows are identically zero are
+     * skipped. The four parity banks of a stride-2 data gradient (vu_pack_dgrad_weight) hold 1, 2, 2 and 4 non-zero taps of 9. */
+    int tap_mask;
 } vu_conv_args;
 int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream);
 
@@ -267,6 +270,13 @@ int vu_bn_finalize(const double* sums, double count, int C, float eps, float mom
 int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const float* mean, const float* invstd,
                 const float* gamma, const float* beta, const void* residual, int res_ctot, int res_coff, int relu,
                 void* y, int y_ctot, int y_coff, int dtype, vu_stream_t stream);
+/* vu_bn_finalize + vu_bn_apply in ONE launch: every CTA derives mean / invstd of its channels from the fp64 sums (the
+ * statistics pass or the producing conv's epilogue, vu_conv_args.stat_sums); count = npix. mean / invstd [C] are written
+ * for the backward and the running statistics are updated (NULL = leave them). */
+int vu_bn_apply_sums(const void* x, size_t npix, int C, int x_ctot, int x_coff, const double* sums, float eps, float momentum,
+                     float* running_mean, float* running_var, float* mean, float* invstd, const float* gamma,
+                     const float* beta, const void* residual, int res_ctot, int res_coff, int relu, void* y, int y_ctot,
+                     int y_coff, int dtype, vu_stream_t stream);
 int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_coff, const void* dy, int dy_ctot, int dy_coff,
               const void* y_relu, int y_ctot, int y_coff, const float* mean, const float* invstd, const float* gamma,
               double* sums, void* dx, int dx_ctot, int dx_coff, void* dz_out, int dz_ctot, int dz_coff,

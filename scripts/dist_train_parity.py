@@ -53,6 +53,22 @@ g1 = ts_local.flat_g.clone()
 ts_local.zero_grad(); ts_local.forward_backward(x, m, 0.001, eps)
 spread = ((ts_local.flat_g - g1).norm() / g1.norm()).reshape(1)
 dist.all_reduce(spread, op=dist.ReduceOp.MAX)
+# gradient accumulation under DP (train.py:398,406: accumulation_steps = 2): only the LAST micro-batch communicates
+# (sync=False on the others), and the result equals one plain all-reduce of the accumulated local gradients
+x2, m2 = x.roll(7, dims=3).contiguous(), m.roll(7, dims=3).contiguous()
+ts_dp.zero_grad()
+ts_dp.forward_backward(x, m, 0.001, eps, accum=2, sync=False)
+ts_dp.forward_backward(x2, m2, 0.001, eps, accum=2, sync=True)
+ts_dp._wait_all_reduce()
+torch.cuda.synchronize()
+got_acc = ts_dp.flat_g.clone()
+ts_local.zero_grad()
+ts_local.forward_backward(x, m, 0.001, eps, accum=2)
+ts_local.forward_backward(x2, m2, 0.001, eps, accum=2)
+want_acc = ts_local.flat_g.clone()
+dist.all_reduce(want_acc)
+err_acc = ((got_acc - want_acc).norm() / want_acc.norm()).reshape(1)
+dist.all_reduce(err_acc, op=dist.ReduceOp.MAX)
 ts_dp.optimizer_step()
 p0 = ts_dp.flat_p.clone()
 dist.broadcast(p0, 0)
@@ -83,7 +99,9 @@ for _ in range(5):
     ts_local.step(x, m, 0.001, eps)
 e1.record(); torch.cuda.synchronize()
 if rank == 0:
-    ok = err.item() < 1e-6 and same.item() == 0.0
+    ok = err.item() < 1e-6 and same.item() == 0.0 and err_acc.item() < 3.0 * spread.item() + 1e-6
+    print(f"DP + accumulation (2 micro-batches, sync on the last only) vs plain all-reduce of the accumulated local gradients: "
+          f"rel {err_acc.item():.1e} (budget 3 x run-to-run spread {spread.item():.1e})", flush=True)
     print(f"DP training world {world} B={B}x{S}x{S} per rank: bucketed all-reduce vs one plain all-reduce of the same local gradients rel {err.item():.1e} "
           f"(run-to-run spread of two backward passes {spread.item():.1e}); "
           f"max |param - rank0 param| after the step {same.item():.1e} {'PASS' if ok else 'FAIL'}; "

@@ -32,6 +32,7 @@ class ConvArgs(C.Structure):
         ("fuse_w", C.c_void_p), ("fuse_bias", C.c_float), ("fuse_out", C.c_void_p),
         ("pos_bias", C.c_void_p),
         ("stat_sums", C.c_void_p),
+        ("tap_mask", C.c_int),
     ]
 
 
@@ -80,6 +81,7 @@ SIGNATURES = {
     "vu_bn_stats": [p, sz, i, i, i, p, i, p],
     "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
     "vu_bn_apply": [p, sz, i, i, i, p, p, p, p, p, i, i, i, p, i, i, i, p],
+    "vu_bn_apply_sums": [p, sz, i, i, i, p, f, f, p, p, p, p, p, p, p, i, i, i, p, i, i, i, p],
     "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, p, i, p],
     "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],
     "vu_maxpool_bwd": [p, p, p, i, i, i, i, i, i, i, i, i, i, i, i, i, i, p],

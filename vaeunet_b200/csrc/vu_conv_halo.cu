@@ -411,6 +411,7 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
     const int up = a->out_up > 0 ? a->out_up : 1;
     if (!(a->KH == 3 && a->KW == 3 && a->stride == 1 && a->pad == 1 && up == 1)) return 0;
     if (!(a->Cout == 64 || a->Cout == 128)) return 0;
+    if (a->tap_mask != 0 && a->tap_mask != 0x1FF) return 0;      // tap subsets run on the per-tap kernel
     static const int disabled = getenv("VU_NO_HALO") ? atoi(getenv("VU_NO_HALO")) : 0;
     if (disabled) return 0;
     if (a->W < 96) return 0;   // narrow maps: the 128-pixel tile row would be mostly padding

@@ -609,11 +609,16 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         nmaps = 1;
         int t = 0;
         for (int r = 0; r < KH; ++r)
-            for (int s = 0; s < KW; ++s, ++t) {
+            for (int s = 0; s < KW; ++s) {
+                if (a->tap_mask != 0 && !((a->tap_mask >> (r * KW + s)) & 1)) continue;   // all-zero filter tap
                 kp.tap_dh[t] = (int8_t)(r - P); kp.tap_dw[t] = (int8_t)(s - P);
-                kp.tap_map[t] = 0; kp.tap_widx[t] = (int8_t)t;
+                kp.tap_map[t] = 0; kp.tap_widx[t] = (int8_t)(r * KW + s);
+                ++t;
             }
+        if (t == 0) return set_error(VU_ERR_INVALID, "conv: tap_mask selects no tap");
+        kp.num_taps = t;
     } else {
+        if (a->tap_mask != 0) return set_error(VU_ERR_UNSUPPORTED, "conv: tap_mask needs stride 1");
         // parity planes: plane (pr,pc) holds rows pr, pr+2, ... and cols pc, pc+2, ...
         for (int pr = 0; pr < 2; ++pr)
             for (int pc = 0; pc < 2; ++pc) {

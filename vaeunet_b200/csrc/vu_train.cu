@@ -120,17 +120,30 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
     }
 }
 
+// mean / invstd of channel c from the fp64 sums (same expressions in every kernel that derives them, so the forward's
+// coefficients and the statistics saved for the backward agree bit for bit). fp64 multiplies only: an fp64 division or
+// square root per thread made these prologues longer than the loops they precede.
+__device__ __forceinline__ void bn_stat_from_sums(const double* __restrict__ sums, int C, int c, double inv_count, float eps,
+                                                  float& mean, float& invstd, double& var_out) {
+    const double m = sums[c] * inv_count;
+    double var = sums[C + c] * inv_count - m * m;
+    if (var < 0.0) var = 0.0;
+    mean = (float)m;
+    invstd = 1.0f / sqrtf((float)var + eps);
+    var_out = var;
+}
+
 // mean / invstd from the fp64 sums; running statistics updated like nn.BatchNorm2d (momentum, unbiased var).
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, int C, float eps, float momentum,
                                    float* __restrict__ mean, float* __restrict__ invstd,
                                    float* __restrict__ running_mean, float* __restrict__ running_var) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
-    const double m = sums[c] / count;
-    double var = sums[C + c] / count - m * m;
-    if (var < 0.0) var = 0.0;
-    mean[c] = (float)m;
-    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    float mf, isf; double var;
+    bn_stat_from_sums(sums, C, c, 1.0 / count, eps, mf, isf, var);
+    const double m = (double)mf;
+    mean[c] = mf;
+    invstd[c] = isf;
     if (running_mean != nullptr) {
         const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
         running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
@@ -141,21 +154,44 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
 // y = act(gamma * (x - mean) * invstd + beta + residual) = act(x * sc + sh + residual).
 // The launch uses gridDim * 256 threads with 256 % C8 == 0 whenever C8 is a power of two (every BatchNorm of the model),
 // so a thread keeps the same 8 channels for its whole grid-stride loop and loads the coefficients once (FIXED = true).
+// SUMS variant (sums != nullptr): the batch statistics are derived in the kernel from the fp64 sums the producing conv (or
+// vu_bn_stats) accumulated - no separate finalize launch; block 0 also writes mean / invstd for the backward and updates the
+// running statistics like nn.BatchNorm2d (momentum, unbiased variance).
 template <bool FIXED>
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const float* __restrict__ mean,
                 const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                 const uint16_t* __restrict__ res, int res_ctot, int res_coff, int relu, uint16_t* __restrict__ y,
-                int y_ctot, int y_coff, size_t npix, int C8, int dtype) {
+                int y_ctot, int y_coff, size_t npix, int C8, int dtype, const double* __restrict__ sums = nullptr,
+                double count = 1.0, double inv_count = 1.0, float eps = 0.f, float momentum = 0.f,
+                float* __restrict__ running_mean = nullptr,
+                float* __restrict__ running_var = nullptr, float* __restrict__ mean_out = nullptr,
+                float* __restrict__ invstd_out = nullptr) {
     const size_t total = npix * C8;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const int C = C8 * 8;
+    if (sums != nullptr && blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            float m, is; double var;
+            bn_stat_from_sums(sums, C, c, inv_count, eps, m, is, var);
+            mean_out[c] = m; invstd_out[c] = is;
+            if (running_mean != nullptr) {
+                const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+            }
+        }
+    }
     float sc[8], sh[8];
     auto coeff = [&](int c8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = c8 * 8 + j;
-            sc[j] = invstd[c] * gamma[c];
-            sh[j] = beta[c] - mean[c] * sc[j];
+            float m, is;
+            if (sums != nullptr) { double var; bn_stat_from_sums(sums, C, c, inv_count, eps, m, is, var); }
+            else { m = mean[c]; is = invstd[c]; }
+            sc[j] = is * gamma[c];
+            sh[j] = beta[c] - m * sc[j];
         }
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -345,6 +381,28 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
             (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
             (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype);
     VU_CHECK_LAUNCH("bn_apply");
+    return 0;
+}
+
+extern "C" int vu_bn_apply_sums(const void* x, size_t npix, int C, int x_ctot, int x_coff, const double* sums, float eps,
+                                float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                                const float* gamma, const float* beta, const void* residual, int res_ctot, int res_coff,
+                                int relu, void* y, int y_ctot, int y_coff, int dtype, vu_stream_t st) {
+    if (!x || !y || !sums || !mean || !invstd || !gamma || !beta || npix < 1) return set_error(VU_ERR_INVALID, "bn_apply_sums: null");
+    VU_TR_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff | res_ctot | res_coff) % 8, "bn_apply_sums");
+    const int C8 = C / 8;
+    const int grid = tr_grid(npix * C8, 256 * 4, 16);
+    if (256 % C8 == 0)
+        bn_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, x_ctot, x_coff, nullptr, nullptr, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
+            (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype, sums, (double)npix, 1.0 / (double)npix, eps, momentum, running_mean,
+            running_var, mean, invstd);
+    else
+        bn_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)st>>>(
+            (const uint16_t*)x, x_ctot, x_coff, nullptr, nullptr, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
+            (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype, sums, (double)npix, 1.0 / (double)npix, eps, momentum, running_mean,
+            running_var, mean, invstd);
+    VU_CHECK_LAUNCH("bn_apply_sums");
     return 0;
 }
 

@@ -75,39 +75,43 @@ __global__ void map_bn_sigmoid_bwd_kernel(const float* __restrict__ x, const flo
 }
 
 // ---------------------------------------------------------------- dense layers on vectors
-// One block per 32 output channels; the block sees all M rows, so train-mode BatchNorm statistics (over the M rows —
-// every pixel of a spatially constant map is the same vector) need no cross-block reduction.
 //   y_raw[m,c] = b[c] + sum_l z[m,l] w[c,l];  y = act(gamma (y_raw - mean) invstd + beta)
+// One WARP per output channel (8 channels per block): the lanes split the L inputs of each dot product (coalesced rows of z
+// and w) and combine with a shuffle butterfly; afterwards lane m % 32 holds row m of the channel, so the train-mode BatchNorm
+// statistics over the M rows (every pixel of a spatially constant map is the same vector) are warp reductions too. All
+// orders are fixed: results are bit-reproducible from run to run. (The first version gave a thread whole dot products -
+// strided weight reads on 4..16 blocks: 148 us for the 512 -> 128 gate layer; this one is a few microseconds.)
 constexpr int kVecM = 64;
 __global__ void __launch_bounds__(256)
 vec_layer_fwd_kernel(const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ b, int M, int L,
                      int C, const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
                      double stat_count, float* running_mean, float* running_var, int relu, float* __restrict__ y_raw,
                      float* __restrict__ y, float* __restrict__ mean_o, float* __restrict__ invstd_o) {
-    __shared__ float s_raw[kVecM][33];
-    const int c0 = blockIdx.x * 32;
-    for (int i = threadIdx.x; i < M * 32; i += 256) {
-        const int m = i / 32, cl = i % 32, c = c0 + cl;
+    const int lane = threadIdx.x & 31, c = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (c >= C) return;                                   // warp-uniform
+    const float* wr = w + (size_t)c * L;
+    const float bias = b ? b[c] : 0.f;
+    float v[2] = {0.f, 0.f};                              // rows lane, lane + 32
+    for (int m = 0; m < M; ++m) {
+        const float* zr = z + (size_t)m * L;
         float acc = 0.f;
-        if (c < C) {
-            acc = b ? b[c] : 0.f;
-            for (int l = 0; l < L; ++l) acc = fmaf(z[(size_t)m * L + l], w[(size_t)c * L + l], acc);
-            y_raw[(size_t)m * C + c] = acc;
-        }
-        s_raw[m][cl] = acc;
+        for (int l = lane; l < L; l += 32) acc = fmaf(__ldg(zr + l), __ldg(wr + l), acc);
+        acc = warp_sum(acc) + bias;
+        if ((m & 31) == lane) { if (m < 32) v[0] = acc; else v[1] = acc; }
     }
-    __syncthreads();
-    if (threadIdx.x < 32 && c0 + threadIdx.x < C) {
-        const int c = c0 + threadIdx.x, cl = threadIdx.x;
-        float mean = 0.f, invstd = 1.f, g = 1.f, be = 0.f;
-        if (gamma != nullptr) {
-            double s0 = 0.0, s1 = 0.0;
-            for (int m = 0; m < M; ++m) { s0 += s_raw[m][cl]; s1 += (double)s_raw[m][cl] * s_raw[m][cl]; }
-            const double mu = s0 / M;
-            double var = s1 / M - mu * mu;
-            if (var < 0.0) var = 0.0;
-            mean = (float)mu; invstd = (float)(1.0 / sqrt(var + (double)eps));
-            g = gamma[c]; be = beta[c];
+    const bool has0 = lane < M, has1 = lane + 32 < M;
+    if (has0) y_raw[(size_t)lane * C + c] = v[0];
+    if (has1) y_raw[(size_t)(lane + 32) * C + c] = v[1];
+    float mean = 0.f, invstd = 1.f, g = 1.f, be = 0.f;
+    if (gamma != nullptr) {
+        const double s0 = warp_sum_d((has0 ? (double)v[0] : 0.0) + (has1 ? (double)v[1] : 0.0));
+        const double s1 = warp_sum_d((has0 ? (double)v[0] * v[0] : 0.0) + (has1 ? (double)v[1] * v[1] : 0.0));
+        const double mu = s0 / M;
+        double var = s1 / M - mu * mu;
+        if (var < 0.0) var = 0.0;
+        mean = (float)mu; invstd = (float)(1.0 / sqrt(var + (double)eps));
+        g = gamma[c]; be = beta[c];
+        if (lane == 0) {
             mean_o[c] = mean; invstd_o[c] = invstd;
             if (running_mean) {
                 const double unbiased = stat_count > 1.0 ? var * stat_count / (stat_count - 1.0) : var;
@@ -115,102 +119,114 @@ vec_layer_fwd_kernel(const float* __restrict__ z, const float* __restrict__ w, c
                 running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
             }
         }
-        for (int m = 0; m < M; ++m) {
-            float v = (s_raw[m][cl] - mean) * invstd * g + be;
-            y[(size_t)m * C + c] = relu ? fmaxf(v, 0.f) : v;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int m = lane + 32 * h;
+        if (m < M) {
+            const float o = (v[h] - mean) * invstd * g + be;
+            y[(size_t)m * C + c] = relu ? fmaxf(o, 0.f) : o;
         }
     }
 }
 
-// dy -> (ReLU mask from y) -> BN backward over the M rows -> dy_raw tile s_d[m][0..31] of channels c0..c0+31 (all threads of
-// the block take part; ends with a __syncthreads). When `grads` is set, thread cl < 32 also accumulates dgamma / dbeta / db.
-__device__ __forceinline__ void vec_dy_raw_tile(float (*s_d)[33], int c0, const float* __restrict__ dy,
-                                                const float* __restrict__ y_raw, const float* __restrict__ y, int M, int C,
-                                                const float* __restrict__ gamma, const float* __restrict__ mean,
-                                                const float* __restrict__ invstd, int relu, bool grads, float* __restrict__ db,
-                                                float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    for (int i = threadIdx.x; i < M * 32; i += blockDim.x) {
-        const int m = i / 32, cl = i % 32, c = c0 + cl;
-        float g = 0.f;
-        if (c < C) {
-            g = dy[(size_t)m * C + c];
-            if (relu && !(y[(size_t)m * C + c] > 0.f)) g = 0.f;
-        }
-        s_d[m][cl] = g;
-    }
-    __syncthreads();
-    if (threadIdx.x < 32 && c0 + threadIdx.x < C) {
-        const int c = c0 + threadIdx.x, cl = threadIdx.x;
-        if (gamma != nullptr) {
-            double s0 = 0.0, s1 = 0.0;
-            for (int m = 0; m < M; ++m) {
-                const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
-                s0 += s_d[m][cl]; s1 += (double)s_d[m][cl] * xh;
-            }
-            if (grads && dgamma) { dgamma[c] += (float)s1; dbeta[c] += (float)s0; }
-            const float m0 = (float)(s0 / M), m1 = (float)(s1 / M);
-            for (int m = 0; m < M; ++m) {
-                const float xh = (y_raw[(size_t)m * C + c] - mean[c]) * invstd[c];
-                s_d[m][cl] = gamma[c] * invstd[c] * (s_d[m][cl] - m0 - xh * m1);
-            }
-        }
-        if (grads && db) {
-            float s = 0.f;
-            for (int m = 0; m < M; ++m) s += s_d[m][cl];
-            db[c] += s;
-        }
-    }
-    __syncthreads();
-}
-
-// dw[c,l] += sum_m dy_raw z, db[c] += sum_m dy_raw, dgamma / dbeta += (parameter gradients accumulate). One block per 32
-// channels.
+// Backward of the layer for one channel per warp: dy -> (ReLU mask from y) -> BatchNorm backward over the M rows -> dy_raw
+// (rows lane, lane + 32 in registers; written to dy_raw_out [M][C] for the input-gradient kernel), parameter gradients
+// db / dgamma / dbeta accumulated, then dw[c,l] += sum_m dy_raw[m] z[m,l] with the lanes across l (coalesced z rows).
 __global__ void __launch_bounds__(256)
 vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ y_raw,
                      const float* __restrict__ y, int M, int L, int C, const float* __restrict__ gamma,
                      const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ dw,
                      float* __restrict__ db, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      float* __restrict__ dy_raw_out) {
-    __shared__ float s_d[kVecM][33];
-    const int c0 = blockIdx.x * 32;
-    vec_dy_raw_tile(s_d, c0, dy, y_raw, y, M, C, gamma, mean, invstd, relu, true, db, dgamma, dbeta);
-    if (dy_raw_out != nullptr)                 // [M][C] for the input-gradient kernel
-        for (int i = threadIdx.x; i < M * 32; i += 256) {
-            const int m = i / 32, cl = i % 32;
-            if (c0 + cl < C) dy_raw_out[(size_t)m * C + c0 + cl] = s_d[m][cl];
+    const int lane = threadIdx.x & 31, c = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (c >= C) return;                                   // warp-uniform
+    float d[2] = {0.f, 0.f};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int m = lane + 32 * h;
+        if (m < M) {
+            float g = dy[(size_t)m * C + c];
+            if (relu && !(y[(size_t)m * C + c] > 0.f)) g = 0.f;
+            d[h] = g;
         }
-    if (dw != nullptr)
-        for (int i = threadIdx.x; i < 32 * L; i += 256) {
-            const int cl = i / L, l = i % L, c = c0 + cl;
-            if (c >= C) continue;
-            float acc = 0.f;
-            for (int m = 0; m < M; ++m) acc = fmaf(s_d[m][cl], z[(size_t)m * L + l], acc);
-            dw[(size_t)c * L + l] += acc;
+    }
+    if (gamma != nullptr) {
+        const float mu = mean[c], is = invstd[c];
+        float xh[2] = {0.f, 0.f};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int m = lane + 32 * h;
+            if (m < M) xh[h] = (y_raw[(size_t)m * C + c] - mu) * is;
         }
+        const double s0 = warp_sum_d((double)d[0] + (double)d[1]);
+        const double s1 = warp_sum_d((double)d[0] * xh[0] + (double)d[1] * xh[1]);
+        if (lane == 0 && dgamma) { dgamma[c] += (float)s1; dbeta[c] += (float)s0; }
+        const float m0 = (float)(s0 / M), m1 = (float)(s1 / M), a = gamma[c] * is;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (lane + 32 * h < M) d[h] = a * (d[h] - m0 - xh[h] * m1);
+    }
+    if (db != nullptr) {
+        const float s = warp_sum(d[0] + d[1]);
+        if (lane == 0) db[c] += s;
+    }
+    if (dy_raw_out != nullptr) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (lane + 32 * h < M) dy_raw_out[(size_t)(lane + 32 * h) * C + c] = d[h];
+    }
+    if (dw != nullptr) {
+        for (int l0 = 0; l0 < L; l0 += 128) {             // 4 columns per lane per pass
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int m = 0; m < M; ++m) {
+                const float g = __shfl_sync(0xffffffffu, m < 32 ? d[0] : d[1], m & 31);
+                const float* zr = z + (size_t)m * L + l0 + lane;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (l0 + lane + 32 * u < L) acc[u] = fmaf(g, __ldg(zr + 32 * u), acc[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (l0 + lane + 32 * u < L) dw[(size_t)c * L + l0 + lane + 32 * u] += acc[u];
+        }
+    }
 }
 
-// dz[m,l] += sum_c dy_raw[m,c] w[c,l] from the [M][C] pre-BN gradient the kernel above wrote. One block per 32 columns l,
-// channels walked in a fixed order (no atomics): the input gradient is bit-reproducible from run to run - it feeds the
-// BatchNorm backward of the 2x2 / 4x4 encoder maps, which amplifies fp32 atomics-order noise by orders of magnitude.
+// dz[m,l] += sum_c dy_raw[m,c] w[c,l] from the [M][C] pre-BN gradient the kernel above wrote. One block per 32 columns l
+// (lane = column); the 8 warps take the channels c = warp, warp + 8, ... and their partial sums are combined through shared
+// memory in warp order - a fixed order without atomics: the input gradient is bit-reproducible from run to run (it feeds the
+// BatchNorm backward of the 2x2 / 4x4 encoder maps, which amplifies fp32 atomics-order noise by orders of magnitude).
 __global__ void __launch_bounds__(256)
 vec_layer_dz_kernel(const float* __restrict__ dy_raw, const float* __restrict__ w, int M, int L, int C,
                     float* __restrict__ dz) {
-    const int ll = threadIdx.x % 32, mg = threadIdx.x / 32;     // thread: column l, rows mg, mg + 8, ...
-    const int l = blockIdx.x * 32 + ll;
-    if (l >= L) return;
-    float acc[kVecM / 8];
+    __shared__ float part[8][16][33];
+    const int lane = threadIdx.x & 31, wg = threadIdx.x >> 5;
+    const int l = blockIdx.x * 32 + lane;
+    for (int m0 = 0; m0 < M; m0 += 16) {                  // 16 rows per pass
+        float acc[16];
 #pragma unroll
-    for (int j = 0; j < kVecM / 8; ++j) acc[j] = 0.f;
-#pragma unroll 4
-    for (int c = 0; c < C; ++c) {
-        const float wv = __ldg(w + (size_t)c * L + l);
+        for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+        for (int c = wg; c < C; c += 8) {
+            const float wv = l < L ? __ldg(w + (size_t)c * L + l) : 0.f;
 #pragma unroll
-        for (int j = 0; j < kVecM / 8; ++j)
-            if (mg + 8 * j < M) acc[j] = fmaf(__ldg(dy_raw + (size_t)(mg + 8 * j) * C + c), wv, acc[j]);
+            for (int j = 0; j < 16; ++j)
+                if (m0 + j < M) acc[j] = fmaf(__ldg(dy_raw + (size_t)(m0 + j) * C + c), wv, acc[j]);   // warp-uniform address
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) part[wg][j][lane] = acc[j];
+        __syncthreads();
+        for (int i = threadIdx.x; i < 16 * 32; i += 256) {
+            const int j = i >> 5, ll = i & 31;
+            if (m0 + j < M && blockIdx.x * 32 + ll < L) {
+                float t = 0.f;
+#pragma unroll
+                for (int g = 0; g < 8; ++g) t += part[g][j][ll];
+                dz[(size_t)(m0 + j) * L + blockIdx.x * 32 + ll] += t;
+            }
+        }
+        __syncthreads();
     }
-#pragma unroll
-    for (int j = 0; j < kVecM / 8; ++j)
-        if (mg + 8 * j < M) dz[(size_t)(mg + 8 * j) * L + l] += acc[j];
 }
 
 // z = mu + eps * exp(.5 lv) * T  ->  dmu += dz (summed over samples), dlv += dz * eps * .5 * exp(.5 lv) * T
@@ -348,7 +364,7 @@ extern "C" int vu_vec_layer_fwd(const float* z, const float* w, const float* b, 
                                 vu_stream_t st) {
     if (!z || !w || !y_raw || !y || M < 1 || M > kVecM) return set_error(VU_ERR_INVALID, "vec_layer_fwd: bad args (M <= 64)");
     if (gamma && (!beta || !mean || !invstd)) return set_error(VU_ERR_INVALID, "vec_layer_fwd: BN needs beta/mean/invstd");
-    vec_layer_fwd_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)st>>>(z, w, b, M, L, C, gamma, beta, eps, momentum, stat_count,
+    vec_layer_fwd_kernel<<<(C + 7) / 8, 256, 0, (cudaStream_t)st>>>(z, w, b, M, L, C, gamma, beta, eps, momentum, stat_count,
                                                                       running_mean, running_var, relu, y_raw, y, mean, invstd);
     VU_CHECK_LAUNCH("vec_layer_fwd");
     return 0;
@@ -359,7 +375,7 @@ extern "C" int vu_vec_layer_bwd(const float* dy, const float* z, const float* w,
                                 float* dw, float* db, float* dgamma, float* dbeta, float* scratch, vu_stream_t st) {
     if (!dy || !z || !w || !y_raw || !y || M < 1 || M > kVecM) return set_error(VU_ERR_INVALID, "vec_layer_bwd: bad args (M <= 64)");
     if (dz && !scratch) return set_error(VU_ERR_INVALID, "vec_layer_bwd: dz needs the M*C scratch buffer");
-    vec_layer_bwd_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)st>>>(dy, z, y_raw, y, M, L, C, gamma, mean, invstd, relu, dw,
+    vec_layer_bwd_kernel<<<(C + 7) / 8, 256, 0, (cudaStream_t)st>>>(dy, z, y_raw, y, M, L, C, gamma, mean, invstd, relu, dw,
                                                                       db, dgamma, dbeta, dz ? scratch : nullptr);
     VU_CHECK_LAUNCH("vec_layer_bwd");
     if (dz != nullptr) {

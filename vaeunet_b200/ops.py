@@ -20,6 +20,8 @@ _TORCH_DT = {BF16: torch.bfloat16, F16: torch.float16}
 # default 16-bit storage type of activations / filter banks (see unet/_base.py KernelModule.compute_dtype)
 DEFAULT_DTYPE = F16
 
+import os as _os
+S2_TAP_MASK = _os.environ.get("VU_S2_TAP_MASK", "1") != "0"    # stride-2 data gradient: skip the all-zero taps of the parity banks
 # launch counter (bench.py reports it as gpu_launches)
 LAUNCHES = 0
 # when set to a list, conv2d appends (start_event, end_event, algorithmic_flop) per launch (bench.py roofline)
@@ -109,7 +111,7 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
            out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0,
            fuse_w: Optional[torch.Tensor] = None, fuse_bias: float = 0.0, fuse_out: Optional[torch.Tensor] = None,
            store: bool = True, pos_bias: Optional[torch.Tensor] = None,
-           stat_sums: Optional[torch.Tensor] = None) -> Optional[Act]:
+           stat_sums: Optional[torch.Tensor] = None, tap_mask: int = 0) -> Optional[Act]:
     """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y.
     pos_bias: fp32 [N, 9, Cout] pre-scale bias by border class (`border_bias`): spatially constant input channels left out.
     stat_sums: ZEROED fp64 [2*Cout]; the epilogue adds per-channel sum / sum of squares of the stored outputs (the
@@ -156,13 +158,15 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
         a.stat_sums = stat_sums.data_ptr()
     else:
         a.stat_sums = None
+    a.tap_mask = tap_mask
     if CONV_TIMING is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
         e1.record()
-        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * k * k * x.C,
-                            f"N{x.N} {x.H}x{x.W} Cin{x.C} Cout{Cout} k{k} s{stride}"))
+        ntaps = bin(tap_mask).count("1") if tap_mask else k * k
+        CONV_TIMING.append((e0, e1, 2.0 * x.N * Ho * Wo * Cout * ntaps * x.C,
+                            f"N{x.N} {x.H}x{x.W} Cin{x.C} Cout{Cout} k{k} s{stride}" + (f" taps{ntaps}" if tap_mask else "")))
     else:
         check(load().vu_conv2d_fwd(C.byref(a), _stream()), "vu_conv2d_fwd")
     _count()
@@ -238,9 +242,17 @@ def conv2d_dgrad(dy: Act, banks, k: int, stride: int, H: int, W: int, out: Optio
         out.t[..., out.coff:out.coff + out.C].zero_()
         _count()
         return conv2d(dy, banks[0], 1, 1, 0, None, None, False, out=out, out_up=2, out_dh=0, out_dw=0)
+    # non-zero bank rows / columns per parity (vu_pack_dgrad_weight): parity 0 -> {1}, parity 1 -> {1, 2}; the other taps of a
+    # parity bank are identically zero and are skipped (9 tap passes over the four banks instead of 36)
+    nz = ((1,), (1, 2))
     for ph in range(2):
         for pc in range(2):
-            conv2d(dy, banks[ph * 2 + pc], 3, 1, 1, None, None, False, out=out, out_up=2, out_dh=ph, out_dw=pc)
+            mask = 0
+            for r in nz[ph]:
+                for s in nz[pc]:
+                    mask |= 1 << (r * 3 + s)
+            conv2d(dy, banks[ph * 2 + pc], 3, 1, 1, None, None, False, out=out, out_up=2, out_dh=ph, out_dw=pc,
+                   tap_mask=mask if S2_TAP_MASK else 0)
     return out
 
 

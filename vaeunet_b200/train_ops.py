@@ -36,17 +36,17 @@ def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, res
         assert sums.dtype == torch.float64 and sums.numel() == 2 * Cc
     mean = torch.empty(Cc, dtype=torch.float32, device=dev)
     invstd = torch.empty(Cc, dtype=torch.float32, device=dev)
-    check(load().vu_bn_finalize(sums.data_ptr(), float(_npix(x)), Cc, BN_EPS, BN_MOMENTUM, mean.data_ptr(), invstd.data_ptr(),
-                                _ptr(running_mean) if update_running else None,
-                                _ptr(running_var) if update_running else None, _stream()), "vu_bn_finalize")
     if out is None:
         out = ops.new_act(x.N, x.H, x.W, Cc, x.dt, dev)
     r = residual
-    check(load().vu_bn_apply(x.t.data_ptr(), _npix(x), Cc, x.ctot, x.coff, mean.data_ptr(), invstd.data_ptr(),
-                             _f32(gamma).data_ptr(), _f32(beta).data_ptr(), r.t.data_ptr() if r else None,
-                             r.ctot if r else 8, r.coff if r else 0, int(relu), out.t.data_ptr(), out.ctot, out.coff, x.dt,
-                             _stream()), "vu_bn_apply")
-    _count(2)
+    # finalize (mean / invstd / running statistics) happens inside the apply kernel: one launch
+    check(load().vu_bn_apply_sums(x.t.data_ptr(), _npix(x), Cc, x.ctot, x.coff, sums.data_ptr(), BN_EPS, BN_MOMENTUM,
+                                  _ptr(running_mean) if update_running else None,
+                                  _ptr(running_var) if update_running else None, mean.data_ptr(), invstd.data_ptr(),
+                                  _f32(gamma).data_ptr(), _f32(beta).data_ptr(), r.t.data_ptr() if r else None,
+                                  r.ctot if r else 8, r.coff if r else 0, int(relu), out.t.data_ptr(), out.ctot, out.coff, x.dt,
+                                  _stream()), "vu_bn_apply_sums")
+    _count(1)
     return out, mean, invstd
 
 

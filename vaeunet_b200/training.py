@@ -37,6 +37,10 @@ import os
 
 # BatchNorm forward statistics accumulated in the epilogue of the producing conv (VU_FUSE_BN_STATS=0: separate pass)
 FUSE_BN_STATS = os.environ.get("VU_FUSE_BN_STATS", "1") != "0"
+# Weight gradients on a second CUDA stream (VU_TRAIN_STREAMS=0: everything on the current stream). They are leaves of the
+# backward (only the optimizer reads them), so they overlap the BatchNorm-backward / data-gradient chain instead of
+# sitting inside it: tensor-pipe work under the memory-bound kernels of the chain.
+WGRAD_STREAM = os.environ.get("VU_TRAIN_STREAMS", "1") != "0"
 
 _ALIGN = 64   # floats: every parameter starts on a 256-byte boundary of the flat buffers
 
@@ -127,6 +131,11 @@ class TrainStep:
         self._register_convs()
         self.sumsq = torch.zeros(1, dtype=torch.float64, device=self.dev)
         self._pending = []
+        self.side = torch.cuda.Stream(device=self.dev) if WGRAD_STREAM else None
+        self._side_keep = []        # operands of weight gradients in flight on the side stream (kept alive until the join)
+        self._side_used = False
+        self._sync_grads = True
+        self._reduced = False       # the flat gradient already holds an all-reduced sum (no further local accumulation)
 
     # ------------------------------------------------------------------ parameter storage
     def _flatten(self):
@@ -255,7 +264,24 @@ class TrainStep:
 
     def _wgrad(self, x: Act, dy: Act, name: str):
         c = self.convs[name]
-        ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.GP[name])
+        if self.side is None:
+            ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.GP[name])
+            return
+        # fork: the side stream waits for everything enqueued so far (dy is final), then runs the weight gradient
+        # concurrently with the rest of the backward chain
+        main = torch.cuda.current_stream()
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.GP[name])
+        self._side_keep.append((x, dy))
+        self._side_used = True
+
+    def _join_side(self):
+        """The current stream waits for the weight gradients in flight (before their packed buffer is read)."""
+        if self.side is not None and self._side_used:
+            torch.cuda.current_stream().wait_stream(self.side)
+            self._side_keep.clear()     # safe: later allocations are ordered after the wait on this stream
+            self._side_used = False
 
     def _dgrad(self, dy: Act, name: str, H: int, W: int, out: Optional[Act] = None, accumulate=False) -> Act:
         c = self.convs[name]
@@ -494,6 +520,7 @@ class TrainStep:
     # ------------------------------------------------------------------ data parallel (NCCL all-reduce of gradients)
     def _all_reduce_bucket(self, name: str):
         """A bucket of parameters has its final gradients: unpack its conv weight gradients, then start its all-reduce."""
+        self._join_side()
         if name in self.unpack_tables:
             tab, n, max_row = self.unpack_tables[name]
             ops.check(ops.load().vu_unpack_wgrad_batched(self.flat_gp.data_ptr(), self.flat_g.data_ptr(), tab.data_ptr(), n,
@@ -503,8 +530,9 @@ class TrainStep:
 
     def _start_all_reduce(self, name: str):
         """Asynchronous NCCL all-reduce (sum) of one contiguous range of the flat gradient; the 1/world average is folded
-        into the AdamW kernel's gradient scale."""
-        if self.pg is None or self.world == 1:
+        into the AdamW kernel's gradient scale. With gradient accumulation only the LAST micro-batch communicates
+        (`forward_backward(sync=False)` = DDP's no_sync): the buckets then hold the local sum over all micro-batches."""
+        if self.pg is None or self.world == 1 or not self._sync_grads:
             return
         import torch.distributed as dist
         if not self.bucket_all_reduce:
@@ -521,10 +549,20 @@ class TrainStep:
 
     # ------------------------------------------------------------------ the step
     def zero_grad(self):
+        self._wait_all_reduce()
         self.flat_g.zero_()
+        self._reduced = False
 
-    def forward_backward(self, images, masks, beta: float, eps: torch.Tensor, accum: int = 1):
-        """Gradients of one (micro-)batch accumulated into the flat gradient buffer (train.py:387-403)."""
+    def forward_backward(self, images, masks, beta: float, eps: torch.Tensor, accum: int = 1, sync: bool = True):
+        """Gradients of one (micro-)batch accumulated into the flat gradient buffer (train.py:387-403).
+        accum: number of micro-batches per optimizer step (the loss is divided by it, train.py:398).
+        sync: data parallel only - pass False for every micro-batch but the last one of an accumulation window; the
+        gradient all-reduces then start on the last micro-batch only, on the accumulated local gradients."""
+        if self._reduced:
+            raise VaeUnetError("forward_backward after the gradients of this window were all-reduced: call optimizer_step() "
+                               "(or zero_grad()) first, and pass sync=False for all micro-batches but the last")
+        self._sync_grads = bool(sync)
+        self._reduced = bool(sync) and self.pg is not None and self.world > 1
         self.repack()
         _, _, _, S = self.forward(images, eps)
         out, dlogits, dmu, dlv = self.loss_and_grads(S, masks, beta, accum)
@@ -534,6 +572,7 @@ class TrainStep:
     def optimizer_step(self):
         """clip_grad_norm_(max_norm) + AdamW (train.py:405-408) on the flat buffers; averages over the DP group."""
         self._wait_all_reduce()
+        self._reduced = False
         self.step_count += 1
         gscale = 1.0 / (self.loss_scale * self.world)
         T.sumsq(self.flat_g, self.sumsq, True)
