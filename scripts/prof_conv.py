@@ -1,5 +1,5 @@
 """Run one conv layer shape of the bench through the C ABI a few times (target of the ncu captures).
-usage: python scripts/prof_conv.py N H W Cin Cout k [reps] [dtype]"""
+usage: python scripts/prof_conv.py N H W Cin Cout k [reps] [dtype] [stats]   (stats: training epilogue, BN statistics on)"""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -10,6 +10,7 @@ N, H, W, Cin, Cout, k = map(int, sys.argv[1:7])
 reps = int(sys.argv[7]) if len(sys.argv) > 7 else 5
 dt = ops.F16 if (len(sys.argv) <= 8 or sys.argv[8] == "f16") else ops.BF16
 tdt = torch.float16 if dt == ops.F16 else torch.bfloat16
+stats = len(sys.argv) > 9 and sys.argv[9] == "stats"
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev).manual_seed(0)
 x = ops.Act((torch.randn(N, H, W, Cin, device=dev, generator=g)).to(tdt))
@@ -23,7 +24,12 @@ for i in range(reps):
     flush.zero_()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    ops.conv2d(x, wp, k, 1, k // 2, scale, bias, True, out=y)
+    if stats:
+        ss = torch.zeros(2 * Cout, dtype=torch.float64, device=dev)
+        e0.record()
+        ops.conv2d(x, wp, k, 1, k // 2, None, None, False, out=y, stat_sums=ss)
+    else:
+        ops.conv2d(x, wp, k, 1, k // 2, scale, bias, True, out=y)
     e1.record()
     torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))

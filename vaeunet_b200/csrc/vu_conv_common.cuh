@@ -3,6 +3,7 @@
 #pragma once
 #include "vu_ptx.cuh"
 #include "vu_internal.h"
+#include "vu_half.cuh"
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -15,8 +16,7 @@ __device__ __forceinline__ uint32_t pack2(float a, float b, int dtype) {
         __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
         return *reinterpret_cast<uint32_t*>(&v);
     } else {
-        __half2 v = __floats2half2_rn(a, b);
-        return *reinterpret_cast<uint32_t*>(&v);
+        return cvt_f16x2_sat(a, b);      // saturating (vu_half.cuh): no silent inf in fp16 activations
     }
 }
 __device__ __forceinline__ float2 unpack2(uint32_t u, int dtype) {

@@ -6,9 +6,17 @@
 
 namespace vu {
 
+// fp16 conversions SATURATE to +-65504 (cvt.rn.satfinite: one F2FP instruction, same cost as the plain conversion): an
+// activation beyond the fp16 range of a real checkpoint becomes the largest finite value instead of a silent inf that would
+// turn every downstream BatchNorm / sigmoid into NaN. NaN stays NaN. bf16 has the fp32 exponent range and needs none.
+__device__ __forceinline__ uint32_t cvt_f16x2_sat(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
 __device__ __forceinline__ uint16_t f2h(float v, int dtype) {
     if (dtype == 0) { __nv_bfloat16 b = __float2bfloat16_rn(v); return *reinterpret_cast<uint16_t*>(&b); }
-    __half h = __float2half_rn(v); return *reinterpret_cast<uint16_t*>(&h);
+    return static_cast<uint16_t>(cvt_f16x2_sat(v, 0.f) & 0xffffu);
 }
 __device__ __forceinline__ float h2f(uint16_t u, int dtype) {
     if (dtype == 0) return __uint_as_float(static_cast<uint32_t>(u) << 16);
@@ -16,7 +24,7 @@ __device__ __forceinline__ float h2f(uint16_t u, int dtype) {
 }
 __device__ __forceinline__ uint32_t pack2h(float a, float b, int dtype) {
     if (dtype == 0) { __nv_bfloat162 v = __floats2bfloat162_rn(a, b); return *reinterpret_cast<uint32_t*>(&v); }
-    __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&v);
+    return cvt_f16x2_sat(a, b);
 }
 __device__ __forceinline__ void unpack2h(uint32_t u, float& a, float& b, int dtype) {
     if (dtype == 0) { a = __uint_as_float(u << 16); b = __uint_as_float(u & 0xffff0000u); return; }

@@ -91,13 +91,27 @@ vec_layer_fwd_kernel(const float* __restrict__ z, const float* __restrict__ w, c
     if (c >= C) return;                                   // warp-uniform
     const float* wr = w + (size_t)c * L;
     const float bias = b ? b[c] : 0.f;
-    float v[2] = {0.f, 0.f};                              // rows lane, lane + 32
-    for (int m = 0; m < M; ++m) {
-        const float* zr = z + (size_t)m * L;
-        float acc = 0.f;
-        for (int l = lane; l < L; l += 32) acc = fmaf(__ldg(zr + l), __ldg(wr + l), acc);
-        acc = warp_sum(acc) + bias;
-        if ((m & 31) == lane) { if (m < 32) v[0] = acc; else v[1] = acc; }
+    float v[2] = {bias, bias};                            // rows lane, lane + 32
+    // 8 columns per lane per pass, the filter row in registers; every load is unconditional (clamped index, zero weight for
+    // the columns beyond L) so the 8 loads of a row are in flight together - predicated loads compile to branches that
+    // serialise on the L2 latency
+    for (int l0 = 0; l0 < L; l0 += 256) {
+        float wv[8]; int li[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int l = l0 + lane + 32 * u;
+            li[u] = min(l, L - 1);
+            const float t = __ldg(wr + li[u]);
+            wv[u] = l < L ? t : 0.f;
+        }
+        for (int m = 0; m < M; ++m) {
+            const float* zr = z + (size_t)m * L;
+            float acc = 0.f;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc = fmaf(__ldg(zr + li[u]), wv[u], acc);
+            acc = warp_sum(acc);
+            if ((m & 31) == lane) { if (m < 32) v[0] += acc; else v[1] += acc; }
+        }
     }
     const bool has0 = lane < M, has1 = lane + 32 < M;
     if (has0) y_raw[(size_t)lane * C + c] = v[0];
@@ -177,14 +191,17 @@ vec_layer_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ z, 
             if (lane + 32 * h < M) dy_raw_out[(size_t)(lane + 32 * h) * C + c] = d[h];
     }
     if (dw != nullptr) {
-        for (int l0 = 0; l0 < L; l0 += 128) {             // 4 columns per lane per pass
+        for (int l0 = 0; l0 < L; l0 += 128) {             // 4 columns per lane per pass (unconditional, clamped loads)
             float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            int li[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) li[u] = min(l0 + lane + 32 * u, L - 1);
+#pragma unroll 4
             for (int m = 0; m < M; ++m) {
                 const float g = __shfl_sync(0xffffffffu, m < 32 ? d[0] : d[1], m & 31);
-                const float* zr = z + (size_t)m * L + l0 + lane;
+                const float* zr = z + (size_t)m * L;
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (l0 + lane + 32 * u < L) acc[u] = fmaf(g, __ldg(zr + 32 * u), acc[u]);
+                for (int u = 0; u < 4; ++u) acc[u] = fmaf(g, __ldg(zr + li[u]), acc[u]);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -207,11 +224,15 @@ vec_layer_dz_kernel(const float* __restrict__ dy_raw, const float* __restrict__ 
         float acc[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-        for (int c = wg; c < C; c += 8) {
-            const float wv = l < L ? __ldg(w + (size_t)c * L + l) : 0.f;
+        const int lc = min(l, L - 1);
+        int row[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-                if (m0 + j < M) acc[j] = fmaf(__ldg(dy_raw + (size_t)(m0 + j) * C + c), wv, acc[j]);   // warp-uniform address
+        for (int j = 0; j < 16; ++j) row[j] = min(m0 + j, M - 1);          // clamped: loads stay unconditional
+#pragma unroll 2
+        for (int c = wg; c < C; c += 8) {
+            const float wv = __ldg(w + (size_t)c * L + lc);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] = fmaf(__ldg(dy_raw + (size_t)row[j] * C + c), wv, acc[j]);   // warp-uniform address
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) part[wg][j][lane] = acc[j];

@@ -13,6 +13,7 @@ calculate_uncertainty_metrics).
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Union
 
@@ -23,12 +24,16 @@ from .ops import Act
 
 BN_EPS = 1e-5
 RESNET34_STAGES = (3, 4, 6, 3)
+# same switch the C side reads (vu_conv_halo.cu): with the tap-reuse kernel off there is no fused output conv either
+_NO_HALO = os.environ.get("VU_NO_HALO", "0") not in ("", "0")
 
 
 @dataclass
 class ConstVec:
-    """A spatially constant map, stored as one fp32 vector per image: v[D, C]."""
+    """A spatially constant map, stored as one fp32 vector per image: v[D, C]. `hw` is the size the reference's map would
+    have (needed only when no skip connection defines the output size of the next DecoderBlock: use_skip=False)."""
     v: torch.Tensor
+    hw: Optional[tuple] = None
 
 
 def _latent_flags(latent_injection):
@@ -80,7 +85,7 @@ class ConvUnit:
 
     def can_fuse_output(self, x: Act) -> bool:
         """vu_conv_args.fuse_out: 3x3 s1 p1, Cout 64/128, map at least 96 wide."""
-        return self.k == 3 and self.stride == 1 and self.cout in (64, 128) and x.W >= 96
+        return self.k == 3 and self.stride == 1 and self.cout in (64, 128) and x.W >= 96 and not _NO_HALO
 
 
 class VecUnit:
@@ -181,7 +186,7 @@ class ZInitialUnit:
 
     def __call__(self, z: Union[ConstVec, Act]) -> Union[ConstVec, Act]:
         if isinstance(z, ConstVec):
-            return ConstVec(self.vec(z.v, relu=True))
+            return ConstVec(self.vec(z.v, relu=True), z.hw)
         if self.conv is None:
             self.conv = ConvUnit(self.sd, self.prefix + "0.", self.prefix + "1.", 1, 1, 0, self.dev, self.dtype)
         return self.conv(z, relu=True)
@@ -224,9 +229,13 @@ class DecoderBlockUnit:
             D, cx = x.N, x.C
         if skip is not None:
             H, W = skip.H, skip.W
+        elif isinstance(x, Act):
+            H, W = x.H * 2, x.W * 2                       # unet_resnet.py:75-76
         else:
-            assert isinstance(x, Act), "constant x needs a skip to define the output size"
-            H, W = x.H * 2, x.W * 2
+            # use_skip=False with a bottleneck latent: x = z_initial(z_spatial) is a constant map of the size of the smallest
+            # encoder feature (unet_resnet.py:221-229), doubled by this block like any other input
+            assert x.hw is not None, "constant x without a skip needs its map size (ConstVec.hw)"
+            H, W = x.hw[0] * 2, x.hw[1] * 2
         has_skip = skip is not None and self.use_skip
         cs = skip.C if has_skip else 0
         cz = L if self.zproj is not None else 0
@@ -345,7 +354,7 @@ class ResNetVAEEngine:
 
     def decode(self, feats: Sequence[Act], z_dec: torch.Tensor, honour_use_skip: bool = True) -> torch.Tensor:
         """z_dec fp32 [D, L] with D = B * rep (sample-minor) -> logits fp32 [D, n_classes, H/2, W/2]."""
-        z = ConstVec(z_dec.contiguous())
+        z = ConstVec(z_dec.contiguous(), (feats[-1].H, feats[-1].W))
         D = z_dec.shape[0]
         if self.use_bottleneck:
             x: Union[Act, ConstVec] = self.z_initial(z)
