@@ -46,6 +46,64 @@ __device__ __forceinline__ float warp_column_sums32(float (&a)[32], int lane) {
     return a[0];
 }
 
+// ------------------------------------------------------------------ BatchNorm statistics in the conv epilogues
+// Per-channel sum / sum of squares of a 32-pixel x 32-channel chunk held one ROW per lane as 16 packed 16-bit pairs (the
+// values exactly as stored). The chunk is transposed through a 2 KB per-warp scratch (rows of 64 B, 16-byte pieces XOR-
+// swizzled by (row >> 1) & 3: conflict-free both ways): lane = (h, cp) then sums the column pair (2cp, 2cp+1) over the 16 rows of
+// parity h, one shuffle combines the two halves, and lanes 0..15 add the result into this warp's OWN slice of the per-CTA
+// partial arrays with plain read-modify-writes - each (TMEM lane quarter, 32-column chunk) belongs to exactly one warp, so
+// there are no atomics and the summation order is fixed. ~120 instructions per chunk; the first version (two 31-shuffle
+// butterflies + fp64 shared-memory atomics, which compile to CAS loops) cost ~330 and made the training convs epilogue-bound.
+constexpr int kEpiStatMaxCout = 512;
+constexpr int kEpiStatBytes = 4 * 2 * kEpiStatMaxCout * 4;     // [4 lane quarters][sum, sumsq][Cout] fp32
+constexpr int kEpiScratchBytes = 32 * 64;                       // per epilogue warp
+__device__ __forceinline__ void epi_stats_chunk(const uint32_t (&outw)[16], bool valid, int lane, int dtype, uint8_t* scratch,
+                                                float* part_sum, float* part_sq) {
+    uint4* srow = reinterpret_cast<uint4*>(scratch + lane * 64);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        srow[j ^ ((lane >> 1) & 3)] = valid ? make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3])
+                                     : make_uint4(0, 0, 0, 0);
+    __syncwarp();
+    const int h = lane >> 4, cp = lane & 15;
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int r = 2 * k + h;
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(scratch + r * 64 + (((cp >> 2) ^ (k & 3)) << 4) + ((cp & 3) << 2));
+        const float2 f = unpack2(w, dtype);
+        s0 += f.x; s1 += f.y;
+        q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
+    }
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+    q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+    __syncwarp();                                   // the scratch is rewritten by this warp's next chunk
+    if (lane < 16) {
+        float2* ps = reinterpret_cast<float2*>(part_sum + 2 * cp);
+        float2* pq = reinterpret_cast<float2*>(part_sq + 2 * cp);
+        float2 a = *ps, b = *pq;
+        a.x += s0; a.y += s1; b.x += q0; b.y += q1;
+        *ps = a; *pq = b;
+    }
+}
+// After the block-wide barrier at the end of a kernel: combine the four quarters in a fixed order in fp64 and flush this
+// CTA's partials with one fp64 atomic per channel and statistic.
+__device__ __forceinline__ void epi_stats_flush(const float* s_stat, double* stat_sums, int cout, int tid, int nthreads,
+                                                int stride = kEpiStatMaxCout) {
+    for (int c = tid; c < cout; c += nthreads) {
+        double a = 0.0, b = 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            a += (double)s_stat[(q * 2) * stride + c];
+            b += (double)s_stat[(q * 2 + 1) * stride + c];
+        }
+        if (a != 0.0 || b != 0.0) {
+            atomicAdd(&stat_sums[c], a);
+            atomicAdd(&stat_sums[cout + c], b);
+        }
+    }
+}
+
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
                                     CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,

@@ -14,7 +14,9 @@
 //
 //   GEMM view per tile:  HT accumulators [128 pixels x BN], BN = Cout, K = 9 taps x Cin.
 //   Warps:  0 = A (input tile) TMA producer, 1 = TMEM allocator + MMA issuer, 2 = B (filter tap) TMA
-//           producer, 3..6 = epilogue (TMEM -> scale/bias/residual/ReLU -> 16-bit NHWC channel slice).
+//           producer, 3..10 = epilogue (TMEM -> scale/bias/residual/ReLU -> 16-bit NHWC channel slice): two warps per
+//           TMEM lane quarter, taking the even / odd output rows of a tile (one warp per scheduler could not drain a
+//           4-row x 64-channel tile in the ~5k clk its MMAs take: ncu r2a, tensor pipe 16 % on the 64 -> 64 @128^2 layers).
 //   Rings:  A: 2 stages of (HT+2)*130 rows; B: one [BN x 64ch] filter tap per stage; TMEM: 2 sets of HT
 //           accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "vu_conv_common.cuh"
@@ -24,7 +26,8 @@ namespace vu {
 
 constexpr int kHaloWT = 128;               // output pixels per tile row = UMMA M
 constexpr int kHaloPitch = kHaloWT + 2;    // input pixels per tile row (1-pixel halo each side)
-constexpr int kHaloThreads = 224;
+constexpr int kHaloEpiWarps = 8;
+constexpr int kHaloThreads = 96 + 32 * kHaloEpiWarps;
 
 struct HaloParams {
     int n_img, h, w;
@@ -42,25 +45,29 @@ struct HaloParams {
 // PAIR: cluster of two CTAs, tcgen05 cta_group::2 - each CTA stages its own pixel tile and HALF of the filter rows of a tap;
 // the leader's M = 256 MMA reads both (see conv_igemm_pair_kernel). Per MMA an SM then reads 4 KB + BN*16 B of smem operands
 // instead of 4 KB + BN*32 B: the Cout = 64 layers are bound by that read port.
-template <int BN, int HT, bool PAIR = false> struct HaloCfg {
+// STATS: the training flavour that accumulates BatchNorm statistics of the stored outputs (per-CTA partials [4 quarters][2][BN]
+// fp32 + a 2 KB transpose scratch per epilogue warp, vu_conv_common.cuh); it runs with HT = 2.
+template <int BN, int HT, bool PAIR = false, bool STATS = false> struct HaloCfg {
     static constexpr int kARows = (HT + 2) * kHaloPitch;
     static constexpr int kABytes = kARows * 128;                       // what one TMA box delivers
     static constexpr int kAStride = (kABytes + 1023) / 1024 * 1024;   // stage pitch (1024-aligned: swizzle atom)
     static constexpr int kAStages = 2;
     static constexpr int kBBytes = (PAIR ? BN / 2 : BN) * 128;
-    static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : 5;
+    static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : ((STATS && !PAIR) ? 3 : 5);
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4 + 2 * BN * 8;
+    static constexpr int kStatBytes = STATS ? (4 * 2 * BN * 4 + kHaloEpiWarps * kEpiScratchBytes) : 0;
+    static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4 + kStatBytes;
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 232448, "smem budget");
+    static_assert(!STATS || HT == 2, "the statistics flavour runs with two rows per tile");
 };
 
-template <int BN, int HT, bool PAIR>
+template <int BN, int HT, bool PAIR, bool STATS>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                     const HaloParams p) {
-    using Cfg = HaloCfg<BN, HT, PAIR>;
+    using Cfg = HaloCfg<BN, HT, PAIR, STATS>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -81,8 +88,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
     float* s_bias = s_scale + BN;
     float* s_fw = s_bias + BN;
-    double* s_sum = reinterpret_cast<double*>(s_fw + BN);   // per-CTA partial BatchNorm statistics of the stored outputs
-    double* s_sq = s_sum + BN;                              // (fp64: see vu_conv_igemm.cu)
+    float* s_stat = s_fw + BN;                              // STATS: [4 quarters][2][BN] fp32 partial BatchNorm statistics
+    uint8_t* s_scratch = reinterpret_cast<uint8_t*>(s_stat + 4 * 2 * BN);   // + a 2 KB transpose scratch per epilogue warp
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -99,7 +106,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < Cfg::kAStages; ++s) { mbar_init(a_full(s), PAIR ? 2 : 1); mbar_init(a_empty(s), 1); }
         for (int s = 0; s < Cfg::kBStages; ++s) { mbar_init(b_full(s), PAIR ? 2 : 1); mbar_init(b_empty(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(t_full(a), 1); mbar_init(t_empty(a), PAIR ? 256 : 128); }
+        for (int a = 0; a < 2; ++a) { mbar_init(t_full(a), 1); mbar_init(t_empty(a), (PAIR ? 2 : 1) * 32 * kHaloEpiWarps); }
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -110,8 +117,9 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
         s_fw[c] = p.fuse_w ? p.fuse_w[c] : 0.0f;
-        s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
+    if constexpr (STATS)
+        for (int c = threadIdx.x; c < 4 * 2 * BN; c += kHaloThreads) s_stat[c] = 0.0f;
     tc_fence_before();
     if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
@@ -228,12 +236,15 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             __syncwarp();
         }
     } else if (warp >= 3) {
-        // ===================== epilogue: warps 3..6 cover the four TMEM lane quarters =====================
+        // ===================== epilogue: warps 3..10, two per TMEM lane quarter (even / odd rows of the tile) ==========
         const int q = warp & 3;
+        const int half = (warp - 3) >> 2;
         const int m = q * 32 + lane;              // pixel within the tile row
         const bool has_res = p.residual != nullptr, relu = p.relu != 0, store_y = p.y != nullptr;
         const bool fuse = p.fuse_out != nullptr;  // 1x1 Cout->1 output conv on the fp32 activations (final_conv)
+        const bool affine = p.scale != nullptr || p.bias != nullptr;
         const int dtype = p.dtype;
+        uint8_t* scratch = s_scratch + (warp - 3) * kEpiScratchBytes;
         uint32_t tcount = 0;
         const uint32_t leader_t_empty0 = PAIR ? mapa_cluster(t_empty(0), 0) : 0u;
         for (int item = item0; item < num_items; item += item_step, ++tcount) {
@@ -247,7 +258,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
             mbar_wait(t_full(acc), accph);
             tc_fence_after();
 #pragma unroll 1
-            for (int j = 0; j < (tile < p.num_tiles ? HT : 0); ++j) {      // PAIR: the peer's tile past the end is empty
+            for (int j = half; j < (tile < p.num_tiles ? HT : 0); j += 2) {   // PAIR: the peer's tile past the end is empty
                 const int ho = hb * HT + j;
                 const bool valid = (wo < p.w) && (ho < p.h);
                 const size_t pix = (static_cast<size_t>(nb) * p.h + ho) * p.w + wo;
@@ -259,37 +270,47 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                     tmem_ld_32x32b_x32(taddr + c * 32, r);
                     const int ch0 = c * 32;
                     uint4 rv[4];
-                    if (has_res && valid) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.res_ctot + p.res_coff + ch0);
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) rv[i] = __ldg(rp + i);
-                    } else {
+                    if (has_res) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) rv[i] = make_uint4(0, 0, 0, 0);
+                        if (valid) {
+                            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.res_ctot + p.res_coff + ch0);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) rv[i] = __ldg(rp + i);
+                        }
                     }
-                    float4 pb[8];
+                    tmem_ld_wait();
                     if (p.pos_bias != nullptr) {
                         const int hc = min(ho, p.h - 1), wc = min(wo, p.w - 1);
                         const int cls = (hc == 0 ? 0 : (hc == p.h - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.w - 1 ? 2 : 1));
                         const float4* pp = reinterpret_cast<const float4*>(p.pos_bias + (static_cast<size_t>(nb) * 9 + cls) * BN + ch0);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) pb[i] = __ldg(pp + i);
-                    }
-                    tmem_ld_wait();
-                    if (p.pos_bias != nullptr) {
-#pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) + pb[i].x);
-                            r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) + pb[i].y);
-                            r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) + pb[i].z);
-                            r[4 * i + 3] = __float_as_uint(__uint_as_float(r[4 * i + 3]) + pb[i].w);
+                            const float4 b = __ldg(pp + i);
+                            r[4 * i] = __float_as_uint(__uint_as_float(r[4 * i]) + b.x);
+                            r[4 * i + 1] = __float_as_uint(__uint_as_float(r[4 * i + 1]) + b.y);
+                            r[4 * i + 2] = __float_as_uint(__uint_as_float(r[4 * i + 2]) + b.z);
+                            r[4 * i + 3] = __float_as_uint(__uint_as_float(r[4 * i + 3]) + b.w);
                         }
                     }
-                    const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
                     float v[32];
+                    if (affine) {
+                        const float4* sc4 = reinterpret_cast<const float4*>(s_scale + ch0);
+                        const float4* sb4 = reinterpret_cast<const float4*>(s_bias + ch0);
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) v[i] = fmaf(__uint_as_float(r[i]), s_scale[ch0 + i], s_bias[ch0 + i]);
+                        for (int i = 0; i < 8; ++i) {
+                            const float4 a = sc4[i], b = sb4[i];
+                            v[4 * i] = fmaf(__uint_as_float(r[4 * i]), a.x, b.x);
+                            v[4 * i + 1] = fmaf(__uint_as_float(r[4 * i + 1]), a.y, b.y);
+                            v[4 * i + 2] = fmaf(__uint_as_float(r[4 * i + 2]), a.z, b.z);
+                            v[4 * i + 3] = fmaf(__uint_as_float(r[4 * i + 3]), a.w, b.w);
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                    }
                     if (has_res) {
+                        const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
 #pragma unroll
                         for (int i = 0; i < 16; ++i) {
                             const float2 rr = unpack2(rw[i], dtype);
@@ -304,7 +325,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                         for (int i = 0; i < 32; ++i) dot = fmaf(v[i], s_fw[ch0 + i], dot);
                     }
-                    if (valid && store_y) {
+                    if (store_y) {
                         uint32_t outw[16];
                         if (dtype == 0) {
 #pragma unroll
@@ -313,22 +334,17 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 #pragma unroll
                             for (int i = 0; i < 16; ++i) outw[i] = pack2(v[2 * i], v[2 * i + 1], 1);
                         }
-                        uint4* op = reinterpret_cast<uint4*>(p.y + pix * p.y_ctot + p.y_coff + ch0);
+                        if (valid) {
+                            uint4* op = reinterpret_cast<uint4*>(p.y + pix * p.y_ctot + p.y_coff + ch0);
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            op[i] = make_uint4(outw[4 * i], outw[4 * i + 1], outw[4 * i + 2], outw[4 * i + 3]);
-                    }
-                    if (p.stat_sums != nullptr) {      // statistics of the values as stored (rounded to 16 bit)
-                        float a[32], b[32];
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            const float2 f = unpack2(pack2(v[2 * i], v[2 * i + 1], dtype), dtype);
-                            a[2 * i] = valid ? f.x : 0.0f; a[2 * i + 1] = valid ? f.y : 0.0f;
-                            b[2 * i] = a[2 * i] * a[2 * i]; b[2 * i + 1] = a[2 * i + 1] * a[2 * i + 1];
+                            for (int i = 0; i < 4; ++i)
+                                op[i] = make_uint4(outw[4 * i], outw[4 * i + 1], outw[4 * i + 2], outw[4 * i + 3]);
                         }
-                        const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
-                        atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
-                        atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
+                        if constexpr (STATS) {
+                            if (p.stat_sums != nullptr)      // statistics of the values as stored (rounded to 16 bit)
+                                epi_stats_chunk(outw, valid, lane, dtype, scratch, s_stat + (q * 2) * BN + ch0,
+                                                s_stat + (q * 2 + 1) * BN + ch0);
+                        }
                     }
                 }
                 if (fuse && valid) p.fuse_out[pix] = dot + p.fuse_bias;
@@ -340,28 +356,21 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
 
     tc_fence_before();
     if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
-    if (p.stat_sums != nullptr) {
-        for (int c = threadIdx.x; c < BN; c += blockDim.x) {
-            const double a = s_sum[c], b = s_sq[c];
-            if (a != 0.0 || b != 0.0) {
-                atomicAdd(&p.stat_sums[c], a);
-                atomicAdd(&p.stat_sums[BN + c], b);
-            }
-        }
-    }
+    if constexpr (STATS)
+        if (p.stat_sums != nullptr) epi_stats_flush(s_stat, p.stat_sums, BN, threadIdx.x, kHaloThreads, BN);
     if (warp == 1) {
         tc_fence_after();
         if constexpr (PAIR) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base); else tmem_dealloc<Cfg::kTmemCols>(tmem_base);
     }
 }
 
-template <int BN, int HT>
+template <int BN, int HT, bool STATS>
 static int launch_halo(const CUtensorMap& xm, const CUtensorMap& wm, const HaloParams& hp, int max_ctas,
                        cudaStream_t stream) {
-    using Cfg = HaloCfg<BN, HT, false>;
+    using Cfg = HaloCfg<BN, HT, false, STATS>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, false, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(halo): %s", cudaGetErrorString(e));
         attr_set = true;
@@ -369,17 +378,17 @@ static int launch_halo(const CUtensorMap& xm, const CUtensorMap& wm, const HaloP
     int grid = hp.num_tiles;
     const int cap = (max_ctas > 0) ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    conv3x3_halo_kernel<BN, HT, false><<<grid, kHaloThreads, Cfg::kSmemBytes, stream>>>(xm, wm, hp);
+    conv3x3_halo_kernel<BN, HT, false, STATS><<<grid, kHaloThreads, Cfg::kSmemBytes, stream>>>(xm, wm, hp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv3x3_halo launch: %s", cudaGetErrorString(e));
     return 1;
 }
 
 // CTA pairs (cluster of 2 along x); `wm` must have a box of BN/2 filter rows.
-template <int BN, int HT>
+template <int BN, int HT, bool STATS>
 static int launch_halo_pair(const CUtensorMap& xm, const CUtensorMap& wm, const HaloParams& hp, int max_ctas,
                             cudaStream_t stream) {
-    using Cfg = HaloCfg<BN, HT, true>;
+    using Cfg = HaloCfg<BN, HT, true, STATS>;
     static int max_clusters = -1;
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr[1];
@@ -388,12 +397,12 @@ static int launch_halo_pair(const CUtensorMap& xm, const CUtensorMap& wm, const 
     cfg.blockDim = dim3(kHaloThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = stream;
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (max_clusters < 0) {
-        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_halo_kernel<BN, HT, true, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute(halo pair): %s", cudaGetErrorString(e));
         cfg.gridDim = dim3(2 * (num_sms() / 2));
         int n = 0;
-        e = cudaOccupancyMaxActiveClusters(&n, conv3x3_halo_kernel<BN, HT, true>, &cfg);
+        e = cudaOccupancyMaxActiveClusters(&n, conv3x3_halo_kernel<BN, HT, true, STATS>, &cfg);
         if (e != cudaSuccess || n < 1) return set_error(VU_ERR_CUDA, "cudaOccupancyMaxActiveClusters(halo): %s", cudaGetErrorString(e));
         max_clusters = n;
     }
@@ -402,7 +411,7 @@ static int launch_halo_pair(const CUtensorMap& xm, const CUtensorMap& wm, const 
     if (max_ctas > 0 && max_ctas / 2 < cap) cap = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
     if (pairs > cap) pairs = cap;
     cfg.gridDim = dim3(2 * pairs);
-    cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_halo_kernel<BN, HT, true>, xm, wm, hp);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv3x3_halo_kernel<BN, HT, true, STATS>, xm, wm, hp);
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv3x3_halo pair launch: %s", cudaGetErrorString(e));
     return 1;
 }
@@ -422,6 +431,7 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
         ht = (pad4 * 10 <= pad2 * 11) ? 4 : 2;
         static const int force_ht = getenv("VU_HALO_HT") ? atoi(getenv("VU_HALO_HT")) : 0;
         if (force_ht == 2 || force_ht == 4) ht = force_ht;
+        if (a->stat_sums != nullptr) ht = 2;         // the statistics flavour (shared-memory budget)
     }
     HaloParams hp{};
     hp.n_img = a->N; hp.h = a->H; hp.w = a->W;
@@ -460,18 +470,24 @@ int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream) {
         int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
         if (rc) return rc;
     }
+    if (hp.stat_sums != nullptr) {                  // training flavour (ht was forced to 2 above)
+        if (pair) return a->Cout == 64 ? launch_halo_pair<64, 2, true>(xm, wm, hp, a->max_ctas, stream)
+                                       : launch_halo_pair<128, 2, true>(xm, wm, hp, a->max_ctas, stream);
+        return a->Cout == 64 ? launch_halo<64, 2, true>(xm, wm, hp, a->max_ctas, stream)
+                             : launch_halo<128, 2, true>(xm, wm, hp, a->max_ctas, stream);
+    }
     if (pair) {
         if (a->Cout == 64) {
-            if (ht == 4) return launch_halo_pair<64, 4>(xm, wm, hp, a->max_ctas, stream);
-            return launch_halo_pair<64, 2>(xm, wm, hp, a->max_ctas, stream);
+            if (ht == 4) return launch_halo_pair<64, 4, false>(xm, wm, hp, a->max_ctas, stream);
+            return launch_halo_pair<64, 2, false>(xm, wm, hp, a->max_ctas, stream);
         }
-        return launch_halo_pair<128, 2>(xm, wm, hp, a->max_ctas, stream);
+        return launch_halo_pair<128, 2, false>(xm, wm, hp, a->max_ctas, stream);
     }
     if (a->Cout == 64) {
-        if (ht == 4) return launch_halo<64, 4>(xm, wm, hp, a->max_ctas, stream);
-        return launch_halo<64, 2>(xm, wm, hp, a->max_ctas, stream);
+        if (ht == 4) return launch_halo<64, 4, false>(xm, wm, hp, a->max_ctas, stream);
+        return launch_halo<64, 2, false>(xm, wm, hp, a->max_ctas, stream);
     }
-    return launch_halo<128, 2>(xm, wm, hp, a->max_ctas, stream);
+    return launch_halo<128, 2, false>(xm, wm, hp, a->max_ctas, stream);
 }
 
 }  // namespace vu

@@ -22,7 +22,13 @@ constexpr int kBlockK = 64;                       // channels per K block (128 B
 constexpr int kABytes = kTileM * kBlockK * 2;     // 16 KB
 constexpr int kMaxTaps = 9;
 constexpr int kMaxCout = 1024;
-constexpr int kThreads = 192;
+// Warps: 0 = TMA producer, 1 = TMEM allocator + MMA issuer, 2..9 = epilogue. EIGHT epilogue warps (two per TMEM lane quarter,
+// taking the even / odd 32-column chunks of a tile): with K = 9 * 64..256 the MMAs of a 128 x 128 tile take ~4.6k clk, and one
+// warp per scheduler needed ~12k clk to drain it (ncu r2b: the MMA warp sat on the accumulator-empty barrier, tensor pipe 24 %).
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 64 + 32 * kEpiWarps;
+constexpr int kStatMaxCout = kEpiStatMaxCout;     // BatchNorm statistics in the epilogue: Cout <= 512
+constexpr int kSmemLimit = 232448;
 
 struct ConvKParams {
     int n_img, ho, wo;             // output-resolution grid the M tiles cover
@@ -41,22 +47,29 @@ struct ConvKParams {
     double* stat_sums;             // optional [2*cout] fp64: sum / sum of squares of the stored outputs
 };
 
-template <int BN> struct ConvCfg {
+// STATS: the kernel flavour that accumulates BatchNorm statistics (training): it carries the per-CTA partial sums and the
+// per-warp transpose scratch in shared memory and therefore one or two pipeline stages fewer.
+template <int BN, bool STATS> struct ConvCfg {
     static constexpr int kBBytes = BN * kBlockK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (BN == 256) ? 4 : (BN == 128) ? 6 : 8;
-    static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
     static constexpr int kBarBytes = 1024;  // barriers + tmem ptr
-    static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes +
-                                      2 * kMaxCout * 4 + 2 * kMaxCout * 8;   // scale, bias; per-CTA fp64 statistic partials
+    static constexpr int kTailBytes = kBarBytes + 2 * kMaxCout * 4 + (STATS ? kEpiStatBytes + kEpiWarps * kEpiScratchBytes : 0);
+    static constexpr int kMaxStages = (kSmemLimit - 1024 - kTailBytes) / kStageBytes;
+    static constexpr int kStages = kMaxStages > 8 ? 8 : kMaxStages;
+    static constexpr int kTmemCols = (2 * BN < 32) ? 32 : 2 * BN;
+    static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kTailBytes;
+    static_assert(kStages >= 3, "pipeline depth");
 };
 
 // Epilogue of one 128-pixel x BN tile: TMEM -> registers -> (pos_bias, scale/bias, residual, ReLU) -> 16-bit NHWC store,
-// plus the optional BatchNorm statistics of the stored values. Called by the four epilogue warps (q = TMEM lane quarter);
-// `taddr` addresses this warp's lanes of the accumulator.
-template <int BN>
-__device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_t taddr, int n_tile, int m_tile, int q, int lane,
-                                                   const float* s_scale, const float* s_bias, double* s_sum, double* s_sq) {
+// plus the optional BatchNorm statistics of the stored values. Called by the eight epilogue warps: q = TMEM lane quarter,
+// `half` = which 32-column chunks (even / odd) this warp drains; `taddr` addresses this warp's lanes of the accumulator.
+// Every optional piece sits behind a warp-uniform BRANCH (not per-element predication): a raw training conv or a data
+// gradient executes only TMEM load, pack and store.
+template <int BN, bool STATS>
+__device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_t taddr, int n_tile, int m_tile, int q, int half,
+                                                   int lane, const float* s_scale, const float* s_bias, float* s_stat,
+                                                   uint8_t* scratch) {
     const int m = q * 32 + lane;              // row of the tile = pixel
     const int w_l = m % p.wt;
     const int h_l = (m / p.wt) % p.ht;
@@ -69,25 +82,27 @@ __device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_
     const size_t opix = (static_cast<size_t>(ni) * p.out_h + (ho * p.out_up + p.out_dh)) * p.out_w +
                         (wo * p.out_up + p.out_dw);
     const size_t rpix = (static_cast<size_t>(ni) * p.ho + ho) * p.wo + wo;
+    const bool affine = p.scale != nullptr || p.bias != nullptr;
+    const bool has_res = p.residual != nullptr, relu = p.relu != 0;
+    const int dtype = p.dtype;
+    constexpr int kChunks = BN / 32;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = half; c < kChunks; c += 2) {
         const int ch0 = n_tile * BN + c * 32;
         if (ch0 >= p.cout) break;             // partial last N tile (Cout is a multiple of 32; warp-uniform)
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        uint32_t outw[16];
         uint4 rv[4];
-        if (p.residual != nullptr && valid) {
-            const uint4* rp = reinterpret_cast<const uint4*>(
-                p.residual + rpix * p.res_ctot + p.res_coff + ch0);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
-        } else {
+        if (has_res) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) rv[j] = make_uint4(0, 0, 0, 0);
+            if (valid) {
+                const uint4* rp = reinterpret_cast<const uint4*>(p.residual + rpix * p.res_ctot + p.res_coff + ch0);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
+            }
         }
-        const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+        tmem_ld_wait();
         if (p.pos_bias != nullptr) {
             const int hc = min(ho, p.ho - 1), wc = min(wo, p.wo - 1), nc = min(ni, p.n_img - 1);
             const int cls = (hc == 0 ? 0 : (hc == p.ho - 1 ? 2 : 1)) * 3 + (wc == 0 ? 0 : (wc == p.wo - 1 ? 2 : 1));
@@ -101,16 +116,38 @@ __device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_
                 r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + b.w);
             }
         }
+        if (affine) {
+            const float4* sc4 = reinterpret_cast<const float4*>(s_scale + ch0);
+            const float4* sb4 = reinterpret_cast<const float4*>(s_bias + ch0);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            float v0 = __uint_as_float(r[2 * j]) * s_scale[ch0 + 2 * j] + s_bias[ch0 + 2 * j];
-            float v1 = __uint_as_float(r[2 * j + 1]) * s_scale[ch0 + 2 * j + 1] + s_bias[ch0 + 2 * j + 1];
-            if (p.residual != nullptr) {
-                float2 rr = unpack2(rw[j], p.dtype);
-                v0 += rr.x; v1 += rr.y;
+            for (int j = 0; j < 8; ++j) {
+                const float4 a = sc4[j], b = sb4[j];
+                r[4 * j] = __float_as_uint(fmaf(__uint_as_float(r[4 * j]), a.x, b.x));
+                r[4 * j + 1] = __float_as_uint(fmaf(__uint_as_float(r[4 * j + 1]), a.y, b.y));
+                r[4 * j + 2] = __float_as_uint(fmaf(__uint_as_float(r[4 * j + 2]), a.z, b.z));
+                r[4 * j + 3] = __float_as_uint(fmaf(__uint_as_float(r[4 * j + 3]), a.w, b.w));
             }
-            if (p.relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
-            outw[j] = pack2(v0, v1, p.dtype);
+        }
+        if (has_res) {
+            const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float2 rr = unpack2(rw[j], dtype);
+                r[2 * j] = __float_as_uint(__uint_as_float(r[2 * j]) + rr.x);
+                r[2 * j + 1] = __float_as_uint(__uint_as_float(r[2 * j + 1]) + rr.y);
+            }
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.0f));
+        }
+        uint32_t outw[16];
+        if (dtype == 0) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) outw[j] = pack2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]), 0);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) outw[j] = pack2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]), 1);
         }
         if (valid) {
             uint4* op = reinterpret_cast<uint4*>(p.y + opix * p.y_ctot + p.y_coff + ch0);
@@ -118,27 +155,20 @@ __device__ __forceinline__ void conv_epilogue_tile(const ConvKParams& p, uint32_
             for (int j = 0; j < 4; ++j)
                 op[j] = make_uint4(outw[4 * j], outw[4 * j + 1], outw[4 * j + 2], outw[4 * j + 3]);
         }
-        if (p.stat_sums != nullptr) {          // statistics of the values as stored (16-bit rounded); warp-uniform branch
-            float a[32], b[32];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float2 f = unpack2(outw[j], p.dtype);
-                a[2 * j] = valid ? f.x : 0.0f; a[2 * j + 1] = valid ? f.y : 0.0f;
-                b[2 * j] = a[2 * j] * a[2 * j]; b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
-            }
-            const float cs = warp_column_sums32(a, lane), cq = warp_column_sums32(b, lane);
-            atomicAdd(&s_sum[ch0 + lane], static_cast<double>(cs));
-            atomicAdd(&s_sq[ch0 + lane], static_cast<double>(cq));
+        if constexpr (STATS) {
+            if (p.stat_sums != nullptr)        // statistics of the values as stored (16-bit rounded); warp-uniform branch
+                epi_stats_chunk(outw, valid, lane, dtype, scratch, s_stat + (q * 2) * kStatMaxCout + ch0,
+                                s_stat + (q * 2 + 1) * kStatMaxCout + ch0);
         }
     }
 }
 
-template <int BN>
+template <int BN, bool STATS>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                   const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a3,
                   const __grid_constant__ CUtensorMap map_w, const ConvKParams p) {
-    using Cfg = ConvCfg<BN>;
+    using Cfg = ConvCfg<BN, STATS>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -153,11 +183,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
     float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
     float* s_bias = s_scale + kMaxCout;
-    // per-CTA partial sums of the stored outputs (BatchNorm statistics). fp64: the warp-level column sums are computed in
-    // a fixed order, so everything whose order depends on scheduling is accumulated in double and the result is
-    // reproducible to ~1e-16 (a train-mode BatchNorm over a handful of values amplifies fp32-level noise)
-    double* s_sum = reinterpret_cast<double*>(s_bias + kMaxCout);
-    double* s_sq = s_sum + kMaxCout;
+    // STATS: per-CTA partial BatchNorm statistics [4 quarters][2][kStatMaxCout] fp32 + a 2 KB transpose scratch per epilogue
+    // warp (vu_conv_common.cuh: epi_stats_chunk)
+    float* s_stat = s_bias + kMaxCout;
+    uint8_t* s_scratch = reinterpret_cast<uint8_t*>(s_stat) + kEpiStatBytes;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -166,7 +195,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         tma_prefetch_desc(&map_a0);
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 128); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 32 * kEpiWarps); }
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -176,8 +205,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
     for (int c = threadIdx.x; c < p.cout; c += kThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
-        s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
+    if constexpr (STATS)
+        for (int c = threadIdx.x; c < kEpiStatBytes / 4; c += kThreads) s_stat[c] = 0.0f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -252,8 +282,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
             }
         }
     } else {
-        // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+        // ===================== epilogue (8 warps: 2 per TMEM lane quarter) =====================
         const int q = warp & 3;                   // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;         // even / odd 32-column chunks
+        uint8_t* scratch = s_scratch + (warp - 2) * kEpiScratchBytes;
         uint32_t tcount = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
             const int acc = tcount & 1;
@@ -262,8 +294,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
             const int m_tile = tile / p.num_n_tiles;
             mbar_wait(tfull_bar(acc), accph);
             tc_fence_after();
-            conv_epilogue_tile<BN>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q, lane,
-                                   s_scale, s_bias, s_sum, s_sq);
+            conv_epilogue_tile<BN, STATS>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q, half,
+                                          lane, s_scale, s_bias, s_stat, scratch);
             tc_fence_before();
             mbar_arrive(tempty_bar(acc));
         }
@@ -271,11 +303,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
 
     tc_fence_before();
     __syncthreads();
-    if (p.stat_sums != nullptr && blockIdx.x < total_tiles)       // one fp64 flush of this CTA's partials
-        for (int c = threadIdx.x; c < p.cout; c += kThreads) {
-            atomicAdd(&p.stat_sums[c], s_sum[c]);
-            atomicAdd(&p.stat_sums[p.cout + c], s_sq[c]);
-        }
+    if constexpr (STATS)
+        if (p.stat_sums != nullptr) epi_stats_flush(s_stat, p.stat_sums, p.cout, threadIdx.x, kThreads);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<Cfg::kTmemCols>(tmem_base);
@@ -292,22 +321,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
 //   tfull[a]  : per CTA, same multicast commit; each CTA's epilogue drains its own TMEM lanes
 //   tempty[a] : leader's barrier, 256 arrivals (the epilogue threads of both CTAs)
 // ------------------------------------------------------------------------------------------
-template <int BN> struct PairCfg {
+template <int BN, bool STATS> struct PairCfg {
     static constexpr int kBBytes = (BN / 2) * kBlockK * 2;          // this CTA's half of the filter rows
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (BN == 256) ? 6 : 8;
-    static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 1024;
-    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + 2 * kMaxCout * 4 + 2 * kMaxCout * 8;
-    static_assert(kSmemBytes <= 232448, "smem budget");
+    static constexpr int kTailBytes = kBarBytes + 2 * kMaxCout * 4 + (STATS ? kEpiStatBytes + kEpiWarps * kEpiScratchBytes : 0);
+    static constexpr int kMaxStages = (kSmemLimit - 1024 - kTailBytes) / kStageBytes;
+    static constexpr int kStages = kMaxStages > 8 ? 8 : kMaxStages;
+    static constexpr int kTmemCols = 2 * BN;
+    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kTailBytes;
+    static_assert(kStages >= 4, "pipeline depth");
 };
 
-template <int BN>
+template <int BN, bool STATS>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                        const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_a3,
                        const __grid_constant__ CUtensorMap map_w, const ConvKParams p) {
-    using Cfg = PairCfg<BN>;
+    using Cfg = PairCfg<BN, STATS>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -321,8 +352,8 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
         reinterpret_cast<volatile uint32_t*>(smem_al + Cfg::kStages * Cfg::kStageBytes + 8 * (2 * Cfg::kStages + 4));
     float* s_scale = reinterpret_cast<float*>(smem_al + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
     float* s_bias = s_scale + kMaxCout;
-    double* s_sum = reinterpret_cast<double*>(s_bias + kMaxCout);
-    double* s_sq = s_sum + kMaxCout;
+    float* s_stat = s_bias + kMaxCout;
+    uint8_t* s_scratch = reinterpret_cast<uint8_t*>(s_stat) + kEpiStatBytes;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -333,7 +364,7 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
         tma_prefetch_desc(&map_a0);
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(full_bar(s), 2); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 256); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 2 * 32 * kEpiWarps); }
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -343,8 +374,9 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
     for (int c = threadIdx.x; c < p.cout; c += kThreads) {
         s_scale[c] = p.scale ? p.scale[c] : 1.0f;
         s_bias[c] = p.bias ? p.bias[c] : 0.0f;
-        s_sum[c] = 0.0; s_sq[c] = 0.0;
     }
+    if constexpr (STATS)
+        for (int c = threadIdx.x; c < kEpiStatBytes / 4; c += kThreads) s_stat[c] = 0.0f;
     tc_fence_before();
     cluster_sync_all();                                   // barrier inits + TMEM allocation visible to the peer
     tc_fence_after();
@@ -423,8 +455,10 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
             }
         }
     } else {
-        // ===================== epilogue: each CTA drains its own 128 TMEM lanes =====================
+        // ===================== epilogue: each CTA drains its own 128 TMEM lanes (8 warps) =====================
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        uint8_t* scratch = s_scratch + (warp - 2) * kEpiScratchBytes;
         const uint32_t leader_tempty0 = mapa_cluster(tempty_bar(0), 0);
         uint32_t tcount = 0;
         for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
@@ -435,8 +469,8 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
             mbar_wait(tfull_bar(acc), accph);
             tc_fence_after();
             if (m_tile < p.num_m_tiles)
-                conv_epilogue_tile<BN>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q, lane,
-                                       s_scale, s_bias, s_sum, s_sq);
+                conv_epilogue_tile<BN, STATS>(p, tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN, n_tile, m_tile, q,
+                                              half, lane, s_scale, s_bias, s_stat, scratch);
             tc_fence_before();
             mbar_arrive_cluster(leader_tempty0 + 8u * acc);
         }
@@ -444,14 +478,8 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
 
     tc_fence_before();
     cluster_sync_all();                                   // no CTA leaves while the peer may still signal it / read its smem
-    if (p.stat_sums != nullptr)
-        for (int c = threadIdx.x; c < p.cout; c += kThreads) {
-            const double a = s_sum[c], b = s_sq[c];
-            if (a != 0.0 || b != 0.0) {
-                atomicAdd(&p.stat_sums[c], a);
-                atomicAdd(&p.stat_sums[p.cout + c], b);
-            }
-        }
+    if constexpr (STATS)
+        if (p.stat_sums != nullptr) epi_stats_flush(s_stat, p.stat_sums, p.cout, threadIdx.x, kThreads);
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
@@ -478,13 +506,13 @@ static void choose_tile(int n, int h, int w, int* wt_o, int* ht_o, int* nt_o) {
     }
 }
 
-template <int BN>
+template <int BN, bool STATS>
 static int launch_conv(const CUtensorMap* am, const CUtensorMap& wm, const ConvKParams& kp, int max_ctas,
                        cudaStream_t stream) {
-    using Cfg = ConvCfg<BN>;
+    using Cfg = ConvCfg<BN, STATS>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BN, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         attr_set = true;
@@ -493,17 +521,17 @@ static int launch_conv(const CUtensorMap* am, const CUtensorMap& wm, const ConvK
     const int sms = num_sms();
     int cap = (max_ctas > 0) ? max_ctas : sms;
     if (grid > cap) grid = cap;
-    conv_igemm_kernel<BN><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(am[0], am[1], am[2], am[3], wm, kp);
+    conv_igemm_kernel<BN, STATS><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(am[0], am[1], am[2], am[3], wm, kp);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_igemm launch: %s", cudaGetErrorString(e));
     return 0;
 }
 
 // CTA pairs: cluster of 2 along x. -> 0 launched, >0 error; `max_clusters` is how many pairs can be co-resident.
-template <int BN>
+template <int BN, bool STATS>
 static int launch_conv_pair(const CUtensorMap* am, const CUtensorMap& wm, const ConvKParams& kp, int max_ctas,
                             cudaStream_t stream) {
-    using Cfg = PairCfg<BN>;
+    using Cfg = PairCfg<BN, STATS>;
     static int max_clusters = -1;
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr[1];
@@ -512,12 +540,12 @@ static int launch_conv_pair(const CUtensorMap* am, const CUtensorMap& wm, const 
     cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = Cfg::kSmemBytes; cfg.stream = stream;
     cfg.attrs = attr; cfg.numAttrs = 1;
     if (max_clusters < 0) {
-        cudaError_t e = cudaFuncSetAttribute(conv_igemm_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(conv_igemm_pair_kernel<BN, STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         cfg.gridDim = dim3(2 * (num_sms() / 2));
         int n = 0;
-        e = cudaOccupancyMaxActiveClusters(&n, conv_igemm_pair_kernel<BN>, &cfg);
+        e = cudaOccupancyMaxActiveClusters(&n, conv_igemm_pair_kernel<BN, STATS>, &cfg);
         if (e != cudaSuccess || n < 1) return set_error(VU_ERR_CUDA, "cudaOccupancyMaxActiveClusters: %s", cudaGetErrorString(e));
         max_clusters = n;
     }
@@ -526,7 +554,7 @@ static int launch_conv_pair(const CUtensorMap* am, const CUtensorMap& wm, const 
     if (max_ctas > 0 && max_ctas / 2 < cap) cap = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
     if (pairs > cap) pairs = cap;
     cfg.gridDim = dim3(2 * pairs);
-    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_igemm_pair_kernel<BN>, am[0], am[1], am[2], am[3], wm, kp);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_igemm_pair_kernel<BN, STATS>, am[0], am[1], am[2], am[3], wm, kp);
     if (e != cudaSuccess) return set_error(VU_ERR_CUDA, "conv_igemm_pair launch: %s", cudaGetErrorString(e));
     return 0;
 }
@@ -655,13 +683,27 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         int rc = encode_map(&wm, a->dtype, 3, a->w, dims, str, wbox);
         if (rc) return rc;
     }
-    if (pair)
-        return bn == 256 ? launch_conv_pair<256>(am, wm, kp, a->max_ctas, stream)
-                         : launch_conv_pair<128>(am, wm, kp, a->max_ctas, stream);
+    const bool stats = a->stat_sums != nullptr;
+    if (stats && a->Cout > kStatMaxCout)
+        return set_error(VU_ERR_UNSUPPORTED, "conv: stat_sums needs Cout <= %d (got %d): use vu_bn_stats", kStatMaxCout, a->Cout);
+    if (pair) {
+        if (stats) return bn == 256 ? launch_conv_pair<256, true>(am, wm, kp, a->max_ctas, stream)
+                                    : launch_conv_pair<128, true>(am, wm, kp, a->max_ctas, stream);
+        return bn == 256 ? launch_conv_pair<256, false>(am, wm, kp, a->max_ctas, stream)
+                         : launch_conv_pair<128, false>(am, wm, kp, a->max_ctas, stream);
+    }
+    if (stats) {
+        switch (bn) {
+            case 256: return launch_conv<256, true>(am, wm, kp, a->max_ctas, stream);
+            case 128: return launch_conv<128, true>(am, wm, kp, a->max_ctas, stream);
+            case 64: return launch_conv<64, true>(am, wm, kp, a->max_ctas, stream);
+            default: return launch_conv<32, true>(am, wm, kp, a->max_ctas, stream);
+        }
+    }
     switch (bn) {
-        case 256: return launch_conv<256>(am, wm, kp, a->max_ctas, stream);
-        case 128: return launch_conv<128>(am, wm, kp, a->max_ctas, stream);
-        case 64: return launch_conv<64>(am, wm, kp, a->max_ctas, stream);
-        default: return launch_conv<32>(am, wm, kp, a->max_ctas, stream);
+        case 256: return launch_conv<256, false>(am, wm, kp, a->max_ctas, stream);
+        case 128: return launch_conv<128, false>(am, wm, kp, a->max_ctas, stream);
+        case 64: return launch_conv<64, false>(am, wm, kp, a->max_ctas, stream);
+        default: return launch_conv<32, false>(am, wm, kp, a->max_ctas, stream);
     }
 }

@@ -182,17 +182,27 @@ bn_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const fl
             }
         }
     }
+    // y = x * sc + sh: the per-channel coefficients are computed ONCE per block into shared memory (C / 256 channels per
+    // thread) - with a per-thread prologue over its 8 channels the fp64 -> fp32 statistics arithmetic cost more than the
+    // 4..14 chunks a thread then processes
+    extern __shared__ float s_coef[];
+    float* s_sc = s_coef;
+    float* s_sh = s_coef + C;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float m, is;
+        if (sums != nullptr) { double var; bn_stat_from_sums(sums, C, c, inv_count, eps, m, is, var); }
+        else { m = mean[c]; is = invstd[c]; }
+        const float a = is * gamma[c];
+        s_sc[c] = a;
+        s_sh[c] = beta[c] - m * a;
+    }
+    __syncthreads();
     float sc[8], sh[8];
     auto coeff = [&](int c8) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = c8 * 8 + j;
-            float m, is;
-            if (sums != nullptr) { double var; bn_stat_from_sums(sums, C, c, inv_count, eps, m, is, var); }
-            else { m = mean[c]; is = invstd[c]; }
-            sc[j] = is * gamma[c];
-            sh[j] = beta[c] - m * sc[j];
-        }
+        const float4 a0 = *reinterpret_cast<const float4*>(s_sc + c8 * 8), a1 = *reinterpret_cast<const float4*>(s_sc + c8 * 8 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(s_sh + c8 * 8), b1 = *reinterpret_cast<const float4*>(s_sh + c8 * 8 + 4);
+        sc[0] = a0.x; sc[1] = a0.y; sc[2] = a0.z; sc[3] = a0.w; sc[4] = a1.x; sc[5] = a1.y; sc[6] = a1.z; sc[7] = a1.w;
+        sh[0] = b0.x; sh[1] = b0.y; sh[2] = b0.z; sh[3] = b0.w; sh[4] = b1.x; sh[5] = b1.y; sh[6] = b1.z; sh[7] = b1.w;
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     auto one = [&](size_t p, int c8, const uint4& vx, const uint4& vr) {
@@ -251,19 +261,27 @@ bn_bwd_apply_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
         for (int c = threadIdx.x; c < C; c += blockDim.x) { dgamma[c] += (float)sums[C + c]; dbeta[c] += (float)sums[c]; }
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const float inv_count = (float)(1.0 / count);
+    // coefficients once per block in shared memory (see bn_apply_kernel): dx = ka * dz + kb * x + kc, mask = x * msc + msh > 0
+    extern __shared__ float s_coef[];
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        // fp32 from here on: fp64 division is ~100x slower than an fp32 multiply
+        const float m_dz = (float)sums[c] * inv_count, m_dzx = (float)sums[C + c] * inv_count;
+        const float is = invstd[c], a = gamma[c] * is;
+        const float b = -a * m_dzx * is;
+        s_coef[c] = a;
+        s_coef[C + c] = b;
+        s_coef[2 * C + c] = -a * m_dz - b * mean[c];
+        s_coef[3 * C + c] = is * gamma[c];                                   // same expressions as bn_apply_kernel
+        s_coef[4 * C + c] = relu_beta ? relu_beta[c] - mean[c] * (is * gamma[c]) : 0.f;
+    }
+    __syncthreads();
     float ka[8], kb[8], kc[8], msc[8], msh[8];
     auto coeff = [&](int c8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int c = c8 * 8 + j;
-            // fp32 from here on: every thread runs this prologue and fp64 division is ~100x slower than an fp32 multiply
-            const float m_dz = (float)sums[c] * inv_count, m_dzx = (float)sums[C + c] * inv_count;
-            const float is = invstd[c], a = gamma[c] * is;
-            ka[j] = a;
-            kb[j] = -a * m_dzx * is;
-            kc[j] = -a * m_dz - kb[j] * mean[c];
-            msc[j] = is * gamma[c];                                   // same expressions as bn_apply_kernel
-            msh[j] = relu_beta ? relu_beta[c] - mean[c] * msc[j] : 0.f;
+            ka[j] = s_coef[c]; kb[j] = s_coef[C + c]; kc[j] = s_coef[2 * C + c];
+            msc[j] = s_coef[3 * C + c]; msh[j] = s_coef[4 * C + c];
         }
     };
     size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -373,11 +391,11 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
     const int C8 = C / 8;
     const int grid = tr_grid(npix * C8, 256 * 4, 16);
     if (256 % C8 == 0)
-        bn_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)st>>>(
+        bn_apply_kernel<true><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
             (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype);
     else
-        bn_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)st>>>(
+        bn_apply_kernel<false><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
             (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype);
     VU_CHECK_LAUNCH("bn_apply");
@@ -393,12 +411,12 @@ extern "C" int vu_bn_apply_sums(const void* x, size_t npix, int C, int x_ctot, i
     const int C8 = C / 8;
     const int grid = tr_grid(npix * C8, 256 * 4, 16);
     if (256 % C8 == 0)
-        bn_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)st>>>(
+        bn_apply_kernel<true><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, nullptr, nullptr, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
             (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype, sums, (double)npix, 1.0 / (double)npix, eps, momentum, running_mean,
             running_var, mean, invstd);
     else
-        bn_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)st>>>(
+        bn_apply_kernel<false><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, nullptr, nullptr, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
             (uint16_t*)y, y_ctot, y_coff, npix, C8, dtype, sums, (double)npix, 1.0 / (double)npix, eps, momentum, running_mean,
             running_var, mean, invstd);
@@ -423,12 +441,12 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
     VU_CHECK_LAUNCH("bn_bwd_reduce");
     const int grid = tr_grid(npix * C8, 256 * 4, 16);
     if (256 % C8 == 0)
-        bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(
+        bn_bwd_apply_kernel<true><<<grid, 256, 5 * C * sizeof(float), s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
             mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
             C8, dtype, dgamma, dbeta, y_relu ? nullptr : relu_beta);
     else
-        bn_bwd_apply_kernel<false><<<grid, 256, 0, s>>>(
+        bn_bwd_apply_kernel<false><<<grid, 256, 5 * C * sizeof(float), s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
             mean, invstd, gamma, sums, (double)npix, (uint16_t*)dx, dx_ctot, dx_coff, (uint16_t*)dz_out, dz_ctot, dz_coff, npix,
             C8, dtype, dgamma, dbeta, y_relu ? nullptr : relu_beta);
