@@ -220,7 +220,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         // ===================== TMA producer (one lane) =====================
         if (lane == 0) {
             const CUtensorMap* maps[4] = {&map_a0, &map_a1, &map_a2, &map_a3};
-            uint32_t it = 0;
+            // running stage / phase counters: no division or modulo in the per-k-iteration path of either pipeline end
+            // (with 64-channel k-iterations and BN <= 128 the MMAs of a k-iteration take only ~256 clk)
+            uint32_t s = 0, ph = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 const int n_tile = tile % p.num_n_tiles;
                 const int m_tile = tile / p.num_n_tiles;
@@ -232,14 +234,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
                     const CUtensorMap* ma = maps[p.tap_map[tap]];
                     const int ww = w0 + p.tap_dw[tap], hh = h0 + p.tap_dh[tap];
                     const int widx = p.tap_widx[tap];
-                    for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-                        const int s = it % Cfg::kStages;
-                        const uint32_t ph = (it / Cfg::kStages) & 1;
+                    for (int kb = 0; kb < p.kblocks; ++kb) {
                         mbar_wait(empty_bar(s), ph ^ 1);
                         const uint32_t sa = smem_base + s * Cfg::kStageBytes;
                         mbar_arrive_expect_tx(full_bar(s), Cfg::kStageBytes);
                         tma_load_4d(sa, ma, full_bar(s), kb * kBlockK, ww, hh, n0);
                         tma_load_3d(sa + kABytes, &map_w, full_bar(s), kb * kBlockK, widx, n_tile * BN);
+                        if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
                     }
                 }
             }
@@ -248,23 +249,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
         // ===================== MMA issuer: warp-uniform control flow, one elected lane issues =====
         // (elect.sync instead of `lane == 0`: ptxas then emits bare UTCHMMA, no per-MMA uniform-branch loop)
         const uint32_t idesc = umma_idesc_f16(kTileM, BN, p.dtype == 0 ? 1u : 0u);
-        uint32_t it = 0, tcount = 0;
+        uint32_t s = 0, ph = 0, tcount = 0;
+        const uint64_t desc0 = umma_desc_k_sw128(smem_base);          // stage 0; +stage bytes >> 4 per stage
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
             const int acc = tcount & 1;
             const uint32_t accph = (tcount >> 1) & 1;
             mbar_wait(tempty_bar(acc), accph ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * BN;
-            for (int ki = 0; ki < k_iters; ++ki, ++it) {
-                const int s = it % Cfg::kStages;
-                const uint32_t ph = (it / Cfg::kStages) & 1;
+            int kb = 0;
+            for (int ki = 0; ki < k_iters; ++ki) {
                 mbar_wait(full_bar(s), ph);
                 tc_fence_after();
-                const uint32_t sa = smem_base + s * Cfg::kStageBytes;
-                const uint64_t adesc = umma_desc_k_sw128(sa);
-                const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
-                const int kb = ki % p.kblocks;
-                const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
+                const uint64_t adesc = desc0 + (uint64_t)((s * Cfg::kStageBytes) >> 4);
+                const uint64_t bdesc = adesc + (uint64_t)(kABytes >> 4);
+                const bool last_kb = (kb == p.kblocks - 1);
+                const int nk = last_kb ? p.last_ksteps : (kBlockK / 16);
                 if (elect_one()) {
                     // +32 B per K=16 step inside the 128 B swizzle row (encoded >> 4)
                     if (nk == 4) {
@@ -279,6 +279,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_const
                     if (ki == k_iters - 1) umma_commit(tfull_bar(acc));
                 }
                 __syncwarp();
+                kb = last_kb ? 0 : kb + 1;
+                if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
             }
         }
     } else {
@@ -391,7 +393,7 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
         if (lane == 0) {
             const CUtensorMap* maps[4] = {&map_a0, &map_a1, &map_a2, &map_a3};
             const uint32_t leader_full0 = mapa_cluster(full_bar(0), 0);
-            uint32_t it = 0;
+            uint32_t s = 0, ph = 0;
             for (int tile = pair_id; tile < total_tiles; tile += num_pairs) {
                 const int n_tile = tile % p.num_n_tiles;
                 const int m_tile = 2 * (tile / p.num_n_tiles) + (int)rank;   // may be one past the end: loads zero fill
@@ -403,9 +405,7 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
                     const CUtensorMap* ma = maps[p.tap_map[tap]];
                     const int ww = w0 + p.tap_dw[tap], hh = h0 + p.tap_dh[tap];
                     const int widx = p.tap_widx[tap];
-                    for (int kb = 0; kb < p.kblocks; ++kb, ++it) {
-                        const int s = it % Cfg::kStages;
-                        const uint32_t ph = (it / Cfg::kStages) & 1;
+                    for (int kb = 0; kb < p.kblocks; ++kb) {
                         mbar_wait(empty_bar(s), ph ^ 1);
                         const uint32_t sa = smem_base + s * Cfg::kStageBytes;
                         if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2 * Cfg::kStageBytes);
@@ -413,6 +413,7 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
                         tma_load_4d_pair(sa, ma, full_bar(s), kb * kBlockK, ww, hh, n0);
                         tma_load_3d_pair(sa + kABytes, &map_w, full_bar(s), kb * kBlockK, widx,
                                          n_tile * BN + (int)rank * (BN / 2));
+                        if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
                     }
                 }
             }
@@ -421,23 +422,22 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
         // ===================== MMA issuer: leader CTA only =====================
         if (rank == 0) {
             const uint32_t idesc = umma_idesc_f16(2 * kTileM, BN, p.dtype == 0 ? 1u : 0u);
-            uint32_t it = 0, tcount = 0;
+            uint32_t s = 0, ph = 0, tcount = 0;
+            const uint64_t desc0 = umma_desc_k_sw128(smem_base);
             for (int tile = pair_id; tile < total_tiles; tile += num_pairs, ++tcount) {
                 const int acc = tcount & 1;
                 const uint32_t accph = (tcount >> 1) & 1;
                 mbar_wait(tempty_bar(acc), accph ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int ki = 0; ki < k_iters; ++ki, ++it) {
-                    const int s = it % Cfg::kStages;
-                    const uint32_t ph = (it / Cfg::kStages) & 1;
+                int kb = 0;
+                for (int ki = 0; ki < k_iters; ++ki) {
                     mbar_wait(full_bar(s), ph);
                     tc_fence_after();
-                    const uint32_t sa = smem_base + s * Cfg::kStageBytes;
-                    const uint64_t adesc = umma_desc_k_sw128(sa);
-                    const uint64_t bdesc = umma_desc_k_sw128(sa + kABytes);
-                    const int kb = ki % p.kblocks;
-                    const int nk = (kb == p.kblocks - 1) ? p.last_ksteps : (kBlockK / 16);
+                    const uint64_t adesc = desc0 + (uint64_t)((s * Cfg::kStageBytes) >> 4);
+                    const uint64_t bdesc = adesc + (uint64_t)(kABytes >> 4);
+                    const bool last_kb = (kb == p.kblocks - 1);
+                    const int nk = last_kb ? p.last_ksteps : (kBlockK / 16);
                     if (elect_one()) {
                         if (nk == 4) {
 #pragma unroll
@@ -451,6 +451,8 @@ conv_igemm_pair_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_
                         if (ki == k_iters - 1) umma_commit_pair(tfull_bar(acc), 3);
                     }
                     __syncwarp();
+                    kb = last_kb ? 0 : kb + 1;
+                    if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
                 }
             }
         }
