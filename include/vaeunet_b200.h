@@ -270,6 +270,11 @@ int vu_bn_finalize(const double* sums, double count, int C, float eps, float mom
 int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_coff, const float* mean, const float* invstd,
                 const float* gamma, const float* beta, const void* residual, int res_ctot, int res_coff, int relu,
                 void* y, int y_ctot, int y_coff, int dtype, vu_stream_t stream);
+/* running_mean / running_var update of nn.BatchNorm2d (momentum, unbiased variance) from saved batch statistics
+ * (mean, invstd over `count` values per channel): the functional torch custom ops (vaeunet::batch_norm_train, ::vec_layer,
+ * ::map_bn_sigmoid) leave the module buffers alone and vaeunet::bn_update_running mutates them. */
+int vu_bn_update_running(const float* mean, const float* invstd, double count, int C, float eps, float momentum,
+                         float* running_mean, float* running_var, vu_stream_t stream);
 /* vu_bn_finalize + vu_bn_apply in ONE launch: every CTA derives mean / invstd of its channels from the fp64 sums (the
  * statistics pass or the producing conv's epilogue, vu_conv_args.stat_sums); count = npix. mean / invstd [C] are written
  * for the backward and the running statistics are updated (NULL = leave them). */

@@ -1,0 +1,193 @@
+"""GPU parity of the torch custom ops (torch.ops.vaeunet.*) and of the train-mode module surface built on them: the
+reference's literal training-step body (train.py:381-414: model.train(); seg, mu, logvar = model(images); loss = criterion
++ beta * KL; loss.backward(); clip_grad_norm_; optimizer.step()) runs on the drop-in modules and its gradients match the
+fp32 CPU oracle's autograd - for the default UNetResNet, the non-default configurations TrainStep does not cover
+(latent_injection, use_skip=False, use_attention=False) and the basic UNet with ConvTranspose2d / bilinear up-sampling.
+
+Gradient bars: f16 storage with a 1024x loss scale (the reference trains under fp16 autocast + GradScaler); full-gradient
+cosine >= 0.98 against the fp32 oracle and within the 16-bit format budget the rounded oracle measures in the same run
+(see tests/test_training_gpu.py for why gradients of the seeded random network carry a format budget)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+SCALE = 1024.0
+
+
+def _cos(a, b):
+    return (a.double() @ b.double() / (a.double().norm() * b.double().norm() + 1e-300)).item()
+
+
+def _reference_step_body(model, images, masks, eps, beta, lesion):
+    """train.py:385-408 with the drop-in loss functions; returns the loss terms and leaves .grad populated."""
+    from vaeunet_b200.utils.loss import CombinedLoss, MASegmentationLoss, kl_with_free_bits
+    criterion = MASegmentationLoss(class_weight=0.9) if lesion == "MA" else CombinedLoss()
+    model.train()
+    model.zero_grad(set_to_none=True)
+    seg, mu, logvar = model(images, eps=eps)          # reference: model(images); eps injected for parity
+    recon = criterion(seg, masks)
+    kl = kl_with_free_bits(mu, logvar, free_bits=1e-3)
+    loss = recon + beta * kl
+    (loss * SCALE).backward()                          # GradScaler.scale(loss).backward()
+    return loss.detach(), recon.detach(), kl.detach(), seg.detach()
+
+
+def _flat(grads, names):
+    return torch.cat([grads[k].flatten().float() for k in names])
+
+
+CONFIGS = [
+    ("default", dict()),
+    ("inject_first", dict(latent_injection="first")),
+    ("inject_none", dict(latent_injection="none")),
+    ("bottleneck_only", dict(latent_injection="bottleneck")),
+    ("no_skip", dict(use_skip=False)),
+    ("no_attention", dict(use_attention=False)),
+]
+
+
+@pytest.mark.parametrize("name,kw", CONFIGS, ids=[c[0] for c in CONFIGS])
+def test_module_train_step_matches_oracle_autograd(cuda_dev, name, kw):
+    from oracle import vaeunet_oracle as O
+    from vaeunet_b200 import testing
+    from vaeunet_b200.synthetic import synthetic_fundus
+    from vaeunet_b200.unet import UNetResNet
+    dev = cuda_dev
+    if "latent_injection" in kw or not kw:
+        sd, mkw = testing.resnet_fixture(**kw)
+    else:
+        sd, mkw = testing.resnet_variant_state(**kw)
+    model = UNetResNet(**mkw)
+    model.load_state_dict(sd)
+    model = model.to(dev)
+    model.compute_dtype = "f16"
+    B, S, beta = 8, 64, 0.001
+    x, m = synthetic_fundus(B, S, S, seed=31)
+    eps = torch.randn(B, 32, generator=torch.Generator().manual_seed(32))
+    cfg = O.ResNetCfg(use_attention=mkw.get("use_attention", True), use_skip=mkw.get("use_skip", True),
+                      latent_injection=mkw.get("latent_injection", "all"))
+    loss_r, recon_r, kl_r, grads_r, upd_r = O.training_grads(sd, cfg, x, m, eps, beta, 1e-3, "EX")
+    with O.storage_rounding(torch.float16):
+        _, _, _, grads_q, _ = O.training_grads(sd, cfg, x, m, eps, beta, 1e-3, "EX")
+    loss, recon, kl, seg = _reference_step_body(model, x.to(dev), m.to(dev), eps.to(dev), beta, "EX")
+    torch.cuda.synchronize()
+    assert abs(loss.item() - loss_r.item()) <= 3e-3 * abs(loss_r.item()), (loss.item(), loss_r.item())
+    assert abs(kl.item() - kl_r.item()) <= 3e-3 * abs(kl_r.item()) + 1e-5
+    got = {k: (p.grad.detach().cpu() / SCALE if p.grad is not None else torch.zeros_like(p).cpu())
+           for k, p in model.named_parameters()}
+    names = [k for k in grads_r if k in got]
+    assert len(names) == len(grads_r)
+    fg, fr, fq = _flat(got, names), _flat(grads_r, names), _flat(grads_q, names)
+    cos, budget = _cos(fg, fr), _cos(fq, fr)
+    assert cos >= budget - 0.015 and cos >= 0.98, (name, cos, budget)
+    gmax = max(grads_r[k].norm().item() for k in names)
+    rel = lambda a, b: ((a - b).norm() / (b.norm() + 1e-20)).item()
+    bad = {k: (rel(got[k], grads_r[k]), rel(grads_q[k], grads_r[k])) for k in names
+           if grads_r[k].norm().item() > 1e-3 * gmax and rel(got[k], grads_r[k]) > 3.0 * rel(grads_q[k], grads_r[k]) + 0.05}
+    assert not bad, f"{name}: tensors beyond 3x the format budget: {bad}"
+    # running statistics were updated like nn.BatchNorm2d in train mode
+    bufs = dict(model.named_buffers())
+    worst = max(((bufs[k].cpu() - v).norm() / (v.norm() + 1e-12)).item() for k, v in upd_r.items())
+    assert worst <= 2e-2, worst
+    assert int(bufs["encoder.bn1.num_batches_tracked"]) == 1
+    # the rest of the reference loop body: unscale, clip, optimizer step (torch's own optimizer on the module parameters)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-5)
+    for p in model.parameters():
+        if p.grad is not None:
+            p.grad.div_(SCALE)
+    torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+    opt.step()
+    model.eval()
+    with torch.no_grad():
+        lg, _, _ = model(x.to(dev), eps=eps.to(dev))       # eval-mode kernels see the updated weights
+    assert torch.isfinite(lg).all()
+
+
+def test_module_train_matches_trainstep(cuda_dev):
+    """The general autograd path and the fused TrainStep compute the same step: loss terms to 1e-3, gradients to the spread of
+    two equally valid 16-bit evaluation orders (cosine >= 0.99 at f16 + loss scale)."""
+    from vaeunet_b200 import ops, testing
+    from vaeunet_b200.synthetic import synthetic_fundus
+    from vaeunet_b200.training import TrainStep
+    from vaeunet_b200.unet import UNetResNet
+    dev = cuda_dev
+    sd, mkw = testing.resnet_fixture()
+    B, S, beta = 8, 64, 0.001
+    x, m = synthetic_fundus(B, S, S, seed=41)
+    eps = torch.randn(B, 32, generator=torch.Generator().manual_seed(42))
+    model = UNetResNet(**mkw); model.load_state_dict(sd); model = model.to(dev); model.compute_dtype = "f16"
+    loss, recon, kl, seg = _reference_step_body(model, x.to(dev), m.to(dev), eps.to(dev), beta, "EX")
+    ga = {k: p.grad.detach().clone() / SCALE for k, p in model.named_parameters()}
+    twin = UNetResNet(**mkw); twin.load_state_dict(sd); twin = twin.to(dev).train()
+    ts = TrainStep(twin, lesion="EX", dtype=ops.F16, loss_scale=SCALE)
+    ts.zero_grad()
+    out = ts.forward_backward(x.to(dev), m.to(dev), beta, eps.to(dev))
+    torch.cuda.synchronize()
+    assert abs(out["loss"].item() - loss.item()) <= 1e-3 * abs(loss.item())
+    names = list(ga)
+    fa = torch.cat([ga[k].flatten() for k in names])
+    fb = torch.cat([(ts.G[k] / SCALE).flatten() for k in names])
+    assert _cos(fa.cpu(), fb.cpu()) >= 0.99
+
+
+@pytest.mark.parametrize("bilinear", [False, True], ids=["convT", "bilinear"])
+def test_basic_unet_train_step_matches_oracle_autograd(cuda_dev, bilinear):
+    """Basic attention U-Net in train mode (unet/unet_model.py, unet/unet_parts.py): ConvTranspose2d forward / dgrad / wgrad
+    (or bilinear up-sampling), MaxPool2d(2), attention gates, OutConv - gradients vs the oracle's autograd."""
+    from oracle import vaeunet_oracle as O
+    from vaeunet_b200 import testing
+    from vaeunet_b200.synthetic import synthetic_fundus
+    from vaeunet_b200.unet import UNet
+    from vaeunet_b200.utils.loss import CombinedLoss
+    dev = cuda_dev
+    sd = testing.unet_fixture(bilinear=bilinear)
+    model = UNet(3, 1, bilinear); model.load_state_dict(sd); model = model.to(dev); model.compute_dtype = "f16"
+    B, S = 4, 64
+    x, m = synthetic_fundus(B, S, S, seed=51)
+    leaves = {k: (v.detach().clone().requires_grad_(True) if v.is_floating_point() and not k.endswith(("running_mean", "running_var")) else v)
+              for k, v in sd.items()}
+
+    def oracle_grads():
+        st = O.BNState(training=True)
+        out = O.unet_forward(leaves, x, bilinear, st)
+        loss = O.combined_loss(out, m)
+        names = [k for k, v in leaves.items() if isinstance(v, torch.Tensor) and v.requires_grad]
+        gs = torch.autograd.grad(loss, [leaves[k] for k in names], allow_unused=True)
+        return loss.detach(), {k: (g if g is not None else torch.zeros_like(leaves[k])) for k, g in zip(names, gs)}
+
+    loss_r, grads_r = oracle_grads()
+    with O.storage_rounding(torch.float16):
+        _, grads_q = oracle_grads()
+    model.train(); model.zero_grad(set_to_none=True)
+    out = model(x.to(dev))
+    loss = CombinedLoss()(out, m.to(dev))
+    (loss * SCALE).backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - loss_r.item()) <= 3e-3 * abs(loss_r.item()), (loss.item(), loss_r.item())
+    got = {k: p.grad.detach().cpu() / SCALE for k, p in model.named_parameters() if p.grad is not None}
+    names = [k for k in grads_r if k in got]
+    assert len(names) == len(grads_r), set(grads_r) - set(got)
+    fg, fr, fq = _flat(got, names), _flat(grads_r, names), _flat(grads_q, names)
+    cos, budget = _cos(fg, fr), _cos(fq, fr)
+    assert cos >= budget - 0.015 and cos >= 0.98, (cos, budget)
+    if not bilinear:                      # the transposed-conv weights specifically (dW of ConvTranspose2d)
+        for k in ("up1.up.weight", "up4.up.weight", "up4.up.bias"):
+            assert _cos(got[k].flatten(), grads_r[k].flatten()) >= 0.97, k
+
+
+def test_custom_ops_registered_with_fake_and_autograd(cuda_dev):
+    """torch.ops.vaeunet.* exist, propagate shapes on FakeTensors, and opcheck accepts the conv op's registrations."""
+    from vaeunet_b200 import torch_ops
+    for n in torch_ops.OP_NAMES:
+        assert hasattr(torch.ops.vaeunet, n), n
+    dev = cuda_dev
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, 16, 16, 64, generator=g).to(torch.float16).to(dev).requires_grad_(True)
+    w = (torch.randn(64, 64, 3, 3, generator=g) * 0.05).to(dev).requires_grad_(True)
+    torch.library.opcheck(torch.ops.vaeunet.conv2d.default, (x, w, None, 1, 1),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    y = torch.ops.vaeunet.conv2d(x, w, None, 1, 1)
+    ref = torch.nn.functional.conv2d(x.detach().float().permute(0, 3, 1, 2).cpu(), w.detach().half().float().cpu(), None, 1, 1)
+    assert ((y.float().cpu().permute(0, 3, 1, 2) - ref).abs().max() <= 2e-2 * ref.abs().max())
+    y.float().square().sum().backward()
+    assert x.grad is not None and w.grad is not None and w.grad.shape == w.shape

@@ -69,3 +69,41 @@ def test_module_surface_names():
               "kl_with_free_bits"):
         assert hasattr(loss, n)
     assert hasattr(uncertainty_metrics, "calculate_expected_calibration_error")
+
+
+def test_torch_custom_ops_registered_and_fake():
+    """the ops are torch.library custom ops (torch.ops.vaeunet.*) with fake (meta) implementations - shape
+    propagation works without a device - and autograd registrations on the differentiable ones."""
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    from vaeunet_b200 import torch_ops
+    for n in torch_ops.OP_NAMES:
+        assert hasattr(torch.ops.vaeunet, n), n
+    with FakeTensorMode():
+        x = torch.empty(2, 32, 32, 64, dtype=torch.float16)
+        assert torch.ops.vaeunet.conv2d(x, torch.empty(128, 64, 3, 3), None, 2, 1).shape == (2, 16, 16, 128)
+        assert torch.ops.vaeunet.conv_transpose2x2(x, torch.empty(64, 32, 2, 2), torch.empty(32)).shape == (2, 64, 64, 32)
+        y, mean, invstd = torch.ops.vaeunet.batch_norm_train(x, torch.empty(64), torch.empty(64), None, True)
+        assert y.shape == x.shape and mean.shape == (64,)
+        p, code = torch.ops.vaeunet.maxpool(x, 2, 2, 0)
+        assert p.shape == (2, 16, 16, 64) and code.dtype == torch.uint8
+        assert torch.ops.vaeunet.bilinear_ac(x, 64, 64).shape == (2, 64, 64, 64)
+        img = torch.empty(2, 3, 64, 64)
+        assert torch.ops.vaeunet.conv_small_cin(img, torch.empty(64, 3, 7, 7), 2, 3, 1).shape == (2, 32, 32, 64)
+        m5 = torch.ops.vaeunet.uncertainty_reduce(torch.empty(2, 10, 32, 32), 64, 64)
+        assert len(m5) == 5 and m5[0].shape == (2, 64, 64)
+
+
+def test_module_train_mode_needs_a_device():
+    """model.train(); model(x) goes to the autograd path (torch.ops.vaeunet.*), which - like everything else - has no CPU
+    fallback: it raises VaeUnetError on a CPU tensor instead of silently running torch ops."""
+    import pytest
+    import torch
+    from vaeunet_b200._lib import VaeUnetError
+    from vaeunet_b200.unet import UNet, UNetResNet
+    m = UNetResNet(3, 1, pretrained=False).train()
+    with pytest.raises(VaeUnetError):
+        m(torch.zeros(2, 3, 64, 64))
+    u = UNet(3, 1).train()
+    with pytest.raises(VaeUnetError):
+        u(torch.zeros(2, 3, 64, 64))

@@ -81,6 +81,7 @@ SIGNATURES = {
     "vu_bn_stats": [p, sz, i, i, i, p, i, p],
     "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
     "vu_bn_apply": [p, sz, i, i, i, p, p, p, p, p, i, i, i, p, i, i, i, p],
+    "vu_bn_update_running": [p, p, C.c_double, i, f, f, p, p, p],
     "vu_bn_apply_sums": [p, sz, i, i, i, p, f, f, p, p, p, p, p, p, p, i, i, i, p, i, i, i, p],
     "vu_bn_bwd": [p, sz, i, i, i, p, i, i, p, i, i, p, p, p, p, p, i, i, p, i, i, p, p, p, i, p],
     "vu_add_nhwc": [p, i, i, p, i, i, sz, i, i, p],

@@ -151,6 +151,21 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
     }
 }
 
+// Running statistics of nn.BatchNorm2d from the saved batch statistics (the functional torch custom ops update them in a
+// separate, mutating op): var = 1 / invstd^2 - eps (biased), running_var takes the unbiased estimate.
+__global__ void bn_update_running_kernel(const float* __restrict__ mean, const float* __restrict__ invstd, double count,
+                                         float eps, float momentum, float* __restrict__ running_mean,
+                                         float* __restrict__ running_var, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const double is = (double)invstd[c];
+    double var = 1.0 / (is * is) - (double)eps;
+    if (var < 0.0) var = 0.0;
+    const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean[c];
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+}
+
 // y = act(gamma * (x - mean) * invstd + beta + residual) = act(x * sc + sh + residual).
 // The launch uses gridDim * 256 threads with 256 % C8 == 0 whenever C8 is a power of two (every BatchNorm of the model),
 // so a thread keeps the same 8 channels for its whole grid-stride loop and loads the coefficients once (FIXED = true).
@@ -379,6 +394,15 @@ extern "C" int vu_bn_finalize(const double* sums, double count, int C, float eps
     bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)st>>>(sums, count, C, eps, momentum, mean, invstd,
                                                                        running_mean, running_var);
     VU_CHECK_LAUNCH("bn_finalize");
+    return 0;
+}
+
+extern "C" int vu_bn_update_running(const float* mean, const float* invstd, double count, int C, float eps, float momentum,
+                                    float* running_mean, float* running_var, vu_stream_t st) {
+    if (!mean || !invstd || !running_mean || !running_var || C < 1 || count < 1) return set_error(VU_ERR_INVALID, "bn_update_running: bad args");
+    bn_update_running_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)st>>>(mean, invstd, count, eps, momentum, running_mean,
+                                                                            running_var, C);
+    VU_CHECK_LAUNCH("bn_update_running");
     return 0;
 }
 

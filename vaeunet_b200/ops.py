@@ -111,8 +111,10 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
            out_up: int = 1, out_dh: int = 0, out_dw: int = 0, max_ctas: int = 0,
            fuse_w: Optional[torch.Tensor] = None, fuse_bias: float = 0.0, fuse_out: Optional[torch.Tensor] = None,
            store: bool = True, pos_bias: Optional[torch.Tensor] = None,
-           stat_sums: Optional[torch.Tensor] = None, tap_mask: int = 0) -> Optional[Act]:
+           stat_sums: Optional[torch.Tensor] = None, tap_mask: int = 0, x_elem_offset: int = 0) -> Optional[Act]:
     """fuse_w/fuse_bias/fuse_out: fused 1x1 Cout->1 output conv (fp32 [N,Ho,Wo]); store=False skips writing y.
+    x_elem_offset: the input base pointer is advanced by this many 16-bit elements (a shifted view that keeps the image /
+    row pitches of x: the (a, b) parity plane of a tensor read by a stride-2 1x1 conv starts (a*W + b)*ctot elements in).
     pos_bias: fp32 [N, 9, Cout] pre-scale bias by border class (`border_bias`): spatially constant input channels left out.
     stat_sums: ZEROED fp64 [2*Cout]; the epilogue adds per-channel sum / sum of squares of the stored outputs (the
     statistics a following train-mode BatchNorm needs: bn_train_fwd(sums=))."""
@@ -128,7 +130,7 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
             out = new_act(x.N, Ho * out_up, Wo * out_up, Cout, x.dt, x.t.device)
         assert out.C == Cout and out.N == x.N and out.H == Ho * out_up and out.W == Wo * out_up, "conv output shape"
     a = ConvArgs()
-    a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
+    a.x = x.t.data_ptr() + 2 * x_elem_offset; a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
     a.w = w_packed.data_ptr(); a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad
     a.scale = _ptr(scale); a.bias = _ptr(bias)
     if residual is not None:
@@ -174,7 +176,7 @@ def conv2d(x: Act, w_packed: torch.Tensor, k: int, stride: int, pad: int, scale:
 
 
 def conv2d_wgrad(x: Act, dy: Act, k: int, stride: int, pad: int, out: Optional[torch.Tensor] = None,
-                 oihw: bool = False) -> torch.Tensor:
+                 oihw: bool = False, x_elem_offset: int = 0) -> torch.Tensor:
     """dW of conv2d(x, W), fp32, ACCUMULATED into `out` if given: packed tap order [Cout, k*k, Cin], or (oihw) the
     parameter's own layout [Cout, Cin, k, k]."""
     require_device()
@@ -187,7 +189,7 @@ def conv2d_wgrad(x: Act, dy: Act, k: int, stride: int, pad: int, out: Optional[t
         out = torch.zeros(shape, dtype=torch.float32, device=x.t.device)
     assert tuple(out.shape) == shape and out.dtype == torch.float32 and out.is_contiguous()
     a = ConvArgs()
-    a.x = x.t.data_ptr(); a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
+    a.x = x.t.data_ptr() + 2 * x_elem_offset; a.N = x.N; a.H = x.H; a.W = x.W; a.x_ctot = x.ctot; a.x_coff = x.coff; a.Cin = x.C
     a.Cout = Cout; a.KH = k; a.KW = k; a.stride = stride; a.pad = pad; a.dtype = x.dt
     fn = load().vu_conv2d_wgrad_oihw if oihw else load().vu_conv2d_wgrad
     if CONV_TIMING is not None:

@@ -72,3 +72,19 @@ def unet_fixture(seed: int = 0, bilinear: bool = False):
     from .unet.unet_model import UNet
     tmpl = UNet(3, 1, bilinear).state_dict()
     return load_fixture("fixture_unet" + ("_bilinear" if bilinear else ""), tmpl, seed)
+
+
+def resnet_variant_state(seed: int = 0, **model_kwargs):
+    """State for a UNetResNet VARIANT without its own calibrated fixture (use_skip=False, use_attention=False, ...): seeded
+    init overlaid with every tensor of the default fixture whose key and shape match (encoder statistics, rescaled heads,
+    output conv). -> (state_dict on CPU, model kwargs)."""
+    from .unet.unet_resnet import UNetResNet
+    kw = dict(n_channels=3, n_classes=1, pretrained=False)
+    kw.update(model_kwargs)
+    tmpl = UNetResNet(**kw).state_dict()
+    sd = seeded_state_dict(tmpl, seed)
+    overlay = torch.load(GOLDEN / "fixture_resnet.pt", map_location="cpu", weights_only=True)
+    for k, v in overlay.items():
+        if k in sd and sd[k].shape == v.shape and not k.startswith("decoder_blocks."):
+            sd[k] = v.clone()
+    return sd, kw

@@ -228,20 +228,25 @@ conv_transpose2x2.register_autograd(_ct_bwd, setup_context=_ct_setup)
 
 
 # ---------------------------------------------------------------------------------------------------- BatchNorm (train mode)
-@_lib_op(f"{NS}::batch_norm_train", mutates_args=("running_mean", "running_var"))
-def batch_norm_train(x: Tensor, gamma: Tensor, beta: Tensor, running_mean: Tensor, running_var: Tensor,
-                     residual: Optional[Tensor], relu: bool) -> Tuple[Tensor, Tensor, Tensor]:
-    """y = act(BN_batch-stats(x) + residual) on an NHWC 16-bit map -> (y, mean, invstd); running statistics updated like
-    nn.BatchNorm2d (momentum 0.1, unbiased variance)."""
-    y, mean, invstd = T.bn_train_fwd(Act(_c(x)), gamma, beta, running_mean, running_var, relu,
-                                     Act(_c(residual)) if residual is not None else None)
+@_lib_op(f"{NS}::batch_norm_train", mutates_args=())
+def batch_norm_train(x: Tensor, gamma: Tensor, beta: Tensor, residual: Optional[Tensor], relu: bool) -> Tuple[Tensor, Tensor, Tensor]:
+    """y = act(BN_batch-stats(x) + residual) on an NHWC 16-bit map -> (y, mean, invstd). Functional: the module's running
+    statistics are updated by vaeunet::bn_update_running from (mean, invstd)."""
+    y, mean, invstd = T.bn_train_fwd(Act(_c(x)), gamma, beta, None, None, relu,
+                                     Act(_c(residual)) if residual is not None else None, update_running=False)
     return y.t, mean, invstd
 
 
 @batch_norm_train.register_fake
-def _(x, gamma, beta, running_mean, running_var, residual, relu):
+def _(x, gamma, beta, residual, relu):
     C = x.shape[3]
     return x.new_empty(x.shape), x.new_empty((C,), dtype=torch.float32), x.new_empty((C,), dtype=torch.float32)
+
+
+@_lib_op(f"{NS}::bn_update_running", mutates_args=("running_mean", "running_var"))
+def bn_update_running(running_mean: Tensor, running_var: Tensor, mean: Tensor, invstd: Tensor, count: float) -> None:
+    """running_mean / running_var of nn.BatchNorm2d (momentum 0.1, unbiased variance over `count` values per channel)."""
+    T.bn_update_running(mean, invstd, count, running_mean, running_var)
 
 
 @_lib_op(f"{NS}::batch_norm_train_bwd", mutates_args=())
@@ -262,7 +267,7 @@ def _(x, dy, y, mean, invstd, gamma, want_dz):
 
 
 def _bn_setup(ctx, inputs, output):
-    x, gamma, beta, rm, rv, residual, relu = inputs
+    x, gamma, beta, residual, relu = inputs
     y, mean, invstd = output
     ctx.relu, ctx.has_res = relu, residual is not None
     ctx.save_for_backward(x, y if relu else None, mean, invstd, gamma)
@@ -272,9 +277,9 @@ def _bn_setup(ctx, inputs, output):
 def _bn_bwd(ctx, dy, dmean, dinvstd):
     x, y, mean, invstd, gamma = ctx.saved_tensors
     if dy is None:
-        return (None,) * 7
+        return (None,) * 5
     dx, dg, db, dz = torch.ops.vaeunet.batch_norm_train_bwd(x, _c(dy), y, mean, invstd, gamma, ctx.has_res)
-    return dx, dg, db, None, None, (dz if ctx.has_res else None), None
+    return dx, dg, db, (dz if ctx.has_res else None), None
 
 
 batch_norm_train.register_autograd(_bn_bwd, setup_context=_bn_setup)
@@ -427,14 +432,14 @@ def _c1_bwd(ctx, dm):
 conv1x1_to_map.register_autograd(_c1_bwd, setup_context=_c1_setup)
 
 
-@_lib_op(f"{NS}::map_bn_sigmoid", mutates_args=("running_mean", "running_var"))
-def map_bn_sigmoid(m: Tensor, gamma: Tensor, beta: Tensor, running_mean: Tensor, running_var: Tensor) -> Tuple[Tensor, Tensor]:
-    """psi = sigmoid(BatchNorm2d(1)(m)) in train mode on an fp32 map -> (psi, stat = {mean, invstd})."""
-    return T.map_bn_sigmoid_fwd(_c(m), gamma, beta, running_mean, running_var)
+@_lib_op(f"{NS}::map_bn_sigmoid", mutates_args=())
+def map_bn_sigmoid(m: Tensor, gamma: Tensor, beta: Tensor) -> Tuple[Tensor, Tensor]:
+    """psi = sigmoid(BatchNorm2d(1)(m)) in train mode on an fp32 map -> (psi, stat = {mean, invstd}). Functional."""
+    return T.map_bn_sigmoid_fwd(_c(m), gamma, beta, None, None)
 
 
 @map_bn_sigmoid.register_fake
-def _(m, gamma, beta, running_mean, running_var):
+def _(m, gamma, beta):
     return m.new_empty(m.shape), m.new_empty((2,))
 
 
@@ -457,7 +462,7 @@ def _ms_setup(ctx, inputs, output):
 def _ms_bwd(ctx, dpsi, dstat):
     m, psi, stat, gamma = ctx.saved_tensors
     dm, dg, db = torch.ops.vaeunet.map_bn_sigmoid_bwd(m, _c(dpsi), psi, stat, gamma)
-    return dm, dg.reshape(gamma.shape), db.reshape(gamma.shape), None, None
+    return dm, dg.reshape(gamma.shape), db.reshape(gamma.shape)
 
 
 map_bn_sigmoid.register_autograd(_ms_bwd, setup_context=_ms_setup)
@@ -589,19 +594,17 @@ def _rp_bwd(ctx, dz):
 reparameterize.register_autograd(_rp_bwd, setup_context=_rp_setup)
 
 
-@_lib_op(f"{NS}::vec_layer", mutates_args=("running_mean", "running_var"))
-def vec_layer(z: Tensor, w: Tensor, b: Tensor, gamma: Tensor, beta: Tensor, running_mean: Tensor, running_var: Tensor,
-              relu: bool, stat_count: float) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+@_lib_op(f"{NS}::vec_layer", mutates_args=())
+def vec_layer(z: Tensor, w: Tensor, b: Tensor, gamma: Tensor, beta: Tensor, relu: bool) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
     """1x1 conv + train-mode BatchNorm (+ReLU) on a SPATIALLY CONSTANT map = a dense layer on the per-image vectors
-    z [M, L] (z_initial, z_proj, W_g of a constant map) -> (y, y_raw, mean, invstd). stat_count = B*H*W of the
-    map the reference normalises (only the unbiased running variance depends on it)."""
-    y, (_, y_raw, _, mean, invstd) = T.vec_layer_fwd(_c(z), w.reshape(w.shape[0], -1), b, gamma, beta, running_mean,
-                                                     running_var, relu, stat_count)
+    z [M, L] (z_initial, z_proj, W_g of a constant map) -> (y, y_raw, mean, invstd): the statistics over the M
+    rows equal those over the M*H*W identical pixels. Functional (running statistics: vaeunet::bn_update_running)."""
+    y, (_, y_raw, _, mean, invstd) = T.vec_layer_fwd(_c(z), w.reshape(w.shape[0], -1), b, gamma, beta, None, None, relu, 1.0)
     return y, y_raw, mean, invstd
 
 
 @vec_layer.register_fake
-def _(z, w, b, gamma, beta, running_mean, running_var, relu, stat_count):
+def _(z, w, b, gamma, beta, relu):
     M, C = z.shape[0], w.shape[0]
     return z.new_empty((M, C)), z.new_empty((M, C)), z.new_empty((C,)), z.new_empty((C,))
 
@@ -625,14 +628,14 @@ def _vl_setup(ctx, inputs, output):
     z, w, b, gamma = inputs[0], inputs[1], inputs[2], inputs[3]
     y, y_raw, mean, invstd = output
     ctx.save_for_backward(z, w, y_raw, y, mean, invstd, gamma)
-    ctx.relu = inputs[7]
+    ctx.relu = inputs[5]
     ctx.set_materialize_grads(False)
 
 
 def _vl_bwd(ctx, dy, dy_raw, dmean, dinvstd):
     z, w, y_raw, y, mean, invstd, gamma = ctx.saved_tensors
     dz, dw, db, dg, dbeta = torch.ops.vaeunet.vec_layer_bwd(_c(dy), z, w, y_raw, y, mean, invstd, gamma, ctx.relu)
-    return dz, dw, db, dg, dbeta, None, None, None, None
+    return dz, dw, db, dg, dbeta, None
 
 
 vec_layer.register_autograd(_vl_bwd, setup_context=_vl_setup)
@@ -685,7 +688,7 @@ def _(logits, Ho, Wo):
 
 OP_NAMES: List[str] = [
     "conv2d", "conv2d_dgrad", "conv2d_wgrad", "channel_sum", "conv_small_cin", "conv_small_cin_wgrad", "conv_transpose2x2",
-    "conv_transpose2x2_bwd", "batch_norm_train", "batch_norm_train_bwd", "maxpool", "maxpool_bwd", "bilinear_ac",
+    "conv_transpose2x2_bwd", "batch_norm_train", "batch_norm_train_bwd", "bn_update_running", "maxpool", "maxpool_bwd", "bilinear_ac",
     "bilinear_ac_bwd", "resize_map", "resize_map_bwd", "conv1x1_to_map", "conv1x1_to_map_bwd", "map_bn_sigmoid",
     "map_bn_sigmoid_bwd", "scale_by_map", "channel_dot", "latent_head", "latent_head_bwd", "reparameterize",
     "reparameterize_bwd", "vec_layer", "vec_layer_bwd", "broadcast_vec", "image_channel_sum", "uncertainty_reduce",

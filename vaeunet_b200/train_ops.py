@@ -50,6 +50,16 @@ def bn_train_fwd(x: Act, gamma, beta, running_mean, running_var, relu: bool, res
     return out, mean, invstd
 
 
+def bn_update_running(mean: torch.Tensor, invstd: torch.Tensor, count: float, running_mean: torch.Tensor,
+                      running_var: torch.Tensor) -> None:
+    """running statistics of nn.BatchNorm2d (momentum 0.1, unbiased variance) from saved batch statistics."""
+    require_device()
+    check(load().vu_bn_update_running(_f32(mean).data_ptr(), _f32(invstd).data_ptr(), float(count), mean.numel(), BN_EPS,
+                                      BN_MOMENTUM, _f32(running_mean).data_ptr(), _f32(running_var).data_ptr(), _stream()),
+          "vu_bn_update_running")
+    _count()
+
+
 def bn_train_bwd(x_raw: Act, dy: Act, y_relu: Optional[Act], mean, invstd, gamma, want_dz: bool = False,
                  dx: Optional[Act] = None, dgamma: Optional[torch.Tensor] = None, dbeta: Optional[torch.Tensor] = None,
                  relu_beta: Optional[torch.Tensor] = None):

@@ -41,6 +41,7 @@ FUSE_BN_STATS = os.environ.get("VU_FUSE_BN_STATS", "1") != "0"
 # backward (only the optimizer reads them), so they overlap the BatchNorm-backward / data-gradient chain instead of
 # sitting inside it: tensor-pipe work under the memory-bound kernels of the chain.
 WGRAD_STREAM = os.environ.get("VU_TRAIN_STREAMS", "1") != "0"
+_SKIP_WGRAD = os.environ.get("VU_DEBUG_SKIP_WGRAD", "0") == "1"
 
 _ALIGN = 64   # floats: every parameter starts on a 256-byte boundary of the flat buffers
 
@@ -264,6 +265,8 @@ class TrainStep:
 
     def _wgrad(self, x: Act, dy: Act, name: str):
         c = self.convs[name]
+        if _SKIP_WGRAD:                # timing experiment only (scripts/train_breakdown.py): the main chain without its leaves
+            return
         if self.side is None:
             ops.conv2d_wgrad(x, dy, c.k, c.stride, c.k // 2, out=self.GP[name])
             return

@@ -58,8 +58,9 @@ class KernelModule(nn.Module):
     def _require_eval(self):
         if self.training:
             raise VaeUnetError(
-                f"{type(self).__name__}.forward in train() mode: the module surface runs the eval-mode "
-                "(folded BatchNorm) kernels; use vaeunet_b200.training.TrainStep for the training step.")
+                f"{type(self).__name__}.forward in train() mode: sub-modules run the eval-mode (folded BatchNorm) "
+                "kernels. Train through the top-level model (UNetResNet / UNet .forward in train() mode uses the "
+                "torch.ops.vaeunet.* autograd path) or vaeunet_b200.training.TrainStep.")
 
 
 def to_act(x: torch.Tensor, dtype=None) -> ops.Act:

@@ -33,7 +33,10 @@ class UNet(KernelModule):
         return UNetEngine(sd, dev, self.bilinear, self.compute_dtype)
 
     def forward(self, x):
-        self._require_eval()
+        if self.training:
+            # train mode (batch-statistics BatchNorm, autograd): torch.ops.vaeunet.* custom ops
+            from ..autograd_path import unet_forward
+            return unet_forward(self, x)
         return self._unit().forward(x)
 
     def use_checkpointing(self):

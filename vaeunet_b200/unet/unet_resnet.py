@@ -247,7 +247,10 @@ class UNetResNet(KernelModule):
         return mu + eps * std
 
     def forward(self, x, eps: Optional[torch.Tensor] = None):
-        self._require_eval()
+        if self.training:
+            # train mode (batch-statistics BatchNorm, autograd): torch.ops.vaeunet.* custom ops, any configuration
+            from ..autograd_path import unetresnet_forward
+            return unetresnet_forward(self, x, eps)
         return self.engine().forward(x.float().contiguous(), eps)
 
     def encode(self, x):
