@@ -256,6 +256,33 @@ int vu_ece_hist(const float* p, const float* gt, size_t n, int num_bins, double*
 int vu_confusion_counts(const float* x, const float* t, size_t n, float thr, double* counts,
                         vu_stream_t stream);
 
+/* ---------------------------------------------------------------- sort-based uncertainty metrics
+ * Device replacements for numpy argsort + sklearn in utils/uncertainty_metrics.py:175-240 (sparsification curve) and
+ * :270-283 (AUROC / AUPRC of "uncertainty predicts error").
+ * vu_sort_pairs_desc_f32: stable LSD radix sort of (score, 32-bit payload) pairs by score DESCENDING; keys_sorted receives
+ * order-preserving unsigned keys (equal keys <=> equal scores). workspace: vu_sort_workspace_bytes(n) bytes, shared with
+ * vu_binary_curve_auc. */
+size_t vu_sort_workspace_bytes(size_t n);
+int vu_sort_pairs_desc_f32(const float* score, const uint32_t* vals, size_t n, uint32_t* keys_sorted, uint32_t* vals_sorted,
+                           void* workspace, size_t workspace_bytes, vu_stream_t stream);
+/* err[i] = -(g log(p + eps) + (1 - g) log(1 - p + eps)) (uncertainty_metrics.py:179-181); stats: 4 doubles -
+ * [0] sum of the non-NaN errors, [1] number of NaNs, and two uint32 in the low words of [2]: order-preserving encodings
+ * (u ^ (sign ? ~0 : 1 << 31)) of the minimum and maximum error. */
+int vu_pixel_nll_errors(const float* p, const float* gt, size_t n, float eps, float* err, double* stats, vu_stream_t stream);
+/* sums[b] = sum of the float values vals_sorted[i], cuts[b] <= i < cuts[b+1] (device int64 cuts[nbins + 1], ascending). */
+int vu_sorted_bin_sums(const uint32_t* vals_sorted, size_t n, const long long* cuts, int nbins, double* sums,
+                       vu_stream_t stream);
+/* out[0] = sum of x[i] over the set bits of a packed keep-mask (bit i & 7 of byte i >> 3): the random-removal baseline of the
+ * sparsification curve, whose subsets come from numpy's RNG stream by the reference's definition (np.random.seed(i + 1000 b)). */
+int vu_masked_sum(const float* x, const uint8_t* bits, size_t n, double* out, vu_stream_t stream);
+/* labels[i] = ((p[i] > thr) != (gt[i] > 0.5)) (uncertainty_metrics.py:271-275). */
+int vu_error_labels(const float* p, const float* gt, size_t n, float thr, uint32_t* labels, vu_stream_t stream);
+/* Binary-classification curve of pairs sorted by score descending (sklearn _binary_clf_curve: cumulative TP / FP at the last
+ * element of every group of tied scores): out[0] = un-normalised ROC trapezoid area, out[1] = un-normalised average
+ * precision, out[2] = positives, out[3] = negatives; AUROC = out[0] / (out[2] out[3]), AP = out[1] / out[2]. */
+int vu_binary_curve_auc(const uint32_t* keys_sorted, const uint32_t* labels_sorted, size_t n, void* workspace,
+                        size_t workspace_bytes, double* out, vu_stream_t stream);
+
 /* ---------------------------------------------------------------- training step (train.py:385-411)
  * Train-mode BatchNorm2d over an NHWC 16-bit slice (unet_parts.py:41,44; unet_resnet.py:61,67 and every timm BN):
  * vu_bn_stats -> sums[0..C) = sum x, sums[C..2C) = sum x^2 (fp64); vu_bn_finalize -> mean / invstd (biased var, eps)

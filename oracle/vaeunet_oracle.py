@@ -778,3 +778,71 @@ def moments_finalize(counts: Sequence[float], mean: Tensor, m2: Tensor, sh: Tens
     std = torch.sqrt((M2 / (n - 1)).clamp_min(0)) if n > 1 else torch.full_like(m, float("nan"))
     ent = _bin_entropy(m)
     return {"mean": m, "std": std, "entropy": ent, "mutual_info": ent - H / n, "coeff_var": std / (m + 1e-7)}
+
+
+# --------------------------------------------------------------------------------------
+# sort-based uncertainty metrics - numpy restatements, TEST INFRASTRUCTURE ONLY
+# --------------------------------------------------------------------------------------
+def sparsification_metrics(pred_probs: Tensor, uncertainties: Tensor, ground_truth: Tensor, num_points: int = 20):
+    """utils/uncertainty_metrics.py:175-240: normalised error of the kept pixels when the most uncertain / random pixels are
+    removed. The random baseline uses numpy's global RNG exactly as the reference (seed i + 1000 b, choice w/o replacement)."""
+    import numpy as np
+    B = pred_probs.shape[0]
+    eps = 1e-7
+    pe = -(ground_truth * torch.log(pred_probs + eps) + (1 - ground_truth) * torch.log(1 - pred_probs + eps))   # :179-181
+    pe = pe.reshape(B, -1).detach().cpu().numpy()
+    un = uncertainties.reshape(B, -1).detach().cpu().numpy()
+    frac = np.linspace(0, 0.99, num_points)
+    er, eu = np.zeros(num_points), np.zeros(num_points)
+    for b in range(B):
+        e, u = pe[b], un[b]
+        if np.all(e == e[0]) or np.isnan(e).any():                                  # :194
+            continue
+        init = e.mean()
+        if init <= 0 or np.isnan(init):
+            continue
+        n = e.shape[0]
+        order = np.argsort(u)[::-1]                                                 # :202
+        for i, f in enumerate(frac):
+            rem = int(n * f)
+            keep = n - rem
+            if f >= 1.0 or keep <= 0:
+                er[i] += 1.0; eu[i] += 1.0
+                continue
+            np.random.seed(i + b * 1000)                                            # :216
+            ridx = np.random.choice(np.arange(n), keep, replace=False)
+            er[i] += e[ridx].mean() / init
+            eu[i] += e[order[rem:]].mean() / init
+    er /= B; eu /= B                                                                # :226-228 (divides by batch_size)
+    if er[0] > 0:
+        er = er / er[0]
+    if eu[0] > 0:
+        eu = eu / eu[0]
+    for i in range(1, num_points):                                                  # :235-237 monotone envelope
+        if eu[i] > eu[i - 1]:
+            eu[i] = eu[i - 1]
+    return frac, np.nan_to_num(er, nan=1.0, posinf=1.0, neginf=0.0), np.nan_to_num(eu, nan=1.0, posinf=1.0, neginf=0.0)
+
+
+def uncertainty_error_auc(mean_pred: Tensor, gt_mask: Tensor, uncertainty_map: Tensor):
+    """utils/uncertainty_metrics.py:270-283 with sklearn 1.x's roc_auc_score / average_precision_score restated in numpy
+    (sklearn/metrics/_ranking.py: _binary_clf_curve - stable sort by score descending, cumulative TP / FP at the last index of
+    every run of equal scores; AUROC = trapezoid over (FPR, TPR) from the origin; AP = sum (R_k - R_{k-1}) P_k)."""
+    import numpy as np
+    pred_binary = (mean_pred > 0.5).float().view(-1).cpu().numpy()
+    y = (pred_binary != gt_mask.view(-1).cpu().numpy()).astype(np.int64)
+    s = uncertainty_map.view(-1).cpu().numpy()
+    if y.min() == y.max():
+        return float("nan"), float("nan")                                            # sklearn raises ValueError; :279-281
+    order = np.argsort(s, kind="mergesort")[::-1]
+    y, s = y[order], s[order]
+    ends = np.r_[np.where(np.diff(s))[0], y.size - 1]
+    tps = np.cumsum(y)[ends].astype(np.float64)
+    fps = 1.0 + ends - tps
+    P, N = tps[-1], fps[-1]
+    tpr, fpr = np.r_[0.0, tps / P], np.r_[0.0, fps / N]
+    auroc = float(np.sum(np.diff(fpr) * (tpr[1:] + tpr[:-1]) * 0.5))
+    prec = tps / (tps + fps)
+    rec = tps / P
+    ap = float(np.sum(np.diff(np.r_[0.0, rec]) * prec))
+    return auroc, ap

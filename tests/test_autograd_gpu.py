@@ -82,8 +82,11 @@ def test_module_train_step_matches_oracle_autograd(cuda_dev, name, kw):
     assert cos >= budget - 0.015 and cos >= 0.98, (name, cos, budget)
     gmax = max(grads_r[k].norm().item() for k in names)
     rel = lambda a, b: ((a - b).norm() / (b.norm() + 1e-20)).item()
+    # per tensor: within 3x its own format budget; single-element tensors (the gate's psi BatchNorm: one scalar that is a
+    # cancelling sum over all pixels) are held to 0.5 instead - a wiring error is O(1) there too
     bad = {k: (rel(got[k], grads_r[k]), rel(grads_q[k], grads_r[k])) for k in names
-           if grads_r[k].norm().item() > 1e-3 * gmax and rel(got[k], grads_r[k]) > 3.0 * rel(grads_q[k], grads_r[k]) + 0.05}
+           if grads_r[k].norm().item() > 1e-3 * gmax and
+           rel(got[k], grads_r[k]) > (3.0 * rel(grads_q[k], grads_r[k]) + 0.05 if grads_r[k].numel() > 1 else 0.5)}
     assert not bad, f"{name}: tensors beyond 3x the format budget: {bad}"
     # running statistics were updated like nn.BatchNorm2d in train mode
     bufs = dict(model.named_buffers())
@@ -169,7 +172,9 @@ def test_basic_unet_train_step_matches_oracle_autograd(cuda_dev, bilinear):
     assert len(names) == len(grads_r), set(grads_r) - set(got)
     fg, fr, fq = _flat(got, names), _flat(grads_r, names), _flat(grads_q, names)
     cos, budget = _cos(fg, fr), _cos(fq, fr)
-    assert cos >= budget - 0.015 and cos >= 0.98, (cos, budget)
+    worst = sorted(((_cos(got[k].flatten(), grads_r[k].flatten()), _cos(grads_q[k].flatten(), grads_r[k].flatten()), k,
+                     grads_r[k].norm().item()) for k in names), key=lambda t: t[0])[:10]
+    assert cos >= budget - 0.015 and cos >= 0.98, (cos, budget, worst)
     if not bilinear:                      # the transposed-conv weights specifically (dW of ConvTranspose2d)
         for k in ("up1.up.weight", "up4.up.weight", "up4.up.bias"):
             assert _cos(got[k].flatten(), grads_r[k].flatten()) >= 0.97, k

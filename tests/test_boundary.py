@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_ctypes_table_matches_header():
-    names = set(_declared()) - {"vu_last_error"}
+    names = set(_declared()) - {"vu_last_error", "vu_sort_workspace_bytes"}   # the two non-int-returning entry points
     assert names == set(_lib.SIGNATURES), (names ^ set(_lib.SIGNATURES))
     _lib.load()  # resolves restype/argtypes for each of them
 

@@ -222,3 +222,32 @@ def test_temperature_ensemble(gold_next, sd):
     assert (out - g["out"]).abs().max() < 1e-5
     out_u = O.generate_ensemble_prediction(sd, CFG, x, g["temps"], g["samples_per_temp"], g["eps"], False, g["patch"], g["overlap"])
     assert (out_u - g["out_unweighted"]).abs().max() < 1e-5
+
+
+def test_sort_based_metrics_f3():
+    """the oracle's numpy restatements of calculate_sparsification_metrics / calculate_uncertainty_error_auc
+    (incl. its own restatement of sklearn's ROC-AUC / average precision) against the reference's outputs."""
+    import math
+    from vaeunet_b200.testing import f3_inputs
+    F3 = torch.load(G / "golden_f3.pt", weights_only=False)
+    for tag in ("sp_small", "sp_one"):
+        g = F3[tag]
+        B, H, W = g["shape"]
+        p, gt, unc = f3_inputs(g["seed"], B, H, W, False)
+        fr, er, eu = O.sparsification_metrics(p, unc, gt, 20)
+        assert abs(fr - g["frac"].numpy()).max() == 0
+        assert abs(er - g["rand"].numpy()).max() < 1e-12 and abs(eu - g["unc"].numpy()).max() < 1e-12
+    g = F3["sp_degenerate"]
+    p, gt, unc = f3_inputs(13, 2, 20, 24, False)
+    p[1] = 0.5; gt[1] = 1.0
+    _, er, eu = O.sparsification_metrics(p, unc, gt, 10)
+    assert abs(er - g["rand"].numpy()).max() < 1e-12 and abs(eu - g["unc"].numpy()).max() < 1e-12
+    for tag in ("auc_cont", "auc_ties"):
+        g = F3[tag]
+        H, W = g["shape"]
+        p, gt, unc = f3_inputs(g["seed"], 1, H, W, g["ties"])
+        a, b = O.uncertainty_error_auc(p[0], gt[0], unc[0])
+        assert abs(a - g["auroc"]) < 1e-12 and abs(b - g["auprc"]) < 1e-12
+    p, gt, unc = f3_inputs(23, 1, 16, 16, False)
+    a, b = O.uncertainty_error_auc(p[0], (p[0] > 0.5).float(), unc[0])
+    assert math.isnan(a) and math.isnan(b) and math.isnan(F3["auc_one_class"]["auroc"])

@@ -77,6 +77,13 @@ SIGNATURES = {
     "vu_kl_free_bits": [p, p, i, i, f, p, p, p, f, p],
     "vu_ece_hist": [p, p, sz, i, p, p],
     "vu_confusion_counts": [p, p, sz, f, p, p],
+    # ---- sort-based uncertainty metrics
+    "vu_sort_pairs_desc_f32": [p, p, sz, p, p, p, sz, p],
+    "vu_pixel_nll_errors": [p, p, sz, f, p, p, p],
+    "vu_sorted_bin_sums": [p, sz, p, i, p, p],
+    "vu_masked_sum": [p, p, sz, p, p],
+    "vu_error_labels": [p, p, sz, f, p, p],
+    "vu_binary_curve_auc": [p, p, sz, p, sz, p, p],
     # ---- training step
     "vu_bn_stats": [p, sz, i, i, i, p, i, p],
     "vu_bn_finalize": [p, C.c_double, i, f, f, p, p, p, p, p],
@@ -122,6 +129,8 @@ def load() -> C.CDLL:
     lib = C.CDLL(str(LIB_PATH))
     lib.vu_last_error.restype = C.c_char_p
     lib.vu_last_error.argtypes = []
+    lib.vu_sort_workspace_bytes.restype = C.c_size_t
+    lib.vu_sort_workspace_bytes.argtypes = [C.c_size_t]
     for name, argt in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the .so is stale
         fn.restype = C.c_int

@@ -390,7 +390,8 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     wp.num_pix_tiles = wp.tiles_w * wp.tiles_h * wp.tiles_n;
     // measured on B200 (scripts/prof_wgrad.py): the row kernel wins from 2048 pixel tiles up (+30..60 %), the per-tap kernel
     // below 512 (three times more work items keep the K splits long enough to amortise prologue + reductions)
-    if (wp.num_pix_tiles < 1024 && !getenv("VU_WGRAD_ROW3")) return 0;
+    static const int row3_min = getenv("VU_WGRAD_ROW3_MIN") ? atoi(getenv("VU_WGRAD_ROW3_MIN")) : 1024;
+    if (wp.num_pix_tiles < row3_min && !getenv("VU_WGRAD_ROW3")) return 0;
     wp.cout = a->Cout; wp.cin = a->Cin; wp.dw = dw; wp.dtype = a->dtype;
     const int bn = (a->Cin > 64) ? 128 : 64;
     wp.num_m_tiles = (a->Cout + 127) / 128;
@@ -403,7 +404,8 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     if (wp.stages > 4) wp.stages = 4;
     if (wp.stages < 2) return 0;
     const int base_items = 3 * wp.num_m_tiles * wp.num_n_tiles;
-    int ksplit = (2 * num_sms() + base_items - 1) / base_items;
+    static const int waves_x2 = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 3;   // CTAs = SMs * waves_x2 / 2 (sweep: profiles/r2f_wgrad_knobs.log)
+    int ksplit = (waves_x2 * num_sms() / 2 + base_items - 1) / base_items;
     if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
     if (ksplit < 1) ksplit = 1;
     wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;
@@ -466,7 +468,8 @@ static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy
     wp.num_n_tiles = (a->Cin + bn - 1) / bn;
     const int base_items = wp.num_taps * wp.num_m_tiles * wp.num_n_tiles;
     // K splits: fill ~2 waves of SMs, at least 4 k-iterations per item
-    int ksplit = (2 * num_sms() + base_items - 1) / base_items;
+    static const int waves_x2 = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 3;
+    int ksplit = (waves_x2 * num_sms() / 2 + base_items - 1) / base_items;
     if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
     if (ksplit < 1) ksplit = 1;
     wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;

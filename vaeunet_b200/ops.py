@@ -628,3 +628,90 @@ def confusion_counts(x: torch.Tensor, t: torch.Tensor, thr: float = 0.5) -> torc
           "vu_confusion_counts")
     _count(2)
     return c
+
+
+# ------------------------------------------------------------------ sort-based uncertainty metrics
+def _sort_ws(n: int, dev) -> torch.Tensor:
+    return torch.empty(int(load().vu_sort_workspace_bytes(n)), dtype=torch.uint8, device=dev)
+
+
+def sort_pairs_desc(score: torch.Tensor, vals: torch.Tensor, ws: Optional[torch.Tensor] = None):
+    """Stable sort of (score fp32, payload 32-bit) pairs by score DESCENDING. -> (keys uint32-as-int32: order-preserving
+    keys whose equality == score equality, payload in sorted order, workspace)."""
+    require_device()
+    score = _f32(score.contiguous().view(-1))
+    n = score.numel()
+    assert vals.numel() == n and vals.element_size() == 4 and vals.is_contiguous()
+    if ws is None:
+        ws = _sort_ws(n, score.device)
+    keys = torch.empty(n, dtype=torch.int32, device=score.device)
+    out = torch.empty(n, dtype=vals.dtype, device=score.device)
+    check(load().vu_sort_pairs_desc_f32(score.data_ptr(), vals.data_ptr(), n, keys.data_ptr(), out.data_ptr(), ws.data_ptr(),
+                                        ws.numel(), _stream()), "vu_sort_pairs_desc_f32")
+    _count(1 + 3 * 8)
+    return keys, out, ws
+
+
+def pixel_nll_errors(p: torch.Tensor, gt: torch.Tensor, eps: float = 1e-7):
+    """-> (err fp32 like p, stats dict: sum, nan_count, min, max) — uncertainty_metrics.py:179-181."""
+    require_device()
+    p = _f32(p.contiguous()); gt = _f32(gt.float().contiguous())
+    err = torch.empty_like(p)
+    stats = torch.zeros(4, dtype=torch.float64, device=p.device)
+    check(load().vu_pixel_nll_errors(p.data_ptr(), gt.data_ptr(), p.numel(), float(eps), err.data_ptr(), stats.data_ptr(),
+                                     _stream()), "vu_pixel_nll_errors")
+    _count()
+    return err, stats
+
+
+def decode_nll_stats(stats: torch.Tensor):
+    """host view of pixel_nll_errors' statistics (one device -> host read)."""
+    import struct
+    raw = stats.cpu()
+    s, nans = float(raw[0]), float(raw[1])
+    mm = raw[2:3].view(torch.int32)
+    dec = lambda u: struct.unpack("<f", struct.pack("<I", (u ^ 0x80000000) if (u >> 31) else (~u & 0xFFFFFFFF)))[0]
+    lo, hi = int(mm[0]) & 0xFFFFFFFF, int(mm[1]) & 0xFFFFFFFF
+    return s, nans, dec(lo), dec(hi)
+
+
+def sorted_bin_sums(vals_sorted: torch.Tensor, cuts: torch.Tensor) -> torch.Tensor:
+    """vals_sorted: fp32 values (any 32-bit dtype holding float bits); cuts int64 [nb+1] on the device -> fp64 [nb]."""
+    require_device()
+    nb = cuts.numel() - 1
+    assert cuts.dtype == torch.int64 and cuts.is_cuda and cuts.is_contiguous()
+    sums = torch.empty(nb, dtype=torch.float64, device=vals_sorted.device)
+    check(load().vu_sorted_bin_sums(vals_sorted.data_ptr(), vals_sorted.numel(), cuts.data_ptr(), nb, sums.data_ptr(), _stream()),
+          "vu_sorted_bin_sums")
+    _count()
+    return sums
+
+
+def masked_sum(x: torch.Tensor, bits: torch.Tensor) -> torch.Tensor:
+    """sum of fp32 x over the set bits of a packed uint8 keep-mask (little bit order) -> fp64 scalar tensor."""
+    require_device()
+    x = _f32(x.contiguous())
+    assert bits.dtype == torch.uint8 and bits.is_cuda and bits.numel() * 8 >= x.numel()
+    out = torch.empty(1, dtype=torch.float64, device=x.device)
+    check(load().vu_masked_sum(x.data_ptr(), bits.data_ptr(), x.numel(), out.data_ptr(), _stream()), "vu_masked_sum")
+    _count()
+    return out
+
+
+def error_labels(p: torch.Tensor, gt: torch.Tensor, thr: float = 0.5) -> torch.Tensor:
+    require_device()
+    p = _f32(p.contiguous()); gt = _f32(gt.float().contiguous())
+    lab = torch.empty(p.numel(), dtype=torch.int32, device=p.device)
+    check(load().vu_error_labels(p.data_ptr(), gt.data_ptr(), p.numel(), float(thr), lab.data_ptr(), _stream()), "vu_error_labels")
+    _count()
+    return lab
+
+
+def binary_curve_auc(keys_sorted: torch.Tensor, labels_sorted: torch.Tensor, ws: torch.Tensor) -> torch.Tensor:
+    """-> fp64 [4]: un-normalised ROC area, un-normalised average precision, positives, negatives."""
+    require_device()
+    out = torch.empty(4, dtype=torch.float64, device=keys_sorted.device)
+    check(load().vu_binary_curve_auc(keys_sorted.data_ptr(), labels_sorted.data_ptr(), keys_sorted.numel(), ws.data_ptr(),
+                                     ws.numel(), out.data_ptr(), _stream()), "vu_binary_curve_auc")
+    _count(5)
+    return out

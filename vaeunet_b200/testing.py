@@ -88,3 +88,16 @@ def resnet_variant_state(seed: int = 0, **model_kwargs):
         if k in sd and sd[k].shape == v.shape and not k.startswith("decoder_blocks."):
             sd[k] = v.clone()
     return sd, kw
+
+
+def f3_inputs(seed: int, B: int, H: int, W: int, ties: bool):
+    """Correlated synthetic (probabilities, ground truth, uncertainty): uncertainty is high where the prediction is wrong."""
+    g = torch.Generator().manual_seed(seed)
+    gt = (torch.rand(B, H, W, generator=g) > 0.8).float()
+    logit = (gt * 2 - 1) * 1.5 + torch.randn(B, H, W, generator=g) * 1.8
+    p = torch.sigmoid(logit)
+    wrong = ((p > 0.5).float() != gt).float()
+    unc = (0.05 + 0.10 * wrong + 0.35 * torch.rand(B, H, W, generator=g) + 0.3 * (p * (1 - p))).clamp(0, 1)
+    if ties:
+        unc = torch.round(unc * 50) / 50          # heavy ties: sklearn groups equal thresholds
+    return p, gt, unc
