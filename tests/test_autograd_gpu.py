@@ -145,7 +145,7 @@ def test_basic_unet_train_step_matches_oracle_autograd(cuda_dev, bilinear):
     dev = cuda_dev
     sd = testing.unet_fixture(bilinear=bilinear)
     model = UNet(3, 1, bilinear); model.load_state_dict(sd); model = model.to(dev); model.compute_dtype = "f16"
-    B, S = 4, 64
+    B, S = 4, 128          # deepest maps 8 x 8: BatchNorm over 256 values per channel (at 64^2 it is 64 values and chaotic)
     x, m = synthetic_fundus(B, S, S, seed=51)
     leaves = {k: (v.detach().clone().requires_grad_(True) if v.is_floating_point() and not k.endswith(("running_mean", "running_var")) else v)
               for k, v in sd.items()}
@@ -172,8 +172,10 @@ def test_basic_unet_train_step_matches_oracle_autograd(cuda_dev, bilinear):
     assert len(names) == len(grads_r), set(grads_r) - set(got)
     fg, fr, fq = _flat(got, names), _flat(grads_r, names), _flat(grads_q, names)
     cos, budget = _cos(fg, fr), _cos(fq, fr)
-    worst = sorted(((_cos(got[k].flatten(), grads_r[k].flatten()), _cos(grads_q[k].flatten(), grads_r[k].flatten()), k,
-                     grads_r[k].norm().item()) for k in names), key=lambda t: t[0])[:10]
+    tot = float((fg - fr).double().square().sum())
+    worst = sorted(((float((got[k] - grads_r[k]).double().square().sum()) / tot, _cos(got[k].flatten(), grads_r[k].flatten()),
+                     _cos(grads_q[k].flatten(), grads_r[k].flatten()), k) for k in names), key=lambda t: -t[0])[:8]
+    worst = [(round(a, 3), round(b, 4), round(c, 4), k) for a, b, c, k in worst]
     assert cos >= budget - 0.015 and cos >= 0.98, (cos, budget, worst)
     if not bilinear:                      # the transposed-conv weights specifically (dW of ConvTranspose2d)
         for k in ("up1.up.weight", "up4.up.weight", "up4.up.bias"):
@@ -196,3 +198,29 @@ def test_custom_ops_registered_with_fake_and_autograd(cuda_dev):
     assert ((y.float().cpu().permute(0, 3, 1, 2) - ref).abs().max() <= 2e-2 * ref.abs().max())
     y.float().square().sum().backward()
     assert x.grad is not None and w.grad is not None and w.grad.shape == w.shape
+
+
+def test_conv_transpose2x2_op_matches_torch_autograd(cuda_dev):
+    """vaeunet::conv_transpose2x2 forward / dX / dW / db against F.conv_transpose2d autograd on the same 16-bit-rounded
+    operands (ConvTranspose2d k2 s2 of unet/unet_parts.py:76; north_star: dgrad and wgrad of the transposed-conv layers)."""
+    import torch.nn.functional as F
+    dev = cuda_dev
+    g = torch.Generator().manual_seed(61)
+    N, H, W, I, O = 3, 12, 20, 128, 64
+    x = torch.randn(N, I, H, W, generator=g).half().float()
+    w = (torch.randn(I, O, 2, 2, generator=g) / (I ** 0.5)).half().float()
+    b = torch.randn(O, generator=g) * 0.1
+    dy = torch.randn(N, O, 2 * H, 2 * W, generator=g).half().float()
+    xr, wr, br = x.clone().requires_grad_(True), w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = F.conv_transpose2d(xr, wr, br, stride=2)
+    ref.backward(dy)
+    xd = x.permute(0, 2, 3, 1).contiguous().half().to(dev).requires_grad_(True)
+    wd, bd = w.to(dev).requires_grad_(True), b.to(dev).requires_grad_(True)
+    y = torch.ops.vaeunet.conv_transpose2x2(xd, wd, bd)
+    y.backward(dy.permute(0, 2, 3, 1).contiguous().half().to(dev))
+    torch.cuda.synchronize()
+    rel = lambda a, r: ((a.float().cpu() - r).norm() / r.norm()).item()
+    assert rel(y.detach().permute(0, 3, 1, 2), ref.detach()) < 2e-3
+    assert rel(xd.grad.permute(0, 3, 1, 2), xr.grad) < 3e-3          # four f16 partial accumulations
+    assert rel(wd.grad, wr.grad) < 2e-3
+    assert rel(bd.grad, br.grad) < 1e-3

@@ -81,6 +81,37 @@ def _tiles_probs(eng, img, z_dec_rows: torch.Tensor, info, idxs, Ns: int):
     return ops.resize_logits(lg.reshape(T * Ns, h, w), ph, pw, ops.SIG_PRE).reshape(T, Ns, ph, pw)
 
 
+def _blend_weight_map(ph: int, pw: int, i: int, j: int, nh: int, nw: int, overlap: int, device) -> torch.Tensor:
+    """Ramp weights of tile (i, j) in an nh x nw grid (visualize_vae.py:361-378 == :451-470): linspace(0, 1, overlap) on
+    every edge that has a neighbour, only when the tile is longer than 2 * overlap along that axis. Built by running the
+    blend kernel on a tile of ones into an empty canvas of the tile's own size."""
+    ones = torch.ones((ph, pw), dtype=torch.float32, device=device)
+    acc = torch.zeros((ph, pw), dtype=torch.float32, device=device)
+    ws = torch.zeros((ph, pw), dtype=torch.float32, device=device)
+    ops.blend_accumulate(ones, 0, 0, i, j, nh, nw, overlap, acc, ws)
+    return ws
+
+
+def predict_single_patch(model, patch, z, device=None, overlap=100, patch_grid=(1, 1), patch_idx=0):
+    """visualize_vae.py:418-476 (the memory-fallback helper of predict_with_patches): one tile through encoder + decode(z)
+    -> sigmoid at tile/2 -> bilinear up to the tile, plus the tile's ramp blend weight. -> (patch_pred [B,1,h,w], weight
+    [B,1,h,w]). (The reference's version always starts from z_initial whatever `use_bottleneck` says; models
+    without a bottleneck latent go through predict_with_patches' own path.)"""
+    model.eval()
+    eng = model.engine()
+    nh, nw = patch_grid
+    i, j = divmod(int(patch_idx), nw)
+    with torch.no_grad():
+        patch = patch.float().contiguous()
+        B, _, ph, pw = patch.shape
+        feats = eng.encode(patch)
+        lg = eng.decode(feats, _z_vec(z).expand(B, -1).contiguous(), honour_use_skip=False)
+        h, w = lg.shape[2:]
+        pred = ops.resize_logits(lg.reshape(B, h, w), ph, pw, ops.SIG_PRE).reshape(B, 1, ph, pw)
+        wt = _blend_weight_map(ph, pw, i, j, nh, nw, int(overlap), patch.device)
+    return pred, wt.view(1, 1, ph, pw).expand(B, 1, ph, pw).contiguous()
+
+
 def predict_with_patches(model, img, z, patch_size=512, overlap=None, batch_size=4):
     """visualize_vae.py:243-415 for one z ([1,L,1,1]). -> [1,1,H,W] blended probabilities."""
     out = blended_samples(model, img, _z_vec(z), patch_size, overlap, batch_size)
