@@ -234,6 +234,39 @@ int vu_blend_accumulate(const float* tile, int ph, int pw, int sh, int sw, int t
                         int overlap, float* acc, float* wsum, int H, int W, vu_stream_t stream);
 int vu_blend_finalize(const float* acc, const float* wsum, float* out, size_t n, vu_stream_t stream);
 
+/* One launch for a batch of T equal-sized tiles x Ns MC samples (tiles fp32 [T][Ns][ph][pw]; info int32 [T][4] =
+ * {sh, sw, ti, tj} on the device): every pixel of the batch's bounding box [y0,y1) x [x0,x1) is owned by one thread that walks
+ * the tiles in index order (no atomics; the same fp32 summation order as one vu_blend_accumulate per tile). acc fp32
+ * [Ns][H][W]; wsum fp32 [H][W] - ONE weight map, the ramp weights do not depend on the sample. */
+int vu_blend_accumulate_batch(const float* tiles, const int* info, int T, int Ns, int ph, int pw, int nth, int ntw,
+                              int overlap, float* acc, float* wsum, int H, int W, int y0, int y1, int x0, int x1,
+                              vu_stream_t stream);
+/* out[n][i] = acc[n][i] / (wsum[i] + 1e-8), i < plane (visualize_vae.py:409 with the shared weight map). */
+int vu_blend_finalize_shared(const float* acc, const float* wsum, float* out, size_t plane, int Ns, vu_stream_t stream);
+
+/* ---------------------------------------------------------------- patch pipeline
+ * Device side of utils/data_loading.py:302-446,580-601 (resize -> /255 -> 50 %-overlap tiling -> black-border / lesion
+ * flags) and of the tile cutting of predict_with_patches (visualize_vae.py:253-300): the decoded 8-bit image goes to the
+ * device once, everything after it stays there.
+ * vu_resample_u8: ONE pass (axis 0 = along x, 1 = along y) of Pillow's 8-bit ImagingResample on an HWC image with
+ * host-built tables: bounds int32 [out][2] = {first input index, taps}, kk int32 [out][ksize] = coefficients in 22-bit
+ * fixed point; the result is rounded and clipped to 8 bits like Pillow's intermediate and final images (bit-exact with
+ * PIL.Image.resize for BICUBIC / BILINEAR / LANCZOS / BOX when the tables come from the same formulas).
+ * vu_nearest_u8: dst[y][x] = src[yi[y]][xi[x]] (Image.NEAREST with host-built index tables; masks). */
+int vu_resample_u8(const uint8_t* src, int Hs, int Ws, int C, uint8_t* dst, int Hd, int Wd, int axis, const int* bounds,
+                   const int* kk, int ksize, vu_stream_t stream);
+int vu_nearest_u8(const uint8_t* src, int Hs, int Ws, int C, uint8_t* dst, int Hd, int Wd, const int* yi, const int* xi,
+                  vu_stream_t stream);
+/* out fp32 NCHW [T][C][ph][pw] = tiles of one image at coords int32 [T][2] = {y0, x0} (device). src: uint8 HWC [H][W][C]
+ * (src_is_u8; values are divided by `divisor`, 255 for images) or fp32 CHW [C][H][W]. binarise: out = (value > 0) ? 1 : 0
+ * (the reference's mask conversion). Pixels outside the image are 0. */
+int vu_tile_gather(const void* src, int src_is_u8, int C, int H, int W, const int* coords, int T, int ph, int pw,
+                   float divisor, int binarise, float* out, vu_stream_t stream);
+/* stats fp32 [T][2]: {fraction of pixels whose channel mean < black_thr (is_valid_patch, data_loading.py:287-300), 1 if any
+ * mask pixel > 0.5 (has_lesion, :382) else 0}. masks fp32 [T][ph][pw] or NULL. */
+int vu_tile_stats(const float* tiles, int T, int C, int ph, int pw, const float* masks, float black_thr, float* stats,
+                  vu_stream_t stream);
+
 /* ---------------------------------------------------------------- losses / metrics
  * One pass over logits+targets -> 8 partial sums (fp64 accumulators in `sums`):
  *   [0] sum p, [1] sum t, [2] sum p*t, [3] sum BCE-with-logits, [4] sum focal term,

@@ -846,3 +846,104 @@ def uncertainty_error_auc(mean_pred: Tensor, gt_mask: Tensor, uncertainty_map: T
     rec = tps / P
     ap = float(np.sum(np.diff(np.r_[0.0, rec]) * prec))
     return auroc, ap
+
+
+# --------------------------------------------------------------------------------------
+# patch pipeline - numpy restatements, TEST INFRASTRUCTURE ONLY
+# --------------------------------------------------------------------------------------
+# The reference resizes with PIL (utils/data_loading.py:587-590; `pillow~=10.3.0`, requirements.txt:8 - a third-party
+# dependency that is not vendored). Restated from Pillow's src/libImaging/Resample.c (bicubic_filter, precompute_coeffs,
+# normalize_coeffs_8bpc, ImagingResampleHorizontal_8bpc / Vertical_8bpc) and Geometry.c (ImagingScaleAffine + nearest);
+# tests/test_oracle_golden.py pins it bit for bit against PIL.Image.resize.
+def _pil_bicubic(x: float) -> float:
+    a = -0.5
+    x = -x if x < 0.0 else x
+    if x < 1.0:
+        return ((a + 2.0) * x - (a + 3.0)) * x * x + 1
+    if x < 2.0:
+        return (((x - 5) * x + 8) * x - 4) * a
+    return 0.0
+
+
+def _pil_coeffs(in_size: int, out_size: int):
+    import math
+    import numpy as np
+    bits = 32 - 8 - 2
+    scale = in_size / out_size
+    fscale = scale if scale > 1.0 else 1.0
+    support = 2.0 * fscale
+    ksize = int(math.ceil(support)) * 2 + 1
+    bounds, kk = [], np.zeros((out_size, ksize), dtype=np.int64)
+    for xx in range(out_size):
+        center = (xx + 0.5) * scale
+        xmin = max(int(center - support + 0.5), 0)
+        xmax = min(int(center + support + 0.5), in_size) - xmin
+        w = [_pil_bicubic((x + xmin - center + 0.5) / fscale) for x in range(xmax)]
+        ww = 0.0
+        for v in w:
+            ww += v
+        for x, v in enumerate(w):
+            v = v / ww if ww != 0.0 else v
+            kk[xx, x] = int(-0.5 + v * (1 << bits)) if v < 0 else int(0.5 + v * (1 << bits))
+        bounds.append((xmin, xmax))
+    return bounds, kk, bits
+
+
+def pil_resize_u8(arr, new_w: int, new_h: int, is_mask: bool):
+    """np.array(Image.fromarray(arr).resize((new_w, new_h), NEAREST if is_mask else BICUBIC)) for a uint8 [H,W(,C)] array."""
+    import numpy as np
+    a = arr if arr.ndim == 3 else arr[..., None]
+    H, W, C = a.shape
+    if is_mask:
+        def tab(n_in, n_out):
+            step, xo, t = n_in / n_out, (n_in / n_out) * 0.5, []
+            for _ in range(n_out):
+                t.append(int(xo)); xo += step
+            return np.array(t)
+        out = a[tab(H, new_h)][:, tab(W, new_w)]
+    else:
+        x = a.astype(np.int64)
+        if new_w != W:
+            bounds, kk, bits = _pil_coeffs(W, new_w)
+            o = np.zeros((H, new_w, C), dtype=np.int64)
+            for xx, (f, n) in enumerate(bounds):
+                o[:, xx] = np.clip(((1 << (bits - 1)) + (x[:, f:f + n] * kk[xx, :n][None, :, None]).sum(1)) >> bits, 0, 255)
+            x = o
+        if new_h != H:
+            bounds, kk, bits = _pil_coeffs(H, new_h)
+            o = np.zeros((new_h, x.shape[1], C), dtype=np.int64)
+            for yy, (f, n) in enumerate(bounds):
+                o[yy] = np.clip(((1 << (bits - 1)) + (x[f:f + n] * kk[yy, :n][:, None, None]).sum(0)) >> bits, 0, 255)
+            x = o
+        out = x.astype(np.uint8)
+    return out if arr.ndim == 3 else out[..., 0]
+
+
+def patch_pipeline(img_u8, mask_u8, patch_size: int, scale: float, split: str = "train", skip_border_check: bool = False):
+    """preprocess + the patch loop of precompute_all_patches (utils/data_loading.py:580-601, 368-398):
+    -> (images [T,3,p,p] fp32, masks [T,1,p,p] fp32, coords, has_lesion list) of the kept patches."""
+    import numpy as np
+    H, W = img_u8.shape[:2]
+    new_w, new_h = int(scale * W), int(scale * H)
+    img = pil_resize_u8(img_u8, new_w, new_h, False) if (new_w, new_h) != (W, H) else img_u8
+    msk = pil_resize_u8(mask_u8, new_w, new_h, True) if (new_w, new_h) != (W, H) else mask_u8
+    it = torch.as_tensor((img.astype(np.float32) / 255.0).transpose(2, 0, 1))          # :599-600
+    mt = torch.as_tensor((msk > 0).astype(np.float32)).unsqueeze(0)                      # :595
+    _, h, w = it.shape
+    imgs, masks, coords, lesion = [], [], [], []
+    if h < patch_size or w < patch_size:                                                 # :368
+        return None, None, coords, lesion
+    stride = patch_size // 2
+    thr = 0.5 if split == "test" else 0.1                                                # :293-294
+    for y in range(0, h - patch_size + 1, stride):
+        for x in range(0, w - patch_size + 1, stride):
+            ip = it[:, y:y + patch_size, x:x + patch_size]
+            mp = mt[:, y:y + patch_size, x:x + patch_size]
+            if not skip_border_check:
+                black_ratio = (ip.mean(dim=0) < 0.1).float().mean().item()             # :296-299
+                if black_ratio > thr:
+                    continue
+            imgs.append(ip); masks.append(mp); coords.append((y, x)); lesion.append(bool(torch.any(mp > 0.5)))   # :382
+    if not imgs:
+        return None, None, coords, lesion
+    return torch.stack(imgs), torch.stack(masks), coords, lesion

@@ -59,6 +59,9 @@ def _sample_case(rank, world):
     mean, m2, sh = O.moments_partial(probs[lo:hi])
     res = D.merge_sample_moments(hi - lo, mean, m2, sh, O.moments_finalize)
     ref = O.calculate_uncertainty_metrics(probs.unsqueeze(2))
+    # the sync-free form: every rank derives the per-rank counts locally, ONE all-gather, no host read-back
+    res2 = D.merge_sample_moments(hi - lo, mean, m2, sh, O.moments_finalize, all_counts=D.shard_counts(N, world))
+    assert all(torch.equal(res[k], res2[k]) for k in res)
     return {k: float((res[k] - ref[k]).abs().max()) for k in ref}
 
 
@@ -76,7 +79,7 @@ def _empty_shard_case(rank, world):
         mean, m2, sh = O.moments_partial(probs[lo:hi])
     else:
         mean = torch.zeros(1, 4, 4); m2 = torch.zeros(1, 4, 4); sh = torch.zeros(1, 4, 4)
-    res = D.merge_sample_moments(hi - lo, mean, m2, sh, O.moments_finalize)
+    res = D.merge_sample_moments(hi - lo, mean, m2, sh, O.moments_finalize, all_counts=D.shard_counts(1, world))
     return float((res["mean"] - probs[0]).abs().max()), bool(torch.isnan(res["std"]).all())
 
 

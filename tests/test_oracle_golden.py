@@ -251,3 +251,29 @@ def test_sort_based_metrics_f3():
     p, gt, unc = f3_inputs(23, 1, 16, 16, False)
     a, b = O.uncertainty_error_auc(p[0], (p[0] > 0.5).float(), unc[0])
     assert math.isnan(a) and math.isnan(b) and math.isnan(F3["auc_one_class"]["auroc"])
+
+
+def test_patch_pipeline_f4():
+    """the oracle's restatement of Pillow's 8-bit resampling + the reference's patch loop against the golden
+    hashes from the unmodified reference (IDRIDDataset.preprocess / is_valid_patch), and directly against PIL when present."""
+    import hashlib
+    import numpy as np
+    from vaeunet_b200.testing import f4_inputs
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    F4 = torch.load(G / "golden_f4.pt", weights_only=False)
+    for tag, g in F4.items():
+        img, mask = f4_inputs(g["seed"], *g["shape"])
+        imgs, masks, coords, lesion = O.patch_pipeline(img, mask, g["patch"], g["scale"], g["split"])
+        assert coords == g["coords"] and lesion == g["lesion"], tag
+        hs = [sha(imgs[i].contiguous().numpy())[:16] + sha(masks[i].contiguous().numpy())[:16] for i in range(len(coords))]
+        assert hs == g["hashes"], tag                       # bit-exact patches
+    try:
+        from PIL import Image
+    except ImportError:
+        return
+    rng = np.random.default_rng(5)
+    for (H, W, nh, nw) in [(97, 131, 24, 32), (50, 70, 75, 105), (233, 177, 58, 44)]:
+        a = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        assert np.array_equal(O.pil_resize_u8(a, nw, nh, False), np.array(Image.fromarray(a).resize((nw, nh), resample=Image.BICUBIC)))
+        m = (rng.integers(0, 2, (H, W), dtype=np.uint8) * 255)
+        assert np.array_equal(O.pil_resize_u8(m, nw, nh, True), np.array(Image.fromarray(m).resize((nw, nh), resample=Image.NEAREST)))

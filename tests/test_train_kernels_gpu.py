@@ -68,7 +68,10 @@ def test_conv_epilogue_bn_statistics(cuda_dev):
     channel tiles) alike. Checked against fp64 sums of the output read back."""
     from vaeunet_b200 import ops
     g = torch.Generator().manual_seed(5)
-    for name, N, H, W, Cin, Cout, k, stride, bias in [("halo64", 2, 64, 64, 64, 64, 3, 1, False), ("halo32", 1, 96, 160, 96, 32, 3, 1, False),
+    for name, N, H, W, Cin, Cout, k, stride, bias in [("w64_c64", 2, 64, 64, 64, 64, 3, 1, False), ("w160_c32", 1, 96, 160, 96, 32, 3, 1, False),
+                                                      # the smem tap-reuse kernel in its statistics flavour (W >= 96, Cout 64 / 128)
+                                                      ("halo64_w128", 2, 10, 128, 64, 64, 3, 1, False), ("halo224_w256", 1, 7, 256, 224, 64, 3, 1, False),
+                                                      ("halo128_w128", 3, 12, 128, 128, 128, 3, 1, False), ("halo64_odd", 2, 35, 175, 96, 64, 3, 1, False),
                                                       ("ig128", 2, 32, 32, 64, 128, 3, 1, False), ("ig_s2", 2, 33, 31, 64, 128, 3, 2, False),
                                                       ("ig_1x1_bias", 3, 20, 28, 128, 64, 1, 1, True), ("ig_320", 1, 16, 16, 64, 320, 3, 1, False),
                                                       ("ig_512", 4, 8, 8, 256, 512, 3, 1, False)]:

@@ -72,6 +72,12 @@ SIGNATURES = {
     "vu_moments_finalize": [p, p, p, p, i, sz, p, p, p, p, p, p],
     "vu_blend_accumulate": [p, i, i, i, i, i, i, i, i, i, p, p, i, i, p],
     "vu_blend_finalize": [p, p, p, sz, p],
+    "vu_blend_accumulate_batch": [p, p, i, i, i, i, i, i, i, p, p, i, i, i, i, i, i, p],
+    "vu_blend_finalize_shared": [p, p, p, sz, i, p],
+    "vu_resample_u8": [p, i, i, i, p, i, i, i, p, p, i, p],
+    "vu_nearest_u8": [p, i, i, i, p, i, i, p, p, p],
+    "vu_tile_gather": [p, i, i, i, i, p, i, i, i, f, i, p, p],
+    "vu_tile_stats": [p, i, i, i, i, p, f, p, p],
     "vu_seg_loss_sums": [p, p, sz, i, f, f, p, p],
     "vu_seg_loss_bwd": [p, p, sz, p, f, f, f, f, f, f, f, p, p],
     "vu_kl_free_bits": [p, p, i, i, f, p, p, p, f, p],

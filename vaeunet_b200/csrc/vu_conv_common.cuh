@@ -86,14 +86,13 @@ __device__ __forceinline__ void epi_stats_chunk(const uint32_t (&outw)[16], bool
         *ps = a; *pq = b;
     }
 }
-// After the block-wide barrier at the end of a kernel: combine the four quarters in a fixed order in fp64 and flush this
-// CTA's partials with one fp64 atomic per channel and statistic.
+// After the block-wide barrier at the end of a kernel: combine the `nparts` private slices in a fixed order in fp64 and flush
+// this CTA's partials with one fp64 atomic per channel and statistic.
 __device__ __forceinline__ void epi_stats_flush(const float* s_stat, double* stat_sums, int cout, int tid, int nthreads,
-                                                int stride = kEpiStatMaxCout) {
+                                                int stride = kEpiStatMaxCout, int nparts = 4) {
     for (int c = tid; c < cout; c += nthreads) {
         double a = 0.0, b = 0.0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < nparts; ++q) {
             a += (double)s_stat[(q * 2) * stride + c];
             b += (double)s_stat[(q * 2 + 1) * stride + c];
         }

@@ -45,8 +45,9 @@ struct HaloParams {
 // PAIR: cluster of two CTAs, tcgen05 cta_group::2 - each CTA stages its own pixel tile and HALF of the filter rows of a tap;
 // the leader's M = 256 MMA reads both (see conv_igemm_pair_kernel). Per MMA an SM then reads 4 KB + BN*16 B of smem operands
 // instead of 4 KB + BN*32 B: the Cout = 64 layers are bound by that read port.
-// STATS: the training flavour that accumulates BatchNorm statistics of the stored outputs (per-CTA partials [4 quarters][2][BN]
-// fp32 + a 2 KB transpose scratch per epilogue warp, vu_conv_common.cuh); it runs with HT = 2.
+// STATS: the training flavour that accumulates BatchNorm statistics of the stored outputs (per-CTA partials
+// [8 epilogue warps][2][BN] fp32 - here the two warps of a lane quarter take different ROWS of the same channels, so every
+// warp needs its own slice - + a 2 KB transpose scratch per epilogue warp, vu_conv_common.cuh); it runs with HT = 2.
 template <int BN, int HT, bool PAIR = false, bool STATS = false> struct HaloCfg {
     static constexpr int kARows = (HT + 2) * kHaloPitch;
     static constexpr int kABytes = kARows * 128;                       // what one TMA box delivers
@@ -56,7 +57,7 @@ template <int BN, int HT, bool PAIR = false, bool STATS = false> struct HaloCfg 
     static constexpr int kBStages = (BN == 64) ? (HT == 2 ? 8 : 3) : ((STATS && !PAIR) ? 3 : 5);
     static constexpr int kTmemCols = 2 * HT * BN;
     static constexpr int kBarBytes = 256;
-    static constexpr int kStatBytes = STATS ? (4 * 2 * BN * 4 + kHaloEpiWarps * kEpiScratchBytes) : 0;
+    static constexpr int kStatBytes = STATS ? (kHaloEpiWarps * 2 * BN * 4 + kHaloEpiWarps * kEpiScratchBytes) : 0;
     static constexpr int kSmemBytes = 1024 + kAStages * kAStride + kBStages * kBBytes + kBarBytes + 3 * BN * 4 + kStatBytes;
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 232448, "smem budget");
@@ -88,8 +89,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     float* s_scale = reinterpret_cast<float*>(smem_al + kBarOff + Cfg::kBarBytes);
     float* s_bias = s_scale + BN;
     float* s_fw = s_bias + BN;
-    float* s_stat = s_fw + BN;                              // STATS: [4 quarters][2][BN] fp32 partial BatchNorm statistics
-    uint8_t* s_scratch = reinterpret_cast<uint8_t*>(s_stat + 4 * 2 * BN);   // + a 2 KB transpose scratch per epilogue warp
+    float* s_stat = s_fw + BN;                              // STATS: [8 epilogue warps][2][BN] fp32 partial BatchNorm statistics
+    uint8_t* s_scratch = reinterpret_cast<uint8_t*>(s_stat + kHaloEpiWarps * 2 * BN);   // + 2 KB transpose scratch per warp
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -119,7 +120,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
         s_fw[c] = p.fuse_w ? p.fuse_w[c] : 0.0f;
     }
     if constexpr (STATS)
-        for (int c = threadIdx.x; c < 4 * 2 * BN; c += kHaloThreads) s_stat[c] = 0.0f;
+        for (int c = threadIdx.x; c < kHaloEpiWarps * 2 * BN; c += kHaloThreads) s_stat[c] = 0.0f;
     tc_fence_before();
     if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
@@ -342,8 +343,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
                         }
                         if constexpr (STATS) {
                             if (p.stat_sums != nullptr)      // statistics of the values as stored (rounded to 16 bit)
-                                epi_stats_chunk(outw, valid, lane, dtype, scratch, s_stat + (q * 2) * BN + ch0,
-                                                s_stat + (q * 2 + 1) * BN + ch0);
+                                epi_stats_chunk(outw, valid, lane, dtype, scratch, s_stat + ((warp - 3) * 2) * BN + ch0,
+                                                s_stat + ((warp - 3) * 2 + 1) * BN + ch0);
                         }
                     }
                 }
@@ -357,7 +358,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_cons
     tc_fence_before();
     if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
     if constexpr (STATS)
-        if (p.stat_sums != nullptr) epi_stats_flush(s_stat, p.stat_sums, BN, threadIdx.x, kHaloThreads, BN);
+        if (p.stat_sums != nullptr) epi_stats_flush(s_stat, p.stat_sums, BN, threadIdx.x, kHaloThreads, BN, kHaloEpiWarps);
     if (warp == 1) {
         tc_fence_after();
         if constexpr (PAIR) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base); else tmem_dealloc<Cfg::kTmemCols>(tmem_base);

@@ -101,15 +101,22 @@ def broadcast_(t: torch.Tensor, src: int = 0, group=None) -> torch.Tensor:
 
 # ------------------------------------------------------------------ sample-sharded MC (config 4)
 def merge_sample_moments(count: int, mean: torch.Tensor, m2: torch.Tensor, sum_ent: torch.Tensor,
-                         finalize: Callable, group=None) -> Dict[str, torch.Tensor]:
-    """All-gather per-rank (count, mean, M2, sum H) and Chan-merge them. `finalize(counts, mean[S], m2[S], sh[S])`
-    is ops.moments_finalize on the GPU (vu_moments_finalize); the CPU tests pass the oracle's restatement."""
+                         finalize: Callable, group=None, all_counts: Optional[Sequence[int]] = None) -> Dict[str, torch.Tensor]:
+    """All-gather per-rank (mean, M2, sum H) - ONE collective - and Chan-merge them. `finalize(counts, mean[S], m2[S],
+    sh[S])` is ops.moments_finalize on the GPU (vu_moments_finalize); the CPU tests pass the oracle's restatement.
+    all_counts: the per-rank sample counts when every rank can derive them locally (shard_counts(N, world): the usual
+    case) - then nothing is exchanged for them and the merge never synchronises with the host. Without it the counts are
+    all-gathered and read back (one host sync)."""
     packed = torch.stack([mean, m2, sum_ent], 0)                      # one collective for the three maps
     allp = all_gather_stack(packed, group)                             # [world, 3, ...]
-    cnt = all_gather_stack(torch.tensor([float(count)], dtype=torch.float32, device=mean.device), group)
-    counts = [float(c) for c in cnt.reshape(-1).tolist()]
+    if all_counts is not None:
+        counts = [float(c) for c in all_counts]
+        assert len(counts) == allp.shape[0] and counts[world(group)[0]] == float(count)
+    else:
+        cnt = all_gather_stack(torch.tensor([float(count)], dtype=torch.float32, device=mean.device), group)
+        counts = [float(c) for c in cnt.reshape(-1).tolist()]
     keep = [i for i, c in enumerate(counts) if c > 0]                  # ranks without samples contribute nothing
-    sel = allp[keep]
+    sel = allp if len(keep) == len(counts) else allp[keep]
     return finalize([counts[i] for i in keep], sel[:, 0].contiguous(), sel[:, 1].contiguous(), sel[:, 2].contiguous())
 
 
@@ -136,7 +143,8 @@ def mc_predict_sample_sharded(model, images: torch.Tensor, temperature: float, n
         else:
             mean = torch.zeros((B, H, W), dtype=torch.float32, device=images.device)
             m2, sh = torch.zeros_like(mean), torch.zeros_like(mean)
-        res = merge_sample_moments(n_loc, mean, m2, sh, ops.moments_finalize, group)
+        res = merge_sample_moments(n_loc, mean, m2, sh, ops.moments_finalize, group,
+                                   all_counts=shard_counts(num_samples, ws))
     return res
 
 
@@ -193,7 +201,7 @@ def tiled_image_mc(model, img: torch.Tensor, num_samples: int, patch_size: int =
         mine = deal_round_robin(len(info), rank, ws)
         acc, wsum = predict.blended_samples(model, img, z_rows, patch_size, ov, batch_size, tile_subset=mine,
                                             finalize=False)
-        res = strip_reduce(acc, wsum[0], lambda p: ops.uncertainty_reduce(p, p.shape[2], p.shape[3], input_is_prob=True),
+        res = strip_reduce(acc, wsum, lambda p: ops.uncertainty_reduce(p, p.shape[2], p.shape[3], input_is_prob=True),
                            group)
     res["mu"], res["logvar"] = mu, lv
     return res

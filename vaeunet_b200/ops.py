@@ -715,3 +715,95 @@ def binary_curve_auc(keys_sorted: torch.Tensor, labels_sorted: torch.Tensor, ws:
                                      ws.numel(), out.data_ptr(), _stream()), "vu_binary_curve_auc")
     _count(5)
     return out
+
+
+# ------------------------------------------------------------------ patch pipeline / batched blending
+def tile_gather(src: torch.Tensor, coords: torch.Tensor, ph: int, pw: int, divisor: float = 255.0,
+                binarise: bool = False) -> torch.Tensor:
+    """Tiles of ONE device-resident image -> fp32 NCHW batch [T, C, ph, pw]. src: uint8 HWC [H, W, C] (divided by `divisor`)
+    or fp32 CHW [C, H, W] / [1, C, H, W]; coords int32 [T, 2] = (y0, x0) on the device."""
+    require_device()
+    assert coords.dtype == torch.int32 and coords.is_cuda and coords.is_contiguous() and coords.shape[1] == 2
+    T = coords.shape[0]
+    if src.dtype == torch.uint8:
+        assert src.dim() == 3 and src.is_contiguous()
+        H, W, Cc = src.shape
+        is_u8 = 1
+    else:
+        src = _f32(src.contiguous())
+        if src.dim() == 4:
+            assert src.shape[0] == 1
+            src = src[0]
+        Cc, H, W = src.shape
+        is_u8 = 0
+    out = torch.empty((T, Cc, ph, pw), dtype=torch.float32, device=src.device)
+    check(load().vu_tile_gather(src.data_ptr(), is_u8, Cc, H, W, coords.data_ptr(), T, ph, pw, float(divisor), int(binarise),
+                                out.data_ptr(), _stream()), "vu_tile_gather")
+    _count()
+    return out
+
+
+def tile_stats(tiles: torch.Tensor, masks: Optional[torch.Tensor], black_thr: float = 0.1) -> torch.Tensor:
+    """-> fp32 [T, 2]: black-border ratio, lesion flag (data_loading.py:287-300,382)."""
+    require_device()
+    tiles = _f32(tiles)
+    T, Cc, ph, pw = tiles.shape
+    if masks is not None:
+        masks = _f32(masks.contiguous())
+        assert masks.numel() == T * ph * pw
+    out = torch.empty((T, 2), dtype=torch.float32, device=tiles.device)
+    check(load().vu_tile_stats(tiles.data_ptr(), T, Cc, ph, pw, _ptr(masks), float(black_thr), out.data_ptr(), _stream()),
+          "vu_tile_stats")
+    _count()
+    return out
+
+
+def resample_u8(src: torch.Tensor, out_size: int, axis: int, bounds: torch.Tensor, kk: torch.Tensor) -> torch.Tensor:
+    """One pass of Pillow's 8-bit resampling (axis 0 = x, 1 = y) of a uint8 HWC image with host-built tables."""
+    require_device()
+    assert src.dtype == torch.uint8 and src.dim() == 3 and src.is_contiguous()
+    Hs, Ws, Cc = src.shape
+    Hd, Wd = (Hs, out_size) if axis == 0 else (out_size, Ws)
+    assert bounds.dtype == torch.int32 and kk.dtype == torch.int32 and bounds.shape == (out_size, 2) and kk.shape[0] == out_size
+    dst = torch.empty((Hd, Wd, Cc), dtype=torch.uint8, device=src.device)
+    check(load().vu_resample_u8(src.data_ptr(), Hs, Ws, Cc, dst.data_ptr(), Hd, Wd, axis, bounds.contiguous().data_ptr(),
+                                kk.contiguous().data_ptr(), kk.shape[1], _stream()), "vu_resample_u8")
+    _count()
+    return dst
+
+
+def nearest_u8(src: torch.Tensor, yi: torch.Tensor, xi: torch.Tensor) -> torch.Tensor:
+    require_device()
+    assert src.dtype == torch.uint8 and src.dim() == 3 and src.is_contiguous()
+    Hs, Ws, Cc = src.shape
+    dst = torch.empty((yi.numel(), xi.numel(), Cc), dtype=torch.uint8, device=src.device)
+    check(load().vu_nearest_u8(src.data_ptr(), Hs, Ws, Cc, dst.data_ptr(), yi.numel(), xi.numel(), yi.data_ptr(), xi.data_ptr(),
+                               _stream()), "vu_nearest_u8")
+    _count()
+    return dst
+
+
+def blend_accumulate_batch(tiles: torch.Tensor, info: torch.Tensor, bbox, nth: int, ntw: int, overlap: int, acc: torch.Tensor,
+                           wsum: torch.Tensor) -> None:
+    """tiles fp32 [T, Ns, ph, pw]; info int32 [T, 4] = (sh, sw, ti, tj) on the device; bbox = (y0, y1, x0, x1) host ints;
+    acc [Ns, H, W]; wsum [H, W] (one weight map for all samples)."""
+    require_device()
+    tiles = _f32(tiles)
+    T, Ns, ph, pw = tiles.shape
+    H, W = acc.shape[-2:]
+    assert acc.shape[0] == Ns and tuple(wsum.shape) == (H, W) and info.dtype == torch.int32 and info.shape == (T, 4)
+    y0, y1, x0, x1 = bbox
+    check(load().vu_blend_accumulate_batch(tiles.data_ptr(), info.data_ptr(), T, Ns, ph, pw, nth, ntw, overlap, _f32(acc).data_ptr(),
+                                           _f32(wsum).data_ptr(), H, W, y0, y1, x0, x1, _stream()), "vu_blend_accumulate_batch")
+    _count()
+
+
+def blend_finalize_shared(acc: torch.Tensor, wsum: torch.Tensor) -> torch.Tensor:
+    """acc [Ns, H, W] / (wsum [H, W] + 1e-8)."""
+    require_device()
+    out = torch.empty_like(acc)
+    plane = wsum.numel()
+    check(load().vu_blend_finalize_shared(_f32(acc).data_ptr(), _f32(wsum).data_ptr(), out.data_ptr(), plane, acc.numel() // plane,
+                                          _stream()), "vu_blend_finalize_shared")
+    _count()
+    return out

@@ -69,15 +69,17 @@ def default_overlap(patch_size: int) -> int:
 
 
 def _tiles_probs(eng, img, z_dec_rows: torch.Tensor, info, idxs, Ns: int):
-    """Run a batch of equal-sized tiles: encoder once, Ns decodes each (sample-minor).
+    """Run a batch of equal-sized tiles: ONE gather kernel cuts them out of the device-resident image (no torch.cat of
+    slices), encoder once, Ns decodes each (sample-minor).
     -> probabilities [T, Ns, ph, pw] (sigmoid at tile/2, THEN bilinear up: visualize_vae.py:345-358)."""
-    tiles = torch.cat([img[:, :, info[k][0]:info[k][1], info[k][2]:info[k][3]] for k in idxs], 0).contiguous()
+    ph, pw = info[idxs[0]][1] - info[idxs[0]][0], info[idxs[0]][3] - info[idxs[0]][2]
+    coords = torch.tensor([[info[k][0], info[k][2]] for k in idxs], dtype=torch.int32).to(img.device, non_blocking=True)
+    tiles = ops.tile_gather(img, coords, ph, pw)
     T = tiles.shape[0]
     feats = eng.encode(tiles)
     z_dec = z_dec_rows.unsqueeze(0).expand(T, -1, -1).reshape(T * Ns, -1).contiguous()
     lg = eng.decode(feats, z_dec, honour_use_skip=False)          # [T*Ns,1,h,w]
     h, w = lg.shape[2:]
-    ph, pw = tiles.shape[2:]
     return ops.resize_logits(lg.reshape(T * Ns, h, w), ph, pw, ops.SIG_PRE).reshape(T, Ns, ph, pw)
 
 
@@ -121,8 +123,10 @@ def predict_with_patches(model, img, z, patch_size=512, overlap=None, batch_size
 def blended_samples(model, img, z_rows: torch.Tensor, patch_size=512, overlap=None, batch_size=4,
                     tile_subset=None, finalize=True):
     """All Ns samples of a tiled image in one sweep: z_rows [Ns, L] (every tile of a sample shares
-    its z, visualize_vae.py:328-334). -> [Ns,H,W] blended probabilities (or the raw
-    (acc, wsum) accumulators when finalize=False, for multi-GPU tile sharding)."""
+    its z, visualize_vae.py:328-334). -> [Ns,H,W] blended probabilities (or the raw accumulators
+    (acc [Ns,H,W], wsum [H,W]) when finalize=False, for multi-GPU tile sharding).
+    Per tile batch: one gather launch, the network, ONE blend launch for all tiles x samples; the ramp weights do not depend
+    on the sample, so there is a single weight map."""
     model.eval()
     eng = model.engine()
     B, C, H, W = img.shape
@@ -133,7 +137,7 @@ def blended_samples(model, img, z_rows: torch.Tensor, patch_size=512, overlap=No
     Ns = z_rows.shape[0]
     img = img.float().contiguous()
     acc = torch.zeros((Ns, H, W), dtype=torch.float32, device=img.device)
-    wsum = torch.zeros((Ns, H, W), dtype=torch.float32, device=img.device)
+    wsum = torch.zeros((H, W), dtype=torch.float32, device=img.device)
     todo = list(range(len(info))) if tile_subset is None else list(tile_subset)
     with torch.no_grad():
         # group equal-sized tiles (ragged only when the image is smaller than a patch)
@@ -146,14 +150,14 @@ def blended_samples(model, img, z_rows: torch.Tensor, patch_size=512, overlap=No
                     (info[todo[pos]][1] - info[todo[pos]][0], info[todo[pos]][3] - info[todo[pos]][2]) == shp:
                 grp.append(todo[pos]); pos += 1
             probs = _tiles_probs(eng, img, z_rows, info, grp, Ns)
-            for t, k in enumerate(grp):
-                sh, eh, sw, ew = info[k]
-                i, j = divmod(k, nw)
-                for n in range(Ns):
-                    ops.blend_accumulate(probs[t, n], sh, sw, i, j, nh, nw, overlap, acc[n], wsum[n])
+            rows = [[info[k][0], info[k][2], k // nw, k % nw] for k in grp]
+            tinfo = torch.tensor(rows, dtype=torch.int32).to(img.device, non_blocking=True)
+            bbox = (min(info[k][0] for k in grp), max(info[k][1] for k in grp),
+                    min(info[k][2] for k in grp), max(info[k][3] for k in grp))
+            ops.blend_accumulate_batch(probs, tinfo, bbox, nh, nw, overlap, acc, wsum)
     if not finalize:
         return acc, wsum
-    return ops.blend_finalize(acc, wsum)
+    return ops.blend_finalize_shared(acc, wsum)
 
 
 def segmentation_distribution(model, img, num_samples=32, patch_size=None, overlap=None, temperature=1.0,

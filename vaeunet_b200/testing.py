@@ -101,3 +101,22 @@ def f3_inputs(seed: int, B: int, H: int, W: int, ties: bool):
     if ties:
         unc = torch.round(unc * 50) / 50          # heavy ties: sklearn groups equal thresholds
     return p, gt, unc
+
+
+def f4_inputs(seed: int, H: int, W: int):
+    """A synthetic 8-bit 'decoded fundus photograph' [H,W,3] with a black border outside the disc, and an 8-bit lesion mask
+    [H,W] (0 / 255) - the inputs of the patch pipeline tests."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:H, 0:W]
+    r = np.hypot((yy - H / 2) / (0.5 * H), (xx - W / 2) / (0.5 * W))
+    disc = r < 0.92
+    img = np.zeros((H, W, 3), dtype=np.float64)
+    base = np.stack([180 - 60 * r, 90 - 40 * r, 40 - 10 * r], -1)
+    img[disc] = (base + rng.normal(0, 12, (H, W, 3)))[disc]
+    img = np.clip(img, 0, 255).astype(np.uint8)
+    mask = np.zeros((H, W), dtype=np.uint8)
+    for _ in range(6):
+        cy, cx, rad = rng.integers(H // 6, 5 * H // 6), rng.integers(W // 6, 5 * W // 6), rng.integers(3, max(4, H // 20))
+        mask[np.hypot(yy - cy, xx - cx) < rad] = 255
+    return img, mask
