@@ -13,6 +13,8 @@
 #   ncu_full:<regex>:<script args...>   ncu --set full of kernels matching <regex> in `python scripts/<args>` (':' = space)
 #   run:<script args...>                python scripts/<args> (':' = space), output to <tag>_run_<n>.log
 #   sanitize:<tool>:<pytest -k expr>    compute-sanitizer --tool <tool> over the selected GPU tests
+#   dist:<N>:<workload>                 torchrun on N GPUs: bench.py --gpus N --workload <workload>   (gpurun --gpus N)
+#   distrun:<N>:<script args...>        torchrun on N GPUs: scripts/<args>
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 TAG=$1; shift
@@ -51,6 +53,15 @@ for step in "$@"; do
       IFS=':' read -r _ tool expr <<< "$step"
       timeout 2400 compute-sanitizer --tool $tool --print-limit 20 python -m pytest tests -m gpu -x -q -k "$expr" \
         > ${O}_sanitize_$tool.txt 2>&1; tail -15 ${O}_sanitize_$tool.txt ;;
+    dist:*)
+      IFS=':' read -r _ ng w <<< "$step"
+      timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $ng --master-addr 127.0.0.1 --master-port $((29600+n)) \
+        bench.py --gpus $ng --workload $w > ${O}_bench_${w}_${ng}gpu.json 2> ${O}_bench_${w}_${ng}gpu.err
+      grep '^{' ${O}_bench_${w}_${ng}gpu.json | tail -c 1500; tail -3 ${O}_bench_${w}_${ng}gpu.err ;;
+    distrun:*)
+      IFS=':' read -r _ ng rest <<< "$step"; args=${rest//:/ }
+      timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $ng --master-addr 127.0.0.1 --master-port $((29700+n)) \
+        scripts/$args > ${O}_distrun_${ng}gpu_$n.log 2>&1; tail -25 ${O}_distrun_${ng}gpu_$n.log ;;
     *) echo "unknown step $step" ;;
   esac
 done

@@ -1,5 +1,6 @@
 """GPU parity of the tcgen05 implicit-GEMM conv (through the C ABI) against torch CPU fp32
 F.conv2d on the same 16-bit-rounded operands (the oracle's primitive)."""
+import zlib
 import pytest
 import torch
 import torch.nn.functional as F
@@ -46,7 +47,7 @@ def test_conv_igemm(case, cuda_dev):
     name, N, H, W, Cin, Cout, k, stride, relu, use_res, xs, ys, dt = case
     tdt = torch.bfloat16 if dt == "bf16" else torch.float16
     odt = ops.BF16 if dt == "bf16" else ops.F16
-    g = torch.Generator().manual_seed(hash(name) % (2 ** 31))
+    g = torch.Generator().manual_seed(zlib.crc32(name.encode()))
     pad = 1 if k == 3 else 0
     x = torch.randn(N, Cin, H, W, generator=g)
     w = torch.randn(Cout, Cin, k, k, generator=g) * (1.0 / (Cin * k * k) ** 0.5)

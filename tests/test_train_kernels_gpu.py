@@ -1,5 +1,6 @@
 """GPU parity of the training kernels (through the C ABI) against torch CPU autograd on the same
 16-bit-rounded operands: conv weight gradient (MN-major tcgen05 GEMM over pixels) and data gradient."""
+import zlib
 import pytest
 import torch
 import torch.nn.functional as F
@@ -21,7 +22,7 @@ CASES = [
 
 def _setup(case, dev, dt=torch.bfloat16):
     name, N, H, W, Cin, Cout, k, stride = case
-    g = torch.Generator().manual_seed(abs(hash(name)) % (2 ** 31))
+    g = torch.Generator().manual_seed(zlib.crc32(name.encode()))
     pad = k // 2
     x = torch.randn(N, Cin, H, W, generator=g).to(dt).float()
     w = (torch.randn(Cout, Cin, k, k, generator=g) / (Cin * k * k) ** 0.5).to(dt).float()

@@ -21,6 +21,7 @@ import torch
 
 from . import ops
 from .ops import Act
+from ._nvtx import rng
 
 BN_EPS = 1e-5
 RESNET34_STAGES = (3, 4, 6, 3)
@@ -347,13 +348,22 @@ class ResNetVAEEngine:
         self.final = FinalConvUnit(sd, "final_conv.", dev)
 
     def encode(self, images: torch.Tensor) -> List[Act]:
-        return self.encoder(images)
+        with rng("vaeunet.encode"):
+            return self.encoder(images)
 
     def heads(self, f4: Act, eps: Optional[torch.Tensor], temperature: float, Ns: int):
+        with rng("vaeunet.latent_heads"):
+            return self._heads(f4, eps, temperature, Ns)
+
+    def _heads(self, f4: Act, eps: Optional[torch.Tensor], temperature: float, Ns: int):
         return ops.latent_head(f4, self.mu_head.w, self.mu_head.b, self.lv_head.w, self.lv_head.b, eps, temperature, Ns)
 
     def decode(self, feats: Sequence[Act], z_dec: torch.Tensor, honour_use_skip: bool = True) -> torch.Tensor:
         """z_dec fp32 [D, L] with D = B * rep (sample-minor) -> logits fp32 [D, n_classes, H/2, W/2]."""
+        with rng("vaeunet.decode"):
+            return self._decode(feats, z_dec, honour_use_skip)
+
+    def _decode(self, feats: Sequence[Act], z_dec: torch.Tensor, honour_use_skip: bool = True) -> torch.Tensor:
         z = ConstVec(z_dec.contiguous(), (feats[-1].H, feats[-1].W))
         D = z_dec.shape[0]
         if self.use_bottleneck:
@@ -407,7 +417,8 @@ class ResNetVAEEngine:
         H, W = images.shape[2:]
         sample = self.latent_injection != "none"
         lg, mu, lv = self.mc_logits(images, temperature, num_samples, eps, sample)
-        res = ops.uncertainty_reduce(lg.contiguous(), H, W, want_probs=return_samples, outs=tuple(outs))
+        with rng("vaeunet.uncertainty_reduce"):
+            res = ops.uncertainty_reduce(lg.contiguous(), H, W, want_probs=return_samples, outs=tuple(outs))
         res["mu"], res["logvar"] = mu, lv
         return res
 

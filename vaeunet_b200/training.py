@@ -32,6 +32,7 @@ from . import train_ops as T
 from ._lib import VaeUnetError
 from .engine import RESNET34_STAGES
 from .ops import Act
+from ._nvtx import rng
 
 import os
 
@@ -391,6 +392,7 @@ class TrainStep:
         logits = ops.resize_logits(lg_low, H, W, ops.SIG_NONE)
         S["logits"] = logits
         torch._foreach_add_(self.nbt, 1)
+        self._invalidate_packed()          # the running statistics moved: eval-mode folded BN caches are stale
         return logits.view(B, 1, H, W), mu, lv, S
 
     # ------------------------------------------------------------------ loss (utils/loss.py; train.py:312-316,387-398)
@@ -566,14 +568,21 @@ class TrainStep:
                                "(or zero_grad()) first, and pass sync=False for all micro-batches but the last")
         self._sync_grads = bool(sync)
         self._reduced = bool(sync) and self.pg is not None and self.world > 1
-        self.repack()
-        _, _, _, S = self.forward(images, eps)
-        out, dlogits, dmu, dlv = self.loss_and_grads(S, masks, beta, accum)
-        self.backward(S, dlogits, dmu, dlv)
+        with rng("vaeunet.train.forward"):
+            self.repack()
+            _, _, _, S = self.forward(images, eps)
+        with rng("vaeunet.train.loss"):
+            out, dlogits, dmu, dlv = self.loss_and_grads(S, masks, beta, accum)
+        with rng("vaeunet.train.backward"):
+            self.backward(S, dlogits, dmu, dlv)
         return out
 
     def optimizer_step(self):
         """clip_grad_norm_(max_norm) + AdamW (train.py:405-408) on the flat buffers; averages over the DP group."""
+        with rng("vaeunet.train.optimizer"):
+            self._optimizer_step()
+
+    def _optimizer_step(self):
         self._wait_all_reduce()
         self._reduced = False
         self.step_count += 1
