@@ -1,4 +1,5 @@
-"""Time vu_decoder_concat at a decoder-block shape. usage: prof_concat.py D rep hs H Cx Cs F [reps]"""
+"""Time vu_decoder_concat at a decoder-block shape. usage: prof_concat.py D rep hs H Cx Cs F [reps] [Cz]
+(Cz = 0 with Cx == Cs takes the fp16 fast kernel; VU_NO_FAST_CONCAT=1 forces the generic one)"""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -7,6 +8,7 @@ from vaeunet_b200 import ops
 
 D, rep, hs, H, Cx, Cs, F = map(int, sys.argv[1:8])
 reps = int(sys.argv[8]) if len(sys.argv) > 8 else 4
+Cz = int(sys.argv[9]) if len(sys.argv) > 9 else 32
 dev = torch.device("cuda:0")
 dt = torch.float16
 g = torch.Generator(device=dev).manual_seed(0)
@@ -14,8 +16,8 @@ r = lambda *s: ops.Act(torch.randn(*s, device=dev, generator=g).to(dt))
 x, g1 = r(D, hs, hs, Cx), r(D, hs, hs, F)
 x1, skip = r(D // rep, H, H, F), r(D // rep, H, H, Cs)
 pw = torch.randn(F, device=dev, generator=g)
-zv = torch.randn(D, 32, device=dev, generator=g)
-out = ops.new_act(D, H, H, Cx + Cs + 32, ops.F16, dev)
+zv = torch.randn(D, Cz, device=dev, generator=g) if Cz else None
+out = ops.new_act(D, H, H, Cx + Cs + Cz, ops.F16, dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 ts = []
 for i in range(reps):

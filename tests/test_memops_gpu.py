@@ -114,7 +114,15 @@ def test_attention_gate(cuda_dev, F_, Cl, rep):
 
 
 @pytest.mark.parametrize("hs,ws,H,W,Cx,Cs,F_,Cz,rep", [(8, 8, 16, 16, 128, 64, 32, 32, 2), (11, 9, 22, 17, 64, 128, 64, 0, 1),
-                                                        (1, 1, 6, 5, 256, 64, 128, 32, 3), (5, 7, 10, 14, 24, 8, 8, 8, 1)])
+                                                        (1, 1, 6, 5, 256, 64, 128, 32, 3), (5, 7, 10, 14, 24, 8, 8, 8, 1),
+                                                        # the fp16 fast path (Cz = 0, Cx == Cs in {64,128,256}): ragged rows, several runs per row
+                                                        (8, 8, 16, 16, 64, 64, 32, 0, 3), (11, 21, 22, 41, 128, 128, 64, 0, 2),
+                                                        (4, 4, 8, 8, 256, 256, 128, 0, 2), (16, 20, 32, 40, 64, 64, 32, 0, 2),
+                                                        (1, 1, 4, 36, 128, 128, 64, 0, 2),
+                                                        # the decoder blocks' own slice widths (unet_resnet.py:228-231)
+                                                        (8, 8, 16, 16, 128, 64, 32, 0, 3), (9, 11, 18, 21, 128, 64, 32, 0, 2),
+                                                        (5, 6, 10, 12, 256, 64, 64, 0, 2), (3, 3, 6, 7, 512, 128, 128, 0, 2),
+                                                        (2, 3, 4, 6, 512, 256, 128, 0, 2)])
 @pytest.mark.parametrize("dt", ["bf16", "f16"])
 def test_decoder_concat(cuda_dev, hs, ws, H, W, Cx, Cs, F_, Cz, rep, dt):
     """Fused concat producer vs. the reference order of operations (unet/unet_resnet.py:79-98): upsample x to the
