@@ -39,7 +39,7 @@ for step in "$@"; do
       python scripts/summarize_launches.py ${O}_train_launches.csv > ${O}_train_launch_summary.txt 2>&1; python scripts/launch_table.py ${O}_train_launches.csv > ${O}_train_launch_table.txt 2>&1; head -30 ${O}_train_launch_summary.txt ;;
     ncu_mc_list)
       timeout 1200 ncu --metrics $METRICS --clock-control none --csv --log-file ${O}_mc_launches.csv \
-        python bench.py --steps 1 --warmup 3 --no-cpu-baseline --workload mc > ${O}_ncu_mc.log 2>&1
+        python bench.py --steps 1 --warmup 3 --batch 32 --no-cpu-baseline --no-gpu-eager --workload mc > ${O}_ncu_mc.log 2>&1
       python scripts/mc_launch_summary.py ${O}_mc_launches.csv > ${O}_mc_launch_summary.txt 2>&1; head -16 ${O}_mc_launch_summary.txt ;;
     ncu_full:*)
       IFS=':' read -r _ regex rest <<< "$step"; args=${rest//:/ }

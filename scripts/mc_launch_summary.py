@@ -5,7 +5,7 @@ from collections import defaultdict
 lines = [l for l in open(sys.argv[1]) if not l.startswith('==')]
 rows = [r for r in csv.DictReader(lines) if r.get('Metric Name') == 'gpu__time_duration.sum']
 names = [re.sub(r'\(.*', '', r['Kernel Name']) for r in rows]
-starts = [i for i, n in enumerate(names) if 'small_cin_conv_kernel<7' in n]
+starts = [i for i, n in enumerate(names) if 'small_cin_conv_kernel<7' in n or 'small_cin_mma_kernel<7' in n]
 a, b = starts[2], starts[3]
 agg = defaultdict(lambda: [0, 0.0]); tot = 0
 for r, n in zip(rows[a:b], names[a:b]):

@@ -8,6 +8,10 @@ namespace vu {
 
 int set_error(int code, const char* fmt, ...);
 int num_sms();
+// vu_small_cin_mma.cu: tensor-core first conv (Cin = 3); 0 = launched, -1 = shape not covered
+int launch_small_cin_mma(int K, int S, const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
+                         int Cin, int H, int W, int Cout, int pad, int y_ctot, int y_coff, int relu, int dtype,
+                         cudaStream_t stream);
 
 #define VU_CHECK_LAUNCH(name)                                                              \
     do {                                                                                   \

@@ -1,5 +1,6 @@
 // Memory-bound layout / pooling / resize kernels (NHWC 16-bit, 8 channels = 16 B per thread access).
 #include "vu_internal.h"
+#include <cstdlib>
 #include "vu_half.cuh"
 
 namespace vu {
@@ -313,6 +314,12 @@ static int launch_small_cin(const float* x, const float* w, const float* scale, 
     if (Cin < 1 || Cin > 4) return set_error(VU_ERR_UNSUPPORTED, "small-cin conv: Cin must be 1..4 (got %d)", Cin);
     if (Cout % 32 || y_ctot % 8 || y_coff % 8) return set_error(VU_ERR_ALIGN, "small-cin conv: Cout %% 32, slices %% 8");
     if (!scale || !bias) return set_error(VU_ERR_INVALID, "small-cin conv: scale/bias required");
+    static const bool fma_only = getenv("VU_STEM_FMA") != nullptr;      // A/B switch: the FP32-FMA direct convolution
+    if (!fma_only && launch_small_cin_mma(K, S, x, w, scale, bias, y, N, Cin, H, W, Cout, pad, y_ctot, y_coff, relu, dtype,
+                                          stream) == 0) {
+        VU_CHECK_LAUNCH("small_cin_mma");
+        return 0;
+    }
     const int Ho = (H + 2 * pad - K) / S + 1, Wo = (W + 2 * pad - K) / S + 1;
     const size_t smem = (size_t)(4 * TIH * (TIW + 1) + Cin * K * K * Cout) * sizeof(float);
     static bool attr = false;

@@ -1,0 +1,192 @@
+// First convolution of both networks on the tensor cores: Cin = 3 image planes (fp32 NCHW) -> Cout (multiple of 64) NHWC
+// 16-bit, 7x7 stride 2 (ResNet-34 stem, timm resnet34 conv1 + bn1 + act1 as used by unet/unet_resnet.py:131-137) or 3x3
+// stride 1 (DoubleConv's first conv, unet/unet_parts.py:36-47), folded BatchNorm affine (+ ReLU) in the epilogue.
+//
+// Why not the tcgen05 implicit GEMM of vu_conv_igemm.cu: with 3 input channels there is no 64-channel K block for TMA to
+// fetch; the A operand would have to be gathered element by element into a swizzled shared-memory tile first. The layer is
+// 0.3 % of the network's FLOPs (19.7 GFLOP per 16 patches) and bound by its 134 MB output, so the register-operand warp MMA
+// (mma.sync m16n8k8, TF32 inputs, fp32 accumulate) is enough: A fragments are gathered straight from the staged fp32 image
+// tile (one LDS per element, bank-conflict free: a warp's 32 reads fall on 2g + tig consecutive words), B fragments come as
+// one LDS.128 per pair of 8-channel tiles. Replaces the FP32-FMA direct convolution (small_cin_conv_kernel, 0.60 ms per 16
+// patches = 46 % of the FP32 pipe) on the inference path.
+//
+// K ordering: k = (c*K + r)*KP + q with KP = K rounded up to a multiple of 4 (zero filter taps for q >= K), so that every
+// 4-wide half of a k8 step lies inside ONE filter row (c, r) and all its shared-memory offsets are compile-time constants.
+#include "vu_half.cuh"
+#include "vu_internal.h"
+
+namespace vu {
+
+template <int K, int S> struct SmallCinMma {
+    static constexpr int CIN = 3;
+    static constexpr int KP = (K + 3) / 4 * 4;
+    static constexpr int NCR = CIN * K;                       // filter rows (c, r)
+    static constexpr int KTOT = (NCR * KP + 7) / 8 * 8;
+    static constexpr int NKS = KTOT / 8;                      // k8 steps
+    static constexpr int TOH = 8, TOW = 32;                   // output tile: one row of 32 pixels per warp
+    static constexpr int TIH = (TOH - 1) * S + K;
+    static constexpr int TIW = (TOW - 1) * S + KP;
+    static constexpr int TIWP = TIW + 2;
+    static constexpr int kInFloats = CIN * TIH * TIWP;
+    static constexpr int kOutBytesPerWarp = TOW * 64 * 2;     // 32 pixels x 64 channels, 16-bit
+};
+
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// smem: [weights NKS x (Cout/16) x 32 lanes x 4 tf32][scale Cout][bias Cout][input tile][8 warps x 4 KB output staging]
+template <int K, int S>
+__global__ void __launch_bounds__(256, 2)
+small_cin_mma_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ scale,
+                     const float* __restrict__ bias, uint16_t* __restrict__ y, int N, int H, int W, int Cout, int Ho, int Wo,
+                     int pad, int y_ctot, int y_coff, int relu, int dtype) {
+    using C = SmallCinMma<K, S>;
+    extern __shared__ uint4 smem_mma[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, tig = lane & 3;
+    const int nj = Cout / 16;                                   // pairs of 8-channel tiles
+    uint4* s_w = smem_mma;                                      // [NKS][nj][32]
+    float* s_sc = reinterpret_cast<float*>(s_w + C::NKS * nj * 32);
+    float* s_bi = s_sc + Cout;
+    uint32_t* s_in = reinterpret_cast<uint32_t*>(s_bi + Cout);  // [CIN][TIH][TIWP] tf32 bit patterns
+    uint8_t* s_out = reinterpret_cast<uint8_t*>(s_in + (C::kInFloats + 3) / 4 * 4) + warp * C::kOutBytesPerWarp;
+
+    // ---- filter bank -> B fragments (once per CTA): lane (g, tig) of pair j holds W[k0+tig][n0], W[k0+tig+4][n0],
+    //      W[k0+tig][n1], W[k0+tig+4][n1] with n0 = 16 j + g, n1 = n0 + 8
+    for (int i = tid; i < C::NKS * nj * 32 * 4; i += 256) {
+        const int e = i & 3, ln = (i >> 2) & 31, j = (i >> 7) % nj, ks = (i >> 7) / nj;
+        const int k = ks * 8 + (ln & 3) + ((e & 1) ? 4 : 0);
+        const int n = 16 * j + (ln >> 2) + ((e & 2) ? 8 : 0);
+        const int cr = k / C::KP, q = k % C::KP;
+        float v = 0.0f;
+        if (cr < C::NCR && q < K) v = __ldg(w + ((size_t)n * C::NCR + cr) * K + q);   // OIHW: ((n*3 + c)*K + r)*K + q
+        reinterpret_cast<uint32_t*>(s_w)[i] = to_tf32(v);
+    }
+    for (int i = tid; i < Cout; i += 256) { s_sc[i] = scale[i]; s_bi[i] = bias[i]; }
+
+    const int tiles_w = (Wo + C::TOW - 1) / C::TOW, tiles_h = (Ho + C::TOH - 1) / C::TOH;
+    const int total = tiles_w * tiles_h * N;
+    const int a_base = (warp * S) * C::TIWP + g * S + tig;     // this thread's pixel (row = warp, column g) and tap column
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n = tile / (tiles_w * tiles_h);
+        const int oh0 = ((tile / tiles_w) % tiles_h) * C::TOH, ow0 = (tile % tiles_w) * C::TOW;
+        const int ih0 = oh0 * S - pad, iw0 = ow0 * S - pad;
+        __syncthreads();                                        // previous tile's A reads are done (and s_w is complete)
+        for (int i = tid; i < C::CIN * C::TIH * C::TIW; i += 256) {
+            const int c = i / (C::TIH * C::TIW), r = (i / C::TIW) % C::TIH, q = i % C::TIW;
+            const int ih = ih0 + r, iw = iw0 + q;
+            float v = 0.0f;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * C::CIN + c) * H + ih) * W + iw);
+            s_in[(c * C::TIH + r) * C::TIWP + q] = to_tf32(v);
+        }
+        __syncthreads();
+        const int oh = oh0 + warp;
+        for (int cb = 0; cb < Cout; cb += 64) {
+            float acc[2][8][4];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) acc[mt][nt][e] = 0.0f;
+            const uint4* wb = s_w + (cb / 16) * 32 + lane;
+#pragma unroll
+            for (int ks = 0; ks < C::NKS; ++ks) {
+                // the two 4-wide halves of this k8 step: filter row cr and first tap q0 of each (compile-time)
+                const int kA = ks * 8, kB = ks * 8 + 4;
+                const int crA = (kA / C::KP < C::NCR) ? kA / C::KP : C::NCR - 1, qA = kA % C::KP;
+                const int crB = (kB / C::KP < C::NCR) ? kB / C::KP : C::NCR - 1, qB = kB % C::KP;
+                const int offA = ((crA / K) * C::TIH + (crA % K)) * C::TIWP + qA;
+                const int offB = ((crB / K) * C::TIH + (crB % K)) * C::TIWP + qB;
+                uint32_t a[2][4];
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    a[mt][0] = s_in[a_base + offA + (mt * 16) * S];
+                    a[mt][1] = s_in[a_base + offA + (mt * 16 + 8) * S];
+                    a[mt][2] = s_in[a_base + offB + (mt * 16) * S];
+                    a[mt][3] = s_in[a_base + offB + (mt * 16 + 8) * S];
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint4 b = wb[(ks * nj + j) * 32];
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt) {
+                        mma_tf32(acc[mt][2 * j], a[mt], b.x, b.y);
+                        mma_tf32(acc[mt][2 * j + 1], a[mt], b.z, b.w);
+                    }
+                }
+            }
+            // ---- epilogue: affine (+ReLU), 16-bit, through a swizzled per-warp staging tile so that every pixel leaves as
+            //      one 128-byte row (8 lanes x 16 B)
+            __syncwarp();
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+                const float2 sc = *reinterpret_cast<const float2*>(s_sc + cb + nt * 8 + 2 * tig);
+                const float2 bi = *reinterpret_cast<const float2*>(s_bi + cb + nt * 8 + 2 * tig);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int px = mt * 16 + hh * 8 + g;
+                        float v0 = fmaf(acc[mt][nt][2 * hh], sc.x, bi.x), v1 = fmaf(acc[mt][nt][2 * hh + 1], sc.y, bi.y);
+                        if (relu) { v0 = fmaxf(v0, 0.0f); v1 = fmaxf(v1, 0.0f); }
+                        *reinterpret_cast<uint32_t*>(s_out + px * 128 + ((nt ^ (px & 7)) << 4) + tig * 4) = pack2h(v0, v1, dtype);
+                    }
+            }
+            __syncwarp();
+            if (oh < Ho) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int px = i * 4 + (lane >> 3), ch = lane & 7;
+                    const int ow = ow0 + px;
+                    if (ow < Wo) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(s_out + px * 128 + ((ch ^ (px & 7)) << 4));
+                        *(reinterpret_cast<uint4*>(y + (((size_t)n * Ho + oh) * Wo + ow) * y_ctot + y_coff + cb) + ch) = v;
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int K, int S>
+static int launch_mma(const float* x, const float* w, const float* scale, const float* bias, void* y, int N, int H, int W,
+                      int Cout, int pad, int y_ctot, int y_coff, int relu, int dtype, cudaStream_t stream) {
+    using C = SmallCinMma<K, S>;
+    const int Ho = (H + 2 * pad - K) / S + 1, Wo = (W + 2 * pad - K) / S + 1;
+    const size_t smem = (size_t)C::NKS * (Cout / 16) * 32 * 16 + (size_t)2 * Cout * 4 + (size_t)(C::kInFloats + 3) / 4 * 16 +
+                        (size_t)8 * C::kOutBytesPerWarp;
+    if (smem > 110 * 1024) return -1;                           // two CTAs per SM; larger filter banks take the FMA kernel
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(small_cin_mma_kernel<K, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+        attr = true;
+    }
+    const int total = ((Wo + C::TOW - 1) / C::TOW) * ((Ho + C::TOH - 1) / C::TOH) * N;
+    int grid = num_sms() * 2;
+    if (grid > total) grid = total;
+    small_cin_mma_kernel<K, S><<<grid, 256, smem, stream>>>(x, w, scale, bias, static_cast<uint16_t*>(y), N, H, W, Cout, Ho,
+                                                          Wo, pad, y_ctot, y_coff, relu, dtype);
+    return 0;
+}
+
+// -> 0 launched, -1 shape not covered (caller falls back to the FP32-FMA kernel)
+int launch_small_cin_mma(int K, int S, const float* x, const float* w, const float* scale, const float* bias, void* y, int N,
+                         int Cin, int H, int W, int Cout, int pad, int y_ctot, int y_coff, int relu, int dtype,
+                         cudaStream_t stream) {
+    if (Cin != 3 || Cout % 64 || !scale || !bias || y_ctot % 8 || y_coff % 8) return -1;
+    if (K == 7 && S == 2) return launch_mma<7, 2>(x, w, scale, bias, y, N, H, W, Cout, pad, y_ctot, y_coff, relu, dtype, stream);
+    if (K == 3 && S == 1) return launch_mma<3, 1>(x, w, scale, bias, y, N, H, W, Cout, pad, y_ctot, y_coff, relu, dtype, stream);
+    return -1;
+}
+
+}  // namespace vu
