@@ -1,13 +1,14 @@
 #!/bin/bash
-# scratch trip: fast concat kernel vs generic at the three decoder shapes of a 16-patch x 10-sample micro-batch
+# scratch trip: stem split-TF32 parity margins + one-wave grids of the BatchNorm kernels (in-situ kernel sums)
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 O=gpurun_out/$1
-python -m pytest tests/test_memops_gpu.py -x -q -m gpu > ${O}_pytest_memops.txt 2>&1; tail -3 ${O}_pytest_memops.txt
-for env in 0 1; do
-  for shape in "160 10 128 256 128 64 32" "160 10 64 128 256 64 64" "160 10 32 64 512 128 128"; do
-    if [ $env = 1 ]; then VU_NO_FAST_CONCAT=1 python scripts/prof_concat.py $shape 4 0; else python scripts/prof_concat.py $shape 4 0; fi
-  done
-done > ${O}_concat.log 2>&1
-cat ${O}_concat.log
-python bench.py --workload mc --no-cpu-baseline --no-gpu-eager > ${O}_bench_mc.json 2> ${O}_bench_mc.err; tail -c 600 ${O}_bench_mc.json; tail -3 ${O}_bench_mc.err
+python scripts/debug_mc700.py > ${O}_mc700.log 2>&1; cat ${O}_mc700.log | cut -c1-250
+python -m pytest tests/test_memops_gpu.py -x -q -m gpu -k "stem or small_cin" 2>&1 | tail -2
+python bench.py --workload mc --no-cpu-baseline --no-gpu-eager > ${O}_bench_mc.json 2> ${O}_bench_mc.err; tail -c 300 ${O}_bench_mc.json; tail -3 ${O}_bench_mc.err
+for cfg in "8 16 16" "2 16 16" "8 3 16" "8 16 2" "2 3 2" "3 4 3" "4 6 4"; do
+  set -- $cfg
+  echo "== VU_BN_MULT_SUMS=$1 APPLY=$2 BWD=$3"
+  VU_BN_MULT_SUMS=$1 VU_BN_MULT_APPLY=$2 VU_BN_MULT_BWD=$3 python scripts/train_kineto.py 2>&1 | grep "span\|channel_sums_kernel<1>\|bn_bwd_apply\|bn_apply"
+done > ${O}_bn_grid.log 2>&1
+cat ${O}_bn_grid.log

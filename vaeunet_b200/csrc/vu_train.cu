@@ -2,10 +2,23 @@
 // backward over NHWC 16-bit maps, gradient accumulation, and the backward passes of max-pool, bilinear
 // resize, attention gate, output conv and the small latent-vector layers. All arithmetic is fp32 (fp64 for the
 // cross-block accumulation of batch statistics); activations and activation gradients are 16-bit NHWC slices.
+#include <cstdlib>
 #include "vu_half.cuh"
 #include "vu_internal.h"
 
 namespace vu {
+
+// Tuning knobs of the BatchNorm launches (A/B runs): CTAs per SM of the statistics / apply / backward grids. One resident
+// wave each (2 / 3 / 2 CTAs of 256 threads per SM at 118 / 78 / 122 registers): with 8-16 CTAs per SM the per-CTA prologue
+// (coefficients from the fp64 sums -> smem -> sync) was paid 3-4 times in sequence on the 4-70 MB maps of this network
+// (in-situ CUPTI sums per step, profiles/r2v_bn_grid.log: apply 0.69 -> 0.59 ms, backward apply 1.00 -> 0.82 ms).
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+static int bn_mult_sums() { static const int m = env_int("VU_BN_MULT_SUMS", 2); return m; }
+static int bn_mult_apply() { static const int m = env_int("VU_BN_MULT_APPLY", 3); return m; }
+static int bn_mult_bwd() { static const int m = env_int("VU_BN_MULT_BWD", 2); return m; }
 
 static int tr_grid(size_t items, int per_block, int mult = 8) {
     size_t g = (items + per_block - 1) / per_block;
@@ -22,7 +35,7 @@ static int tr_grid(size_t items, int per_block, int mult = 8) {
 // MODE 0: sums[c] += x, sums[C+c] += x^2                                    (BN forward statistics)
 // MODE 1: dz = dy * (y > 0 if y), xh = (x - mean) * invstd: sums[c] += dz, sums[C+c] += dz * xh   (BN backward)
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, const uint16_t* __restrict__ dy,
                     int dy_ctot, int dy_coff, const uint16_t* __restrict__ y, int y_ctot, int y_coff,
                     const float* __restrict__ mean, const float* __restrict__ invstd, size_t npix, int C8,
@@ -35,13 +48,13 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
     float a0[8], a1[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
-    float mu[8], is[8], msc[8], msh[8];
+    float mu[8], msc[8], msh[8];
     if (MODE == 1) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            mu[j] = mean[c8 * 8 + j]; is[j] = invstd[c8 * 8 + j];
+            mu[j] = mean[c8 * 8 + j];
             // ReLU mask recomputed from x exactly as bn_apply_kernel computed the output (no read of y)
-            msc[j] = relu_beta ? is[j] * gamma[c8 * 8 + j] : 0.f;
+            msc[j] = relu_beta ? invstd[c8 * 8 + j] * gamma[c8 * 8 + j] : 0.f;
             msh[j] = relu_beta ? relu_beta[c8 * 8 + j] - mu[j] * msc[j] : 0.f;
         }
     }
@@ -69,6 +82,7 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
                 for (int j = 0; j < 8; ++j) { a0[j] += f[j]; a1[j] = fmaf(f[j], f[j], a1[j]); }
             }
         } else {
+            // a1 accumulates dz * (x - mean); invstd is applied once per block below (8 registers less in the loop)
             auto body = [&](const uint4& vx, const uint4& vg, const uint4& vy) {
                 float f[8], g[8];
                 unpack8(vx, f, dtype);
@@ -83,25 +97,30 @@ channel_sums_kernel(const uint16_t* __restrict__ x, int x_ctot, int x_coff, cons
                     for (int j = 0; j < 8; ++j) g[j] = fmaf(f[j], msc[j], msh[j]) > 0.f ? g[j] : 0.f;
                 }
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { a0[j] += g[j]; a1[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], a1[j]); }
+                for (int j = 0; j < 8; ++j) { a0[j] += g[j]; a1[j] = fmaf(g[j], f[j] - mu[j], a1[j]); }
             };
-            for (; p + step < npix; p += 2 * step) {
-                uint4 vx[2], vg[2], vy[2];
+            constexpr int U = 4;                              // pixels in flight per thread: 8-12 independent 16-byte loads
+            for (; p + (U - 1) * step < npix; p += U * step) {
+                uint4 vx[U], vg[U], vy[U];
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
+                for (int u = 0; u < U; ++u) {
                     const size_t q = p + u * step;
                     vx[u] = __ldg(reinterpret_cast<const uint4*>(x + q * x_ctot + x_coff) + c8);
                     vg[u] = __ldg(reinterpret_cast<const uint4*>(dy + q * dy_ctot + dy_coff) + c8);
                     vy[u] = y ? __ldg(reinterpret_cast<const uint4*>(y + q * y_ctot + y_coff) + c8) : make_uint4(0, 0, 0, 0);
                 }
-                body(vx[0], vg[0], vy[0]);
-                body(vx[1], vg[1], vy[1]);
+#pragma unroll
+                for (int u = 0; u < U; ++u) body(vx[u], vg[u], vy[u]);
             }
             for (; p < npix; p += step) {
                 const uint4 vx = __ldg(reinterpret_cast<const uint4*>(x + p * x_ctot + x_coff) + c8);
                 const uint4 vg = __ldg(reinterpret_cast<const uint4*>(dy + p * dy_ctot + dy_coff) + c8);
                 const uint4 vy = y ? __ldg(reinterpret_cast<const uint4*>(y + p * y_ctot + y_coff) + c8) : make_uint4(0, 0, 0, 0);
                 body(vx, vg, vy);
+            }
+            if (MODE == 1) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a1[j] *= invstd[c8 * 8 + j];
             }
         }
     }
@@ -413,7 +432,7 @@ extern "C" int vu_bn_apply(const void* x, size_t npix, int C, int x_ctot, int x_
     if (!x || !y || !mean || !invstd || !gamma || !beta) return set_error(VU_ERR_INVALID, "bn_apply: null");
     VU_TR_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff | res_ctot | res_coff) % 8, "bn_apply");
     const int C8 = C / 8;
-    const int grid = tr_grid(npix * C8, 256 * 4, 16);
+    const int grid = tr_grid(npix * C8, 256 * 4, bn_mult_apply());
     if (256 % C8 == 0)
         bn_apply_kernel<true><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, mean, invstd, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
@@ -433,7 +452,7 @@ extern "C" int vu_bn_apply_sums(const void* x, size_t npix, int C, int x_ctot, i
     if (!x || !y || !sums || !mean || !invstd || !gamma || !beta || npix < 1) return set_error(VU_ERR_INVALID, "bn_apply_sums: null");
     VU_TR_ALIGN((C | x_ctot | x_coff | y_ctot | y_coff | res_ctot | res_coff) % 8, "bn_apply_sums");
     const int C8 = C / 8;
-    const int grid = tr_grid(npix * C8, 256 * 4, 16);
+    const int grid = tr_grid(npix * C8, 256 * 4, bn_mult_apply());
     if (256 % C8 == 0)
         bn_apply_kernel<true><<<grid, 256, 2 * C * sizeof(float), (cudaStream_t)st>>>(
             (const uint16_t*)x, x_ctot, x_coff, nullptr, nullptr, gamma, beta, (const uint16_t*)residual, res_ctot, res_coff, relu,
@@ -459,11 +478,11 @@ extern "C" int vu_bn_bwd(const void* x, size_t npix, int C, int x_ctot, int x_co
     const int C8 = C / 8, lanes = 256 / C8;
     cudaStream_t s = (cudaStream_t)st;
     cudaMemsetAsync(sums, 0, 2 * C * sizeof(double), s);
-    channel_sums_kernel<1><<<tr_grid(npix, lanes * 8, 8), 256, 2 * lanes * C * sizeof(float), s>>>(
+    channel_sums_kernel<1><<<tr_grid(npix, lanes * 8, bn_mult_sums()), 256, 2 * lanes * C * sizeof(float), s>>>(
         (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
         mean, invstd, npix, C8, sums, dtype, gamma, y_relu ? nullptr : relu_beta);
     VU_CHECK_LAUNCH("bn_bwd_reduce");
-    const int grid = tr_grid(npix * C8, 256 * 4, 16);
+    const int grid = tr_grid(npix * C8, 256 * 4, bn_mult_bwd());
     if (256 % C8 == 0)
         bn_bwd_apply_kernel<true><<<grid, 256, 5 * C * sizeof(float), s>>>(
             (const uint16_t*)x, x_ctot, x_coff, (const uint16_t*)dy, dy_ctot, dy_coff, (const uint16_t*)y_relu, y_ctot, y_coff,
