@@ -52,7 +52,10 @@ def test_conv_wgrad_row_kernel(cuda_dev, monkeypatch):
     from vaeunet_b200 import ops
     monkeypatch.setenv("VU_WGRAD_ROW3", "1")
     for case in [("r3_64_64", 2, 32, 32, 64, 64, 3, 1), ("r3_224_64", 1, 24, 130, 224, 64, 3, 1), ("r3_128_256", 3, 16, 16, 128, 256, 3, 1),
-                 ("r3_ksplit", 4, 128, 128, 64, 64, 3, 1), ("r3_ragged", 2, 20, 48, 32, 96, 3, 1)]:
+                 ("r3_ksplit", 4, 128, 128, 64, 64, 3, 1), ("r3_ragged", 2, 20, 48, 32, 96, 3, 1),
+                 # Cout <= 64: two filter rows stacked in M (the shifted dY rows as the upper half of the A tile)
+                 ("r3_stack_cout32", 2, 40, 64, 64, 32, 3, 1), ("r3_stack_nt2", 4, 32, 16, 96, 64, 3, 1),
+                 ("r3_stack_ragged", 1, 37, 150, 160, 64, 3, 1)]:
         name, N, H, W, Cin, Cout, k, stride = case
         x, w, dy, pad = _setup(case, cuda_dev)
         wr = w.clone().requires_grad_(True)

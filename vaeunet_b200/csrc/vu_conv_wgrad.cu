@@ -185,6 +185,14 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_const
 // the operand descriptor advanced by s pixel rows (128 B each; the 128-byte swizzle is a function of the absolute
 // shared-memory address, the property vu_conv_halo.cu relies on). Three fp32 accumulators of BN columns live in TMEM.
 // Traffic per 3 taps: 32 KB (dY) + ~36 KB (X) instead of 3 x 64 KB.
+//
+// Cout <= 64 (`stack`): an M = 64 MMA costs the same cycles as M = 128, and a zero-filled upper half of the dY tile wasted half
+// of every MMA on the 64-channel layers (layer1, the last decoder block: 1.3 ms of weight gradients per step). Instead the
+// second 64 rows of the A tile are the SAME 64 channels of dY one image row UP (box at h0 - 1): with X at row h + r - 1,
+//   rows  0..63  accumulate  sum dY[h]   * X[h + r - 1]  = filter row r,
+//   rows 64..127 accumulate  sum dY[h-1] * X[h + r - 1]  = sum dY[h'] * X[h' + r] = filter row r + 1,
+// so the work items are r in {0, 2} (two instead of three; the upper half of r = 2 is discarded) and the tile grid covers one
+// extra image row (h = H: dY out of bounds = TMA zero fill for the lower half, dY[H-1] for the upper half).
 struct WgradRow3Params {
     int wt, ht, nt, tiles_w, tiles_h, tiles_n, num_pix_tiles;
     int num_m_tiles, num_n_tiles, ksplit, tiles_per_split;
@@ -194,6 +202,7 @@ struct WgradRow3Params {
     int stage_bytes, stages;
     float* dw;               // packed [Cout][9][Cin]
     int dtype;
+    int stack;               // Cout <= 64: two filter rows per work item (see above)
 };
 
 template <int BN>
@@ -234,7 +243,9 @@ conv_wgrad_row3_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_
 
     // work item = blockIdx.x -> (ksplit, n_tile, m_tile, r), r fastest (neighbouring CTAs share pixel tiles in L2)
     int item = blockIdx.x;
-    const int r = item % 3; item /= 3;
+    int r;
+    if (p.stack) { r = (item & 1) * 2; item >>= 1; }
+    else { r = item % 3; item /= 3; }
     const int m_tile = item % p.num_m_tiles; item /= p.num_m_tiles;
     const int n_tile = item % p.num_n_tiles; item /= p.num_n_tiles;
     const int ks = item;
@@ -256,7 +267,8 @@ conv_wgrad_row3_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_
                 const uint32_t sa = smem_base + s * p.stage_bytes;
                 mbar_arrive_expect_tx(full_bar(s), kWgABytes + (BN / 64) * p.b_box_bytes);
                 tma_load_4d(sa, &map_dy, full_bar(s), m_tile * 128, w0, h0, n0);
-                tma_load_4d(sa + kWgAtomBytes, &map_dy, full_bar(s), m_tile * 128 + 64, w0, h0, n0);
+                if (p.stack) tma_load_4d(sa + kWgAtomBytes, &map_dy, full_bar(s), 0, w0, h0 - 1, n0);
+                else tma_load_4d(sa + kWgAtomBytes, &map_dy, full_bar(s), m_tile * 128 + 64, w0, h0, n0);
 #pragma unroll
                 for (int a = 0; a < BN / 64; ++a)
                     tma_load_4d(sa + kWgABytes + a * p.b_atom_bytes, &map_xh, full_bar(s), n_tile * BN + a * 64, w0 - 1,
@@ -289,12 +301,13 @@ conv_wgrad_row3_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_
         }
     } else if (n_iters > 0) {
         const int q = warp & 3;
-        const int co = m_tile * 128 + q * 32 + lane;
+        const int co = p.stack ? (q & 1) * 32 + lane : m_tile * 128 + q * 32 + lane;
+        const int tr = p.stack ? r + (q >> 1) : r;           // filter row this TMEM lane quarter holds
         mbar_wait(done_bar, 0);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
-        for (int sx = 0; sx < 3; ++sx) {
+        for (int sx = 0; sx < 3 && tr < 3; ++sx) {
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 uint32_t v[32];
@@ -302,7 +315,7 @@ conv_wgrad_row3_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_
                 tmem_ld_wait();
                 const int ci0 = n_tile * BN + c * 32;
                 if (co < p.cout) {
-                    float* dst = p.dw + (static_cast<size_t>(co) * 9 + r * 3 + sx) * p.cin + ci0;
+                    float* dst = p.dw + (static_cast<size_t>(co) * 9 + tr * 3 + sx) * p.cin + ci0;
 #pragma unroll
                     for (int j = 0; j < 32; j += 4)
                         if (ci0 + j < p.cin)
@@ -386,7 +399,9 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     WgradRow3Params wp{};
     if (!wg_choose_tile_row3(a->N, a->H, a->W, &wp.wt, &wp.ht, &wp.nt)) return 0;
     const int Ho = a->H, Wo = a->W;
-    wp.tiles_w = (Wo + wp.wt - 1) / wp.wt; wp.tiles_h = (Ho + wp.ht - 1) / wp.ht; wp.tiles_n = (a->N + wp.nt - 1) / wp.nt;
+    static const bool no_stack = getenv("VU_WGRAD_NO_STACK") != nullptr;
+    wp.stack = (!no_stack && a->Cout <= 64 && wp.ht * 8 <= Ho) ? 1 : 0;
+    wp.tiles_w = (Wo + wp.wt - 1) / wp.wt; wp.tiles_h = (Ho + wp.stack + wp.ht - 1) / wp.ht; wp.tiles_n = (a->N + wp.nt - 1) / wp.nt;
     wp.num_pix_tiles = wp.tiles_w * wp.tiles_h * wp.tiles_n;
     // measured on B200 (scripts/prof_wgrad.py): the row kernel wins from 2048 pixel tiles up (+30..60 %), the per-tap kernel
     // below 512 (three times more work items keep the K splits long enough to amortise prologue + reductions)
@@ -403,7 +418,7 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     wp.stages = smem_budget / wp.stage_bytes;
     if (wp.stages > 4) wp.stages = 4;
     if (wp.stages < 2) return 0;
-    const int base_items = 3 * wp.num_m_tiles * wp.num_n_tiles;
+    const int base_items = (wp.stack ? 2 : 3) * wp.num_m_tiles * wp.num_n_tiles;
     static const int waves_x2 = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 3;   // CTAs = SMs * waves_x2 / 2 (sweep: profiles/r2f_wgrad_knobs.log)
     int ksplit = (waves_x2 * num_sms() / 2 + base_items - 1) / base_items;
     if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
