@@ -63,10 +63,11 @@ def test_maxpool(cuda_dev, k, s, p, H, W):
     assert torch.equal(got, ref)
 
 
+@pytest.mark.parametrize("C", [32, 24, 128, 512])       # 24: generic kernel; powers of two: the pixel-run kernel
 @pytest.mark.parametrize("Hs,Ws,Ho,Wo", [(16, 16, 32, 32), (22, 22, 44, 44), (88, 88, 175, 175), (1, 1, 8, 8), (5, 7, 5, 7)])
-def test_bilinear(cuda_dev, Hs, Ws, Ho, Wo):
+def test_bilinear(cuda_dev, Hs, Ws, Ho, Wo, C):
     from vaeunet_b200 import ops
-    x = _q(torch.randn(2, 32, Hs, Ws))
+    x = _q(torch.randn(2, C, Hs, Ws))
     ref = F.interpolate(x, size=(Ho, Wo), mode="bilinear", align_corners=True)
     got = _from_act(ops.bilinear_ac(_to_act(ops, x, cuda_dev), Ho, Wo))
     assert (got - ref).abs().max() <= 8e-3 * max(ref.abs().max().item(), 1.0)

@@ -181,23 +181,26 @@ def test_maxpool_bilinear_bwd(cuda_dev):
     dx = T.maxpool_bwd(_act(ops, x, d), _act(ops, dy, d), 3, 2, 1)
     assert (_nchw(dx) - xr.grad).abs().max() <= 1e-2 * xr.grad.abs().max()
     # saved-argmax variant (training fast path), with ties: ReLU'd input has many all-zero windows
-    xz = _q(torch.relu(torch.randn(2, 16, 13, 14, generator=g) - 0.8))
-    xzr = xz.clone().requires_grad_(True)
-    yz = F.max_pool2d(xzr, 3, 2, 1)
-    dyz = _q(torch.randn(yz.shape, generator=g))
-    yz.backward(dyz)
-    y2, code = T.maxpool_idx_fwd(_act(ops, xz, d), 3, 2, 1)
-    assert (_nchw(y2) - yz.detach()).abs().max() == 0
-    dx2 = T.maxpool_idx_bwd(code, _act(ops, dyz, d), 13, 14, 3, 2, 1)
-    assert (_nchw(dx2) - xzr.grad).abs().max() <= 1e-2 * xzr.grad.abs().max()
+    # (64 channels: the k3 s2 p1 specialisation of the backward; 16: the generic kernel)
+    for (Cc, hh, ww) in [(16, 13, 14), (64, 13, 14), (64, 32, 40)]:
+        xz = _q(torch.relu(torch.randn(2, Cc, hh, ww, generator=g) - 0.8))
+        xzr = xz.clone().requires_grad_(True)
+        yz = F.max_pool2d(xzr, 3, 2, 1)
+        dyz = _q(torch.randn(yz.shape, generator=g))
+        yz.backward(dyz)
+        y2, code = T.maxpool_idx_fwd(_act(ops, xz, d), 3, 2, 1)
+        assert (_nchw(y2) - yz.detach()).abs().max() == 0
+        dx2 = T.maxpool_idx_bwd(code, _act(ops, dyz, d), hh, ww, 3, 2, 1)
+        assert (_nchw(dx2) - xzr.grad).abs().max() <= 1e-2 * xzr.grad.abs().max(), (Cc, hh, ww)
     for (hs, ws, ho, wo) in [(8, 8, 16, 16), (11, 9, 22, 17), (1, 1, 5, 6), (16, 16, 32, 32), (64, 64, 128, 128),
                              (5, 7, 17, 20), (32, 48, 63, 97)]:     # x2 (unrolled tap kernel), x3 and odd sizes
-        x = torch.randn(2, 24, hs, ws, generator=g).requires_grad_(True)
-        y = F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
-        dy = _q(torch.randn(y.shape, generator=g))
-        y.backward(dy)
-        dx = T.bilinear_ac_bwd(_act(ops, dy, d), hs, ws)
-        assert ((_nchw(dx) - x.grad).norm() / x.grad.norm()).item() < 5e-3, (hs, ws, ho, wo)
+        for Cc in (24, 64, 256):                                     # generic tap kernel / the pixel-run kernel
+            x = torch.randn(2, Cc, hs, ws, generator=g).requires_grad_(True)
+            y = F.interpolate(x, size=(ho, wo), mode="bilinear", align_corners=True)
+            dy = _q(torch.randn(y.shape, generator=g))
+            y.backward(dy)
+            dx = T.bilinear_ac_bwd(_act(ops, dy, d), hs, ws)
+            assert ((_nchw(dx) - x.grad).norm() / x.grad.norm()).item() < 5e-3, (hs, ws, ho, wo, Cc)
         m = torch.randn(3, ho, wo, generator=g)
         xm = torch.randn(3, 1, hs, ws, generator=g).requires_grad_(True)
         F.interpolate(xm, size=(ho, wo), mode="bilinear", align_corners=True).backward(m.unsqueeze(1))

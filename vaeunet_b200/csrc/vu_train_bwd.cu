@@ -2,6 +2,7 @@
 // align_corners resize (16-bit NHWC maps and fp32 single-channel maps), and the per-pixel pieces of the
 // attention gate / output conv (scale by a map, channel dot product, outer product with a vector,
 // map-weighted channel sums, per-image channel sums). Gather formulations: deterministic, no 16-bit atomics.
+#include <cstdlib>
 #include "vu_half.cuh"
 #include "vu_internal.h"
 
@@ -128,6 +129,45 @@ maxpool_idx_bwd_kernel(const uint8_t* __restrict__ code, const uint16_t* __restr
     }
 }
 
+// ResNet's pool (k 3, s 2, p 1) on a power-of-two channel count: one block row per input row (no div/mod), the eight window
+// codes of a chunk compared in two SIMD byte compares, the matching dy halves selected by AND masks before the fp32 sum
+// (same sums as the generic kernel: the non-matching terms are exact zeros either way).
+template <int C8>
+__global__ void __launch_bounds__(256)
+maxpool_idx_bwd_k3s2_kernel(const uint8_t* __restrict__ code, const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff,
+                            uint16_t* __restrict__ dx, int dx_ctot, int dx_coff, int H, int W, int Ho, int Wo, int dtype) {
+    const int ih = blockIdx.y, n = blockIdx.z;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int iw = t / C8, c8 = t % C8;
+    if (iw >= W) return;
+    const int ho_lo = ih >> 1, ho_hi = min(Ho - 1, (ih + 1) >> 1);
+    const int wo_lo = iw >> 1, wo_hi = min(Wo - 1, (iw + 1) >> 1);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        const int ho = ho_lo + a;
+        if (ho > ho_hi) break;
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const int wo = wo_lo + b;
+            if (wo > wo_hi) break;
+            const uint32_t me = (uint32_t)((ih - (ho * 2 - 1)) * 3 + (iw - (wo * 2 - 1)));
+            const uint32_t me4 = me * 0x01010101u;
+            const size_t o = ((size_t)n * Ho + ho) * Wo + wo;
+            const uint2 pk = __ldg(reinterpret_cast<const uint2*>(code + o * (size_t)(C8 * 8)) + c8);
+            uint4 v = __ldg(reinterpret_cast<const uint4*>(dy + o * dy_ctot + dy_coff) + c8);
+            const uint32_t m0 = __vcmpeq4(pk.x, me4), m1 = __vcmpeq4(pk.y, me4);
+            v.x &= __byte_perm(m0, 0, 0x1100); v.y &= __byte_perm(m0, 0, 0x3322);
+            v.z &= __byte_perm(m1, 0, 0x1100); v.w &= __byte_perm(m1, 0, 0x3322);
+            float g[8];
+            unpack8(v, g, dtype);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += g[j];
+        }
+    }
+    *(reinterpret_cast<uint4*>(dx + (((size_t)n * H + ih) * W + iw) * dx_ctot + dx_coff) + c8) = pack8(acc, dtype);
+}
+
 // ---------------------------------------------------------------- bilinear (align_corners=True) backward
 // Adjoint of vu_bilinear_ac_nhwc as a gather: source pixel (hs,ws) collects w(ho;hs) * w(wo;ws) * dy[ho,wo] over the
 // few destination rows / columns whose interpolation footprint contains it (same fp32 index arithmetic as forward).
@@ -244,6 +284,88 @@ bilinear_bwd_taps_kernel(const uint16_t* __restrict__ dy, int dy_ctot, int dy_co
         }
         *dp = pack8(acc, dtype);
     }
+}
+
+// The same gather with the tap tables built ONCE per run of source pixels: a warp owns RUN = min(32, 256 / C8) consecutive
+// source pixels of one source row, lane p computes the first destination column and the five column weights of pixel p into
+// shared memory (lerp_taps costs ~300 instructions: per pixel now, not per 16-byte chunk), the row taps are warp-uniform.
+// Lanes then walk the flattened (pixel, chunk) list with compile-time shifts. Arithmetic and summation order are those of
+// bilinear_bwd_taps_kernel: results are bit-identical.
+template <int C8>
+__global__ void __launch_bounds__(128)
+bilinear_bwd_run_kernel(const uint16_t* __restrict__ dy, int dy_ctot, int dy_coff, uint16_t* __restrict__ dx, int dx_ctot,
+                        int dx_coff, int Hs, int Ws, int Ho, int Wo, float sh, float sw, int accumulate, int dtype,
+                        int runs_per_row, int num_runs) {
+    constexpr int RUN = (256 / C8 < 32) ? 256 / C8 : 32;
+    constexpr int PASSES = RUN * C8 / 32;
+    __shared__ float s_cw[4][32][kBilTaps];
+    __shared__ int s_c0[4][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int run = blockIdx.x * 4 + warp;
+    if (run >= num_runs) return;                 // warp-uniform; only __syncwarp below
+    const int n = blockIdx.y;
+    const int hs = run / runs_per_row;
+    const int ws0 = (run - hs * runs_per_row) * RUN;
+    const int npx = min(RUN, Ws - ws0);
+    float rw[kBilTaps];
+    const int r0 = lerp_taps(hs, sh, Hs, Ho, rw);
+    if (lane < RUN) {
+        float cw[kBilTaps];
+        s_c0[warp][lane] = lerp_taps(ws0 + min(lane, npx - 1), sw, Ws, Wo, cw);
+#pragma unroll
+        for (int k = 0; k < kBilTaps; ++k) s_cw[warp][lane][k] = cw[k];
+    }
+    __syncwarp();
+    const uint16_t* img = dy + (size_t)n * Ho * Wo * dy_ctot + dy_coff;
+    uint16_t* orow = dx + (((size_t)n * Hs + hs) * Ws + ws0) * dx_ctot + dx_coff;
+#pragma unroll 1
+    for (int pass = 0; pass < PASSES; ++pass) {
+        const int idx = pass * 32 + lane, px = idx / C8, c8 = idx % C8;
+        float cw[kBilTaps];
+#pragma unroll
+        for (int k = 0; k < kBilTaps; ++k) cw[k] = s_cw[warp][px][k];
+        const uint16_t* base = img + (size_t)s_c0[warp][px] * dy_ctot + c8 * 8;
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int i = 0; i < kBilTaps; ++i) {
+            if (rw[i] == 0.f) continue;            // warp-uniform
+            const uint16_t* row = base + (size_t)(r0 + i) * Wo * dy_ctot;
+            uint4 v[kBilTaps];
+#pragma unroll
+            for (int k = 0; k < kBilTaps; ++k)
+                v[k] = (cw[k] != 0.f) ? __ldg(reinterpret_cast<const uint4*>(row + (size_t)k * dy_ctot)) : make_uint4(0, 0, 0, 0);
+            float t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < kBilTaps; ++k) {
+                float g[8];
+                unpack8(v[k], g, dtype);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) t[q] = fmaf(cw[k], g[q], t[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[q] = fmaf(rw[i], t[q], acc[q]);
+        }
+        if (px < npx) {
+            uint4* dp = reinterpret_cast<uint4*>(orow + (size_t)px * dx_ctot) + c8;
+            if (accumulate) {
+                float o[8];
+                unpack8(*dp, o, dtype);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) acc[q] += o[q];
+            }
+            *dp = pack8(acc, dtype);
+        }
+    }
+}
+
+template <int C8>
+static void launch_bilinear_bwd_run(const uint16_t* dy, int dy_ctot, int dy_coff, uint16_t* dx, int dx_ctot, int dx_coff, int N,
+                                    int Hs, int Ws, int Ho, int Wo, float sh, float sw, int accumulate, int dtype,
+                                    cudaStream_t st) {
+    constexpr int RUN = (256 / C8 < 32) ? 256 / C8 : 32;
+    const int runs_per_row = (Ws + RUN - 1) / RUN, num_runs = Hs * runs_per_row;
+    bilinear_bwd_run_kernel<C8><<<dim3((num_runs + 3) / 4, N), 128, 0, st>>>(dy, dy_ctot, dy_coff, dx, dx_ctot, dx_coff, Hs, Ws, Ho,
+                                                                           Wo, sh, sw, accumulate, dtype, runs_per_row, num_runs);
 }
 
 __global__ void __launch_bounds__(256)
@@ -402,6 +524,12 @@ extern "C" int vu_maxpool_idx_bwd(const void* code, const void* dy, void* dx, in
     if (!code || !dy || !dx || k < 1 || k > 3) return set_error(VU_ERR_INVALID, "maxpool_idx_bwd: bad args (k <= 3)");
     VU_TB_ALIGN((C | dy_ctot | dy_coff | dx_ctot | dx_coff) % 8, "maxpool_idx_bwd");
     const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+    if (k == 3 && s == 2 && p == 1 && C == 64 && H <= 65535 && N <= 65535) {
+        maxpool_idx_bwd_k3s2_kernel<8><<<dim3((W * 8 + 255) / 256, H, N), 256, 0, (cudaStream_t)st>>>(
+            (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, H, W, Ho, Wo, dtype);
+        VU_CHECK_LAUNCH("maxpool_idx_bwd_k3s2");
+        return 0;
+    }
     if ((size_t)N * H * W * (C / 8) < (1ull << 31))
         maxpool_idx_bwd_kernel<uint32_t><<<tb_grid((size_t)N * H * W * (C / 8)), 256, 0, (cudaStream_t)st>>>(
             (const uint8_t*)code, (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, H, W, C / 8, k, s, p,
@@ -421,7 +549,18 @@ extern "C" int vu_bilinear_ac_bwd(const void* dy, void* dx, int N, int Hs, int W
     const float sh = Ho > 1 ? (float)(Hs - 1) / (float)(Ho - 1) : 0.0f;
     const float sw = Wo > 1 ? (float)(Ws - 1) / (float)(Wo - 1) : 0.0f;
     // a source pixel is touched by at most 2/scale + 1 destination rows: the unrolled kernel covers the x2 upsamples
-    if (sh >= 0.4f && sw >= 0.4f && (size_t)N * Hs * Ws * (C / 8) < (1ull << 31))
+    static const bool generic_only = getenv("VU_BILINEAR_GENERIC") != nullptr;
+    const bool taps_ok = sh >= 0.4f && sw >= 0.4f && (size_t)N * Hs * Ws * (C / 8) < (1ull << 31);
+#define VU_BILB_CASE(c8)                                                                                                       \
+    if (taps_ok && !generic_only && N <= 65535 && C / 8 == c8) {                                                               \
+        launch_bilinear_bwd_run<c8>((const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, sh, \
+                                    sw, accumulate, dtype, (cudaStream_t)st);                                                  \
+        VU_CHECK_LAUNCH("bilinear_bwd_run");                                                                                   \
+        return 0;                                                                                                              \
+    }
+    VU_BILB_CASE(4) VU_BILB_CASE(8) VU_BILB_CASE(16) VU_BILB_CASE(32) VU_BILB_CASE(64)
+#undef VU_BILB_CASE
+    if (taps_ok)
         bilinear_bwd_taps_kernel<uint32_t><<<tb_grid((size_t)N * Hs * Ws * (C / 8)), 256, 0, (cudaStream_t)st>>>(
             (const uint16_t*)dy, dy_ctot, dy_coff, (uint16_t*)dx, dx_ctot, dx_coff, N, Hs, Ws, Ho, Wo, C / 8, sh, sw, accumulate,
             dtype);
