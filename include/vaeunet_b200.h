@@ -298,6 +298,15 @@ int vu_confusion_counts(const float* x, const float* t, size_t n, float thr, dou
 size_t vu_sort_workspace_bytes(size_t n);
 int vu_sort_pairs_desc_f32(const float* score, const uint32_t* vals, size_t n, uint32_t* keys_sorted, uint32_t* vals_sorted,
                            void* workspace, size_t workspace_bytes, vu_stream_t stream);
+/* vu_sort_pairs_desc_f32_static: the same sort with NO caller workspace and no allocation of any kind - its scratch is a
+ * file-scope device array inside the library. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid allocation).
+ * Limit: n <= VU_SORT_STATIC_MAX_N pairs (one 512 x 512 map; larger n is rejected with VU_ERR_UNSUPPORTED); the 6.1 MB array is
+ * held by every GPU that loads the library until the process exits. All calls share it: calls that overlap on the GPU
+ * (different streams / threads) race - serialise them on one stream. */
+#define VU_SORT_STATIC_MAX_N 262144
+int vu_sort_pairs_desc_f32_static(const float* score, const uint32_t* vals, size_t n, uint32_t* keys_sorted,
+                                  uint32_t* vals_sorted, vu_stream_t stream);
 /* err[i] = -(g log(p + eps) + (1 - g) log(1 - p + eps)) (uncertainty_metrics.py:179-181); stats: 4 doubles -
  * [0] sum of the non-NaN errors, [1] number of NaNs, and two uint32 in the low words of [2]: order-preserving encodings
  * (u ^ (sign ? ~0 : 1 << 31)) of the minimum and maximum error. */

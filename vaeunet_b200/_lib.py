@@ -85,6 +85,7 @@ SIGNATURES = {
     "vu_confusion_counts": [p, p, sz, f, p, p],
     # ---- sort-based uncertainty metrics
     "vu_sort_pairs_desc_f32": [p, p, sz, p, p, p, sz, p],
+    "vu_sort_pairs_desc_f32_static": [p, p, sz, p, p, p],
     "vu_pixel_nll_errors": [p, p, sz, f, p, p, p],
     "vu_sorted_bin_sums": [p, sz, p, i, p, p],
     "vu_masked_sum": [p, p, sz, p, p],

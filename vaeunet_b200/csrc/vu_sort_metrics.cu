@@ -407,3 +407,43 @@ extern "C" int vu_binary_curve_auc(const uint32_t* keys_sorted, const uint32_t* 
     VU_CHECK_LAUNCH("binary_curve_auc");
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of vu_sort_pairs_desc_f32 for callers that cannot call cudaMalloc (CUDA graph capture, serving
+// loops, harnesses that forbid allocation): the radix sort's workspace (ping-pong key / payload buffers + digit histograms)
+// lives in a file-scope device array instead of a caller-provided buffer. Limit: n <= VU_SORT_STATIC_MAX_N = 262 144 pairs (one
+// 512 x 512 map); the array is 6.1 MB and is held by every GPU that loads the library until the process exits.
+// ALL calls share the array: two calls that overlap on the GPU (different streams, or one device from two threads) race.
+// Nothing in it has to start at zero - every word the sort reads was written earlier in the same call (keys by
+// make_keys_kernel, every histogram slot by radix_hist_kernel) - so stale contents of the previous call are harmless.
+namespace vu {
+constexpr size_t kSortStaticMaxN = 262144;
+constexpr size_t kSortStaticNb = (kSortStaticMaxN + kSortTile - 1) / kSortTile;
+constexpr size_t a256(size_t v) { return (v + 255) / 256 * 256; }
+constexpr size_t kSortStaticBytes = 4 * a256(kSortStaticMaxN * 4) + a256((size_t)kRadix * kSortStaticNb * 4) +
+                                    2 * a256(kSortStaticNb * 4) + a256(kSortStaticMaxN * 8) + 1024;
+static __device__ __align__(256) unsigned char g_sort_scratch[kSortStaticBytes];
+}  // namespace vu
+
+extern "C" int vu_sort_pairs_desc_f32_static(const float* score, const uint32_t* vals, size_t n, uint32_t* keys_sorted,
+                                             uint32_t* vals_sorted, vu_stream_t st) {
+    if (n > kSortStaticMaxN)
+        return set_error(VU_ERR_UNSUPPORTED, "sort_pairs_static: n = %zu exceeds the static scratch limit of %zu pairs (use "
+                         "vu_sort_pairs_desc_f32 with a caller workspace)", n, (size_t)kSortStaticMaxN);
+    // the symbol's name is a host-side stand-in; its device address is looked up once per device, with that device current
+    constexpr int kMaxDev = 64;
+    static void* dev_ptr[kMaxDev] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDev)
+        return set_error(VU_ERR_CUDA, "sort_pairs_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_sort_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return set_error(VU_ERR_CUDA, "sort_pairs_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        dev_ptr[dev] = p;
+    }
+    if (vu_sort_workspace_bytes(n ? n : 1) > kSortStaticBytes) return set_error(VU_ERR_UNSUPPORTED, "sort_pairs_static: scratch too small");
+    return vu_sort_pairs_desc_f32(score, vals, n, keys_sorted, vals_sorted, dev_ptr[dev], kSortStaticBytes, st);
+}
