@@ -1,14 +1,12 @@
 #!/bin/bash
-# scratch trip: stem split-TF32 parity margins + one-wave grids of the BatchNorm kernels (in-situ kernel sums)
+# scratch trip: flat padded tap-reuse kernel vs the CTA-pair implicit GEMM, layer shapes of the training step (N=16) and MC encoder
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 O=gpurun_out/$1
-python scripts/debug_mc700.py > ${O}_mc700.log 2>&1; cat ${O}_mc700.log | cut -c1-250
-python -m pytest tests/test_memops_gpu.py -x -q -m gpu -k "stem or small_cin" 2>&1 | tail -2
-python bench.py --workload mc --no-cpu-baseline --no-gpu-eager > ${O}_bench_mc.json 2> ${O}_bench_mc.err; tail -c 300 ${O}_bench_mc.json; tail -3 ${O}_bench_mc.err
-for cfg in "8 16 16" "2 16 16" "8 3 16" "8 16 2" "2 3 2" "3 4 3" "4 6 4"; do
-  set -- $cfg
-  echo "== VU_BN_MULT_SUMS=$1 APPLY=$2 BWD=$3"
-  VU_BN_MULT_SUMS=$1 VU_BN_MULT_APPLY=$2 VU_BN_MULT_BWD=$3 python scripts/train_kineto.py 2>&1 | grep "span\|channel_sums_kernel<1>\|bn_bwd_apply\|bn_apply"
-done > ${O}_bn_grid.log 2>&1
-cat ${O}_bn_grid.log
+for shape in "16 64 64 128 128 3" "16 32 32 256 256 3" "16 16 16 512 512 3" "16 32 32 800 512 3" "16 32 32 512 512 3" "16 64 64 672 256 3" "16 64 64 256 256 3" "16 64 64 320 256 3"; do
+  for env in "VU_FLAT=0" "VU_FLAT=2 VU_FLAT_MT=2" "VU_FLAT=2 VU_FLAT_MT=1"; do
+    echo -n "$env  "; env $env python scripts/prof_conv.py $shape 6 f16 | tail -1
+    echo -n "$env stats "; env $env python scripts/prof_conv.py $shape 6 f16 stats | tail -1
+  done
+done > ${O}_flat_vs_pair.log 2>&1
+cat ${O}_flat_vs_pair.log

@@ -38,13 +38,25 @@ CASES = [
     ("pair_cout320", 2, 32, 32, 128, 320, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
     ("pair_slices_res", 2, 32, 32, 192, 256, 3, 1, True, True, (64, 320), (128, 512), "f16"),
     ("pair_1x1_s2", 4, 32, 32, 128, 256, 1, 2, False, False, (0, 0), (0, 0), "bf16"),
+    # flat padded tap-reuse kernel (vu_conv_flat.cu): W <= 64; 256 / 128 positions per CTA, several N tiles, partial last
+    # N tile (Cout 672 = 5 x 128 + 32), partial last K block (Cin 672), odd tile counts, ragged heights, slices + residual
+    ("flat_w64_128", 16, 64, 64, 128, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("flat_w32_256", 16, 32, 32, 256, 256, 3, 1, True, True, (0, 0), (0, 0), "f16"),
+    ("flat_w16_512", 8, 16, 16, 512, 512, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("flat_cout672", 2, 64, 64, 256, 672, 3, 1, False, False, (0, 0), (0, 0), "f16"),
+    ("flat_cin672", 2, 64, 64, 672, 256, 3, 1, True, False, (0, 0), (0, 0), "f16"),
+    ("flat_ragged", 3, 37, 41, 96, 160, 3, 1, True, True, (32, 160), (64, 256), "f16"),
+    ("flat_w8", 5, 9, 8, 64, 64, 3, 1, True, False, (0, 0), (0, 0), "bf16"),
+    ("flat_one_image", 1, 64, 64, 128, 128, 3, 1, True, False, (0, 0), (0, 0), "f16"),
 ]
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
-def test_conv_igemm(case, cuda_dev):
+def test_conv_igemm(case, cuda_dev, monkeypatch):
     from vaeunet_b200 import ops
     name, N, H, W, Cin, Cout, k, stride, relu, use_res, xs, ys, dt = case
+    if name.startswith("flat_"):
+        monkeypatch.setenv("VU_FLAT", "2")       # every shape that fits (auto mode takes Cout <= 128 only)
     tdt = torch.bfloat16 if dt == "bf16" else torch.float16
     odt = ops.BF16 if dt == "bf16" else ops.F16
     g = torch.Generator().manual_seed(zlib.crc32(name.encode()))

@@ -49,12 +49,17 @@ CONV_SHAPES = [
     (2, 50, 128, 64, 64, 3, True),     # tap-reuse HT=2 + statistics (the shape class of the round-2 race)
     (1, 37, 100, 128, 128, 3, True),   # tap-reuse<128> + statistics, ragged
     (2, 24, 24, 96, 64, 1, False),     # 1x1
+    (16, 64, 64, 128, 128, 3, True),   # flat padded tap-reuse (W <= 64), 256 positions per CTA + statistics
+    (16, 32, 32, 256, 256, 3, True),   # flat, two N tiles + statistics
+    (3, 21, 30, 64, 96, 3, False),     # flat, ragged, partial N tile
 ]
 
 
 @pytest.mark.parametrize("N,H,W,Cin,Cout,k,stats", CONV_SHAPES)
-def test_conv_stays_inside_its_slice(cuda_dev, N, H, W, Cin, Cout, k, stats):
+def test_conv_stays_inside_its_slice(cuda_dev, monkeypatch, N, H, W, Cin, Cout, k, stats):
     from vaeunet_b200 import ops
+    if (N, H) in ((16, 64), (16, 32), (3, 21)):
+        monkeypatch.setenv("VU_FLAT", "2")       # the flat padded tap-reuse kernel for every narrow shape (the other rows keep theirs)
     g = torch.Generator(device=cuda_dev).manual_seed(N * 1000 + H)
     x = ops.Act(torch.randn(N, H, W, Cin, device=cuda_dev, generator=g).half())
     w = ops.pack_conv_weight(torch.randn(Cout, Cin, k, k, device=cuda_dev, generator=g) * (Cin * k * k) ** -0.5, ops.F16)
@@ -126,8 +131,11 @@ def test_concat_and_first_conv_stay_inside(cuda_dev):
         assert ok() and torch.equal(out.t[..., out.coff:out.coff + 64], ref.t)
 
 
-@pytest.mark.parametrize("N,H,W,Cin,Cout", [(4, 128, 128, 64, 64), (2, 96, 256, 160, 64), (2, 128, 128, 128, 128), (8, 32, 32, 256, 256)])
-def test_training_epilogue_is_run_to_run_identical(cuda_dev, N, H, W, Cin, Cout):
+@pytest.mark.parametrize("N,H,W,Cin,Cout", [(4, 128, 128, 64, 64), (2, 96, 256, 160, 64), (2, 128, 128, 128, 128), (8, 32, 32, 256, 256),
+                                            (16, 64, 64, 128, 128), (16, 16, 16, 512, 512)])
+def test_training_epilogue_is_run_to_run_identical(cuda_dev, monkeypatch, N, H, W, Cin, Cout):
+    if N == 16:
+        monkeypatch.setenv("VU_FLAT", "2")
     """The statistics partials are per warp; a shared slice raced in round 2 (wrong sums in ~1 of 3 runs at W >= 96)."""
     from vaeunet_b200 import ops
     g = torch.Generator(device=cuda_dev).manual_seed(W + Cin)

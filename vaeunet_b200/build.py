@@ -17,7 +17,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 OUT = PKG / "libvaeunet_b200.so"
 OBJ = PKG / "build"
-SOURCES = ["vu_api.cu", "vu_conv_igemm.cu", "vu_conv_halo.cu", "vu_conv_wgrad.cu", "vu_layout.cu", "vu_small_cin_mma.cu", "vu_gate_latent.cu", "vu_decoder_concat.cu",
+SOURCES = ["vu_api.cu", "vu_conv_igemm.cu", "vu_conv_halo.cu", "vu_conv_flat.cu", "vu_conv_wgrad.cu", "vu_layout.cu", "vu_small_cin_mma.cu", "vu_gate_latent.cu", "vu_decoder_concat.cu",
            "vu_uncertainty.cu", "vu_sort_metrics.cu", "vu_tiles.cu", "vu_loss.cu", "vu_train.cu", "vu_train_bwd.cu", "vu_train_small.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

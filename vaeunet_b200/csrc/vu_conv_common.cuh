@@ -139,5 +139,7 @@ static inline int encode_map(CUtensorMap* m, int dtype, int rank, const void* ba
 // vu_conv_halo.cu: 3x3 s1 p1 convs with Cout in {64,128} on wide maps (smem tap reuse). Returns 1 when it
 // took the launch, 0 when the shape is not its case, < 0 on error.
 int conv3x3_halo_launch(const vu_conv_args* a, cudaStream_t stream);
+// vu_conv_flat.cu: 3x3 s1 p1 convs on narrow maps (W <= 64), tap reuse over a flat padded pixel index. Same return values.
+int conv3x3_flat_launch(const vu_conv_args* a, cudaStream_t stream);
 
 }  // namespace vu

@@ -585,6 +585,10 @@ extern "C" int vu_conv2d_fwd(const vu_conv_args* a, vu_stream_t stream_) {
         const int rc = conv3x3_halo_launch(a, stream);
         if (rc != 0) return rc < 0 ? rc : 0;
     }
+    {   // 3x3 on narrow maps (W <= 64): tap reuse over a flat padded pixel index (vu_conv_flat.cu)
+        const int rc = conv3x3_flat_launch(a, stream);
+        if (rc != 0) return rc < 0 ? rc : 0;
+    }
     if (a->fuse_out || !a->y)
         return set_error(VU_ERR_UNSUPPORTED, "conv: fused output conv needs 3x3 s1 p1, Cout 64/128, W >= 96");
 
