@@ -17,6 +17,10 @@ CASES = [
     ("wg_1x1_s2_64_128", 2, 32, 32, 64, 128, 1, 2),
     ("wg_3x3_32_32_odd", 2, 11, 13, 32, 32, 3, 1),
     ("wg_3x3_ksplit", 4, 128, 128, 64, 64, 3, 1),
+    # Cin % 256 == 0: the 256-column N tile of the per-tap kernel
+    ("wg_3x3_256_256", 4, 32, 32, 256, 256, 3, 1),
+    ("wg_3x3_s2_256_512", 3, 32, 32, 256, 512, 3, 2),
+    ("wg_3x3_512_512_small", 5, 16, 16, 512, 512, 3, 1),
 ]
 
 
@@ -32,7 +36,9 @@ def _setup(case, dev, dt=torch.bfloat16):
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
-def test_conv_wgrad(case, cuda_dev):
+def test_conv_wgrad(case, cuda_dev, monkeypatch):
+    if case[4] % 256 == 0:
+        monkeypatch.setenv("VU_WGRAD_BN256", "1")     # the 256-column N tile (off by default; read per call)
     from vaeunet_b200 import ops
     name, N, H, W, Cin, Cout, k, stride = case
     x, w, dy, pad = _setup(case, cuda_dev)

@@ -33,7 +33,7 @@ struct WgradParams {
 template <int BN> struct WgCfg {
     static constexpr int kBBytes = (BN / 64) * kWgAtomBytes;
     static constexpr int kStageBytes = kWgABytes + kBBytes;
-    static constexpr int kStages = (BN == 128) ? 3 : 4;
+    static constexpr int kStages = (BN == 256) ? 2 : ((BN == 128) ? 3 : 4);     // BN = 256: 96 KB per stage
     static constexpr int kTmemCols = BN < 32 ? 32 : BN;
     static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + 256;
 };
@@ -478,7 +478,12 @@ static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy
     wp.dw = dw; wp.dtype = a->dtype;
     if (oihw) { wp.co_stride = a->Cin * KH * KW; wp.tap_stride = 1; wp.ci_stride = KH * KW; }
     else { wp.co_stride = KH * KW * a->Cin; wp.tap_stride = a->Cin; wp.ci_stride = 1; }
-    const int bn = (a->Cin > 64) ? 128 : 64;
+    // N tile: 256 input channels per work item (VU_WGRAD_BN256=1) was built against the L2->SM bound of this kernel (ncu r1c:
+    // 8.2 TB/s): a k-iteration then moves 32 KB (dY) + 64 KB (X) for twice the MMA work of 32 + 32 KB. In the step it measured
+    // no gain (in-situ CUPTI sums 2.12 vs 2.01 ms per step over the 37 per-tap launches: only two 96 KB stages fit, and at
+    // B = 16 these launches are dominated by their split-K reductions, not by operand traffic), so it stays off by default.
+    const int bn256 = getenv("VU_WGRAD_BN256") ? atoi(getenv("VU_WGRAD_BN256")) : 0;
+    const int bn = (a->Cin > 64) ? ((bn256 && a->Cin % 256 == 0) ? 256 : 128) : 64;
     wp.num_m_tiles = (a->Cout + 127) / 128;
     wp.num_n_tiles = (a->Cin + bn - 1) / bn;
     const int base_items = wp.num_taps * wp.num_m_tiles * wp.num_n_tiles;
@@ -534,6 +539,7 @@ static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy
             }
     }
     const int grid = base_items * wp.ksplit;
+    if (bn == 256) return launch_wgrad<256>(dym, xm, wp, grid, stream);
     if (bn == 128) return launch_wgrad<128>(dym, xm, wp, grid, stream);
     return launch_wgrad<64>(dym, xm, wp, grid, stream);
 }
