@@ -1,12 +1,12 @@
 #!/bin/bash
-# scratch trip: flat padded tap-reuse kernel vs the CTA-pair implicit GEMM, layer shapes of the training step (N=16) and MC encoder
+# scratch trip: K-split policy of the weight gradients, in-situ kernel sums and step time
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 O=gpurun_out/$1
-for shape in "16 64 64 128 128 3" "16 32 32 256 256 3" "16 16 16 512 512 3" "16 32 32 800 512 3" "16 32 32 512 512 3" "16 64 64 672 256 3" "16 64 64 256 256 3" "16 64 64 320 256 3"; do
-  for env in "VU_FLAT=0" "VU_FLAT=2 VU_FLAT_MT=2" "VU_FLAT=2 VU_FLAT_MT=1"; do
-    echo -n "$env  "; env $env python scripts/prof_conv.py $shape 6 f16 | tail -1
-    echo -n "$env stats "; env $env python scripts/prof_conv.py $shape 6 f16 stats | tail -1
-  done
-done > ${O}_flat_vs_pair.log 2>&1
-cat ${O}_flat_vs_pair.log
+python -m pytest tests/test_train_kernels_gpu.py tests/test_guards_gpu.py -x -q -m gpu -k "wgrad" 2>&1 | tail -2
+for env in "VU_WGRAD_HALFWAVES=3" "VU_WGRAD_OVERHEAD=3" "VU_WGRAD_OVERHEAD=6" "VU_WGRAD_OVERHEAD=12" "VU_WGRAD_OVERHEAD=24"; do
+  echo "== $env"
+  env $env python scripts/train_kineto.py 2>&1 | grep "span\|wgrad"
+  env $env python scripts/train_breakdown.py 2>&1 | tail -1
+done > ${O}_ksplit.log 2>&1
+cat ${O}_ksplit.log

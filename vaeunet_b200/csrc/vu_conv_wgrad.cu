@@ -364,6 +364,37 @@ static int launch_wgrad(const CUtensorMap& dym, const CUtensorMap* xm, const Wgr
     return 0;
 }
 
+// K split of a weight-gradient launch. Default: a cost model - time ~ waves x (k-iterations per CTA + c), c = the prologue +
+// epilogue (TMEM allocation, pipeline fill, the 128 x BN fp32 reductions) in units of one k-iteration (VU_WGRAD_OVERHEAD,
+// default 12; 3..24 measure within 0.05 ms of each other, profiles/r2zq_ksplit.log) - minimised over the split count. The first policy, "fill 1.5 waves" (VU_WGRAD_HALFWAVES=n selects it for A/B
+// runs), overshot whole waves: 9 base items -> 25 splits = 225 CTAs = 1.52 waves of 20 k-iterations, where 16 splits = 144
+// CTAs = ONE wave of 32 k-iterations does the same work in ~25 % less time with a third less reduction traffic. Whole training step 12.43 -> 11.89 ms.
+static int wg_choose_ksplit(int base_items, int num_pix_tiles, int* tiles_per_split_out) {
+    static const int halfwaves = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 0;
+    static const double c_over = getenv("VU_WGRAD_OVERHEAD") ? atof(getenv("VU_WGRAD_OVERHEAD")) : 12.0;
+    int ksplit = 1;
+    if (halfwaves > 0) {
+        ksplit = (halfwaves * num_sms() / 2 + base_items - 1) / base_items;
+        if (ksplit > (num_pix_tiles + 3) / 4) ksplit = (num_pix_tiles + 3) / 4;
+        if (ksplit < 1) ksplit = 1;
+    } else {
+        double best = 1e30;
+        const int sms = num_sms();
+        const int ks_max = num_pix_tiles < 256 ? num_pix_tiles : 256;
+        for (int ks = 1; ks <= ks_max; ++ks) {
+            const int tps = (num_pix_tiles + ks - 1) / ks;
+            const int ks_eff = (num_pix_tiles + tps - 1) / tps;
+            const long ctas = (long)base_items * ks_eff;
+            const long waves = (ctas + sms - 1) / sms;
+            const double cost = (double)waves * (tps + c_over);
+            if (cost < best - 1e-9) { best = cost; ksplit = ks_eff; }
+        }
+    }
+    const int tps = (num_pix_tiles + ksplit - 1) / ksplit;
+    *tiles_per_split_out = tps;
+    return (num_pix_tiles + tps - 1) / tps;
+}
+
 // tile (wt, ht, nt) with wt a multiple of 16 (a 16-pixel MMA K step must stay inside one tile row), product 128
 static bool wg_choose_tile_row3(int n, int h, int w, int* wt_o, int* ht_o, int* nt_o) {
     double best = -1.0;
@@ -419,12 +450,7 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     if (wp.stages > 4) wp.stages = 4;
     if (wp.stages < 2) return 0;
     const int base_items = (wp.stack ? 2 : 3) * wp.num_m_tiles * wp.num_n_tiles;
-    static const int waves_x2 = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 3;   // CTAs = SMs * waves_x2 / 2 (sweep: profiles/r2f_wgrad_knobs.log)
-    int ksplit = (waves_x2 * num_sms() / 2 + base_items - 1) / base_items;
-    if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
-    if (ksplit < 1) ksplit = 1;
-    wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;
-    wp.ksplit = (wp.num_pix_tiles + wp.tiles_per_split - 1) / wp.tiles_per_split;
+    wp.ksplit = wg_choose_ksplit(base_items, wp.num_pix_tiles, &wp.tiles_per_split);
 
     CUtensorMap dym, xhm;
     {
@@ -487,13 +513,8 @@ static int wgrad_impl(const vu_conv_args* a, const void* dy, int dy_ctot, int dy
     wp.num_m_tiles = (a->Cout + 127) / 128;
     wp.num_n_tiles = (a->Cin + bn - 1) / bn;
     const int base_items = wp.num_taps * wp.num_m_tiles * wp.num_n_tiles;
-    // K splits: fill ~2 waves of SMs, at least 4 k-iterations per item
-    static const int waves_x2 = getenv("VU_WGRAD_HALFWAVES") ? atoi(getenv("VU_WGRAD_HALFWAVES")) : 3;
-    int ksplit = (waves_x2 * num_sms() / 2 + base_items - 1) / base_items;
-    if (ksplit > (wp.num_pix_tiles + 3) / 4) ksplit = (wp.num_pix_tiles + 3) / 4;
-    if (ksplit < 1) ksplit = 1;
-    wp.tiles_per_split = (wp.num_pix_tiles + ksplit - 1) / ksplit;
-    wp.ksplit = (wp.num_pix_tiles + wp.tiles_per_split - 1) / wp.tiles_per_split;
+    // K splits: cost model (wg_choose_ksplit)
+    wp.ksplit = wg_choose_ksplit(base_items, wp.num_pix_tiles, &wp.tiles_per_split);
 
     const uint32_t box[4] = {64u, (uint32_t)wp.wt, (uint32_t)wp.ht, (uint32_t)wp.nt};
     CUtensorMap dym, xm[4];
