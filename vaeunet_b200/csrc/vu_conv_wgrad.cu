@@ -436,7 +436,7 @@ static int wgrad_row3_try(const vu_conv_args* a, const void* dy, int dy_ctot, in
     wp.num_pix_tiles = wp.tiles_w * wp.tiles_h * wp.tiles_n;
     // measured on B200 (scripts/prof_wgrad.py): the row kernel wins from 2048 pixel tiles up (+30..60 %), the per-tap kernel
     // below 512 (three times more work items keep the K splits long enough to amortise prologue + reductions)
-    static const int row3_min = getenv("VU_WGRAD_ROW3_MIN") ? atoi(getenv("VU_WGRAD_ROW3_MIN")) : 1024;
+    static const int row3_min = getenv("VU_WGRAD_ROW3_MIN") ? atoi(getenv("VU_WGRAD_ROW3_MIN")) : 512;   // 1024 -> 512 with the cost-model K split: step 11.84 -> 11.77 ms (profiles/r2zs_row3min.log)
     if (wp.num_pix_tiles < row3_min && !getenv("VU_WGRAD_ROW3")) return 0;
     wp.cout = a->Cout; wp.cin = a->Cin; wp.dw = dw; wp.dtype = a->dtype;
     const int bn = (a->Cin > 64) ? 128 : 64;
