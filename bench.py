@@ -282,7 +282,13 @@ def bench_train(ctx: Ctx, steps: int, warmup: int, dtype_name: str):
     model = UNetResNet(**kw)
     model.load_state_dict(sd)
     model = model.to(dev).train()
-    pg = dist.group.WORLD if dist is not None else None
+    pg = None
+    if dist is not None:
+        from vaeunet_b200.distributed import gradient_group
+        # 0 = the default communicator. A CTA-limited communicator was tried against SM contention with the persistent conv
+        # kernels and lost: 2 GPUs 12.01 ms/step (default) vs 12.48 (2 CTAs) vs 15.04 (1 CTA), profiles/r2zv_nccl_ctas.log
+        ctas = int(os.environ.get("VU_DP_NCCL_CTAS", "0"))
+        pg = gradient_group(ctas) if ctas > 0 else dist.group.WORLD
     f16 = dtype_name == "f16"
     ts = TrainStep(model, lesion="EX", dtype=ops.F16 if f16 else ops.BF16, loss_scale=1024.0 if f16 else 1.0, process_group=pg)
     B, POOL = TRAIN_B, 4                       # 4 x (50 MB images + 17 MB masks) > L2; activations are GBs per step

@@ -205,3 +205,24 @@ def tiled_image_mc(model, img: torch.Tensor, num_samples: int, patch_size: int =
                            group)
     res["mu"], res["logvar"] = mu, lv
     return res
+
+
+def gradient_group(max_ctas: int = 2):
+    """A process group for the data-parallel gradient all-reduces that NCCL may run on at most `max_ctas` CTAs.
+
+    The training step's convolutions are persistent kernels sized to all 148 SMs; an NCCL kernel that takes 8-16 SMs while a
+    bucket is reduced turns their single wave into a wave plus a tail. The gradients need ~12 GB/s (122 MB per ~10 ms step) of
+    the 900 GB/s NVLink offers, so two CTAs looked plenty - measured, they are not: the
+    reductions then run long enough to be exposed at the end of the backward (2 GPUs: 12.01 ms/step on the default communicator,
+    12.48 with 2 CTAs, 15.04 with 1), so nothing uses this by default (bench.py: VU_DP_NCCL_CTAS). Falls back to the default group when this torch / NCCL cannot take a
+    per-communicator CTA limit."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return None
+    try:
+        opts = dist.ProcessGroupNCCL.Options()
+        opts.config.max_ctas = int(max_ctas)
+        opts.config.min_ctas = 1
+        return dist.new_group(backend="nccl", pg_options=opts)
+    except Exception:
+        return dist.group.WORLD
