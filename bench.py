@@ -698,7 +698,9 @@ def bench_cfg5(ctx: Ctx):
         u8 = host.to(dev, non_blocking=True) if e2e else dev_u8
         img = ops.tile_gather(u8, zero, H, W, 255.0)                     # uint8 HWC -> fp32 [1,3,H,W] on the device
         res = D.tiled_image_mc(model, img, N, 512, 100, 1.0, batch_size=args.tile_batch, eps=eps, group=None)
-        if e2e:
+        if e2e and ctx.rank == 0:
+            # one image = ONE set of result maps: every rank holds them after the all-gather, rank 0 hands them to the host
+            # (all ranks copying 147 MB each over a shared host link doubled the step at 8 GPUs: 15.0 -> 29.4 ms)
             for k in OUTS:
                 hmaps[k].copy_(res[k], non_blocking=True)
 
